@@ -1,0 +1,214 @@
+/*
+ * rt_abi.h -- C ABI of the B200 sphere ray tracer (librt_b200.so).
+ *
+ * This is the drop-in boundary for ONE path of tristanGIANDO/python_ray_tracer:
+ * NumpyRenderer.raytrace_scene and everything it calls.  The reference is pure
+ * Python/NumPy and has no FFI of its own; the entry points below are what a ctypes
+ * binding inside the reference's Renderer port would bind (INTEGRATION.md shows the
+ * stub).  Every entry point names the reference interface it replaces
+ * (paths relative to the reference tree).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types;
+ *   - every function returns RT_OK (0) or a negative rt_status; rt_last_error()
+ *     gives a thread-local message for the last failure;
+ *   - "_dev" pointers are CUDA device pointers owned by the caller, "_host"
+ *     pointers are ordinary host memory owned by the caller;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default
+ *     stream).  Device entry points only enqueue work on `stream`; they do not
+ *     synchronise.  Host entry points are synchronous;
+ *   - the library keeps no scene state between calls.  The host entry points
+ *     keep a per-thread, per-device staging cache (pinned + device scratch) that
+ *     rt_release_cache() frees.
+ *
+ * Scene layout ("sphere SoA"): a field-major table of doubles,
+ *     spheres[f * n_spheres + s],  f in rt_sphere_field,  s = shape index
+ * in the order of Scene3D.shapes (domain.py:53-59).  Point lights: point_lights
+ * [k * 3 + axis] in the order they appear in Scene3D.lights.
+ */
+#ifndef RT_ABI_H
+#define RT_ABI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* The reference's miss sentinel (base.py:12, shader.py:10). */
+#define RT_FARAWAY 1.0e39
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_BAD_ARG = -1,     /* NULL pointer, negative size, unknown enum value          */
+    RT_ERR_CUDA = -2,        /* a CUDA runtime call failed; see rt_last_error()          */
+    RT_ERR_NO_DEVICE = -3,   /* no CUDA device / device index out of range               */
+    RT_ERR_UNSUPPORTED = -4  /* valid request this build cannot serve                    */
+} rt_status;
+
+/* Rows of the sphere SoA.  Geometry: NumpySphere(center, radius, shader)
+ * (shape.py:17-26).  Material: NumpyShader(...) (shader.py:36-54); reflection_gain is
+ * stored by the reference and never read, so it is not carried. */
+typedef enum rt_sphere_field {
+    RT_F_CX = 0,
+    RT_F_CY = 1,
+    RT_F_CZ = 2,
+    RT_F_RADIUS = 3,
+    RT_F_DIFFUSE_GAIN = 4,
+    RT_F_SPECULAR_GAIN = 5,
+    RT_F_SPECULAR_ROUGHNESS = 6,
+    RT_F_IRIDESCENCE_GAIN = 7,
+    RT_F_COLOR_R = 8,  /* Texture.color (shader.py:13-19); ignored by the checker      */
+    RT_F_COLOR_G = 9,
+    RT_F_COLOR_B = 10,
+    RT_F_TEXTURE = 11, /* 0.0 = Texture (constant), 1.0 = TextureChecker (shader.py:22-32) */
+    RT_SPHERE_FIELDS = 12
+} rt_sphere_field;
+
+#define RT_MAX_DOME_LIGHTS 8
+
+/* Everything of Scene3D that is not a shape (domain.py:26-40, 53-59) plus the
+ * trace options.  Passed by pointer, read on the host. */
+typedef struct rt_env {
+    double eye[3];               /* scene.camera.position: target of "direction to ray
+                                    origin" at every bounce (shader.py:76)               */
+    int32_t n_point_lights;      /* rows in the point-light table (>= 1)                 */
+    int32_t n_dome_lights;       /* <= RT_MAX_DOME_LIGHTS; the host folds any excess
+                                    into the last slot                                    */
+    double dome_intensity[RT_MAX_DOME_LIGHTS]; /* DomeLight.intensity in list order
+                                    (shader.py:239-242)                                   */
+    double dome_color[3];        /* colour of the LAST DomeLight, (1,1,1) if none
+                                    (shader.py:237-241)                                   */
+    int32_t max_depth;           /* number of ray generations traced; primary rays are
+                                    generation 0 and rays of generation >= max_depth
+                                    return black.  <= 0: unlimited, like the reference
+                                    (shader.py:143-161 has no cap)                        */
+    int32_t mode;                /* rt_mode                                               */
+    int32_t flags;               /* rt_flags                                              */
+    int32_t reserved;
+    double cutoff;               /* RT_MODE_FAST only: stop a bounce chain once its
+                                    remaining contribution is provably below this
+                                    (linear units).  0 = never cut.                       */
+} rt_env;
+
+typedef enum rt_mode {
+    RT_MODE_EXACT = 0, /* all-FP64, reference operation order, no FMA contraction        */
+    RT_MODE_FAST = 1   /* FP64 geometry, restructured arithmetic, throughput cutoff      */
+} rt_mode;
+
+typedef enum rt_flags {
+    RT_FLAG_NONE = 0,
+    RT_FLAG_ALL_POINT_LIGHTS = 1 /* extension (main.py:45 TODO): sum diffuse/specular and
+                                    shadow over every point light.  Off = reference
+                                    semantics: only lights[0] shades (shader.py:75).     */
+} rt_flags;
+
+/* Camera(position, width, height) (domain.py:14-23). */
+typedef struct rt_camera {
+    double position[3];
+    int32_t width;
+    int32_t height;
+} rt_camera;
+
+typedef enum rt_dtype { RT_DTYPE_F32 = 0, RT_DTYPE_F64 = 1 } rt_dtype;
+
+/* Work counters a launch adds into (device memory, 4 x uint64, caller zeroes):
+ * [0] rays traced (all generations), [1] hits shaded, [2] deepest generation reached + 1,
+ * [3] sphere tests evaluated. */
+#define RT_STATS_WORDS 4
+
+int rt_abi_version(void);
+const char* rt_last_error(void);
+int rt_device_count(int* count_out);
+int rt_release_cache(void);
+
+/*
+ * rt_render_rows_dev -- camera rays for image rows [row0, row1) of cam.
+ * Replaces NumpyRenderer.get_ray_directions (base.py:123-141) followed by
+ * NumpyRenderer.raytrace_scene (base.py:91-121) on those pixels, including every
+ * NumpyShader.create it triggers (shader.py:63-112).
+ *   spheres_dev       sphere SoA, RT_SPHERE_FIELDS x n_spheres doubles
+ *   point_lights_dev  env->n_point_lights x 3 doubles
+ *   rgb_dev           planar linear RGB of the band: channel c of pixel p (row-major
+ *                     inside the band, p = (row-row0)*width + col) is at
+ *                     rgb_dev[c*plane_stride + p], element type rgb_dtype.  May be NULL.
+ *   rgba8_dev         optional: 4 bytes per pixel, uint8(255*clip(v,0,1)) truncating
+ *                     (base.py:143-151) in R,G,B and 255 in A.  May be NULL.
+ *   stats_dev         optional RT_STATS_WORDS x uint64 counters, or NULL.
+ */
+int rt_render_rows_dev(int device, const double* spheres_dev, int32_t n_spheres,
+                       const double* point_lights_dev, const rt_env* env,
+                       const rt_camera* cam, int32_t row0, int32_t row1, void* rgb_dev,
+                       int32_t rgb_dtype, int64_t plane_stride, uint8_t* rgba8_dev,
+                       uint64_t* stats_dev, void* stream);
+
+/*
+ * rt_trace_rays_dev -- an arbitrary batch of n rays.
+ * Replaces NumpyRenderer.raytrace_scene(ray_origin, normalized_ray_direction, scene)
+ * (base.py:91-121) for callers that bring their own rays.
+ *   origins_dev     3 x n doubles, planar (x plane, y plane, z plane), or NULL to
+ *                   broadcast origin0 to every ray (the primary-ray case, where the
+ *                   reference passes scalar origins)
+ *   directions_dev  3 x n doubles, planar
+ *   rgb_dev         as above with p = ray index
+ */
+int rt_trace_rays_dev(int device, const double* spheres_dev, int32_t n_spheres,
+                      const double* point_lights_dev, const rt_env* env,
+                      const double* origins_dev, const double* origin0,
+                      const double* directions_dev, int64_t n_rays, void* rgb_dev,
+                      int32_t rgb_dtype, int64_t plane_stride, uint64_t* stats_dev,
+                      void* stream);
+
+/*
+ * rt_ray_directions_dev -- materialise the unit primary directions of rows
+ * [row0,row1) as 3 planes of doubles.  Replaces NumpyRenderer.get_ray_directions
+ * (base.py:123-141) for callers that want the array itself.
+ */
+int rt_ray_directions_dev(int device, const rt_camera* cam, int32_t row0, int32_t row1,
+                          double* directions_dev, int64_t plane_stride, void* stream);
+
+/*
+ * rt_sphere_distance_dev -- distance from each ray's origin to one sphere along the
+ * ray, RT_FARAWAY on a miss.  Replaces NumpySphere.intersect (shape.py:28-51).
+ *   origins_dev / origin0 / directions_dev  as in rt_trace_rays_dev
+ *   center        3 doubles (host)
+ *   mode          rt_mode: RT_MODE_EXACT evaluates the reference's expression
+ *   distance_dev  n doubles
+ */
+int rt_sphere_distance_dev(int device, const double* origins_dev, const double* origin0,
+                           const double* directions_dev, int64_t n_rays, const double* center,
+                           double radius, int32_t mode, double* distance_dev, void* stream);
+
+/*
+ * rt_quantize_dev -- uint8(255*clip(v,0,1)), truncating, planar -> interleaved.
+ * Replaces the arithmetic of NumpyRenderer.save_image (base.py:143-151); the PNG
+ * container is written by the host.
+ *   channels_out  3 (RGB) or 4 (RGBA, A = 255)
+ */
+int rt_quantize_dev(int device, const void* rgb_dev, int32_t rgb_dtype, int64_t plane_stride,
+                    int64_t n_pixels, uint8_t* out_dev, int32_t channels_out, void* stream);
+
+/*
+ * Host-buffer entry points: the same operations with ordinary host memory on both
+ * sides; uploads, launches, downloads and synchronises internally.
+ *   rgb_host    planar, 3 x n doubles or floats (plane stride = n), may be NULL
+ *   rgb8_host   interleaved RGB bytes (3 per pixel), may be NULL
+ *   stats_host  RT_STATS_WORDS x uint64, may be NULL
+ */
+int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spheres,
+                         const double* point_lights_host, const rt_env* env,
+                         const rt_camera* cam, int32_t row0, int32_t row1, void* rgb_host,
+                         int32_t rgb_dtype, uint8_t* rgb8_host, uint64_t* stats_host);
+
+int rt_trace_rays_host(int device, const double* spheres_host, int32_t n_spheres,
+                       const double* point_lights_host, const rt_env* env,
+                       const double* origins_host, const double* origin0,
+                       const double* directions_host, int64_t n_rays, void* rgb_host,
+                       int32_t rgb_dtype, uint64_t* stats_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_ABI_H */
