@@ -125,6 +125,15 @@ int rt_device_count(int* count_out);
 int rt_release_cache(void);
 
 /*
+ * rt_measure_fma_peak -- achieved FLOP/s (2 per FMA) of a register-resident chain of
+ * independent FMAs of `dtype` (rt_dtype) on every SM of `device`: the ALU roofline
+ * denominator of the trace kernel, measured on the GPU it runs on.  Nothing in the
+ * reference corresponds to it (the reference reports one wall-clock print,
+ * main.py:55-57); it exists for the measurement contract only.  Synchronous.
+ */
+int rt_measure_fma_peak(int device, int32_t dtype, double* flops_out);
+
+/*
  * rt_render_rows_dev -- camera rays for image rows [row0, row1) of cam.
  * Replaces NumpyRenderer.get_ray_directions (base.py:123-141) followed by
  * NumpyRenderer.raytrace_scene (base.py:91-121) on those pixels, including every

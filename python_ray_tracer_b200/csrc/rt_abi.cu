@@ -1,0 +1,278 @@
+// rt_abi.cu -- the C ABI of include/rt_abi.h over the kernels of trace_exact.cu /
+// trace_fast.cu.  Plain pointers and sizes in, status codes out; no state besides a
+// per-thread staging cache used by the *_host entry points.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/rt_abi.h"
+#include "rt_launch.h"
+
+namespace {
+
+thread_local char g_error[512] = "";
+
+int fail(int status, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+    return status;
+}
+
+int cuda_fail(cudaError_t err, const char* what) {
+    return fail(RT_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorString(err), cudaGetErrorName(err));
+}
+
+#define RT_CUDA(call)                                          \
+    do {                                                       \
+        cudaError_t err__ = (call);                            \
+        if (err__ != cudaSuccess) return cuda_fail(err__, #call); \
+    } while (0)
+
+// Makes `device` current for the scope and restores the caller's device afterwards, so
+// the library never disturbs the host framework's notion of the current device.
+struct DeviceScope {
+    int previous = -1;
+    int status = RT_OK;
+    explicit DeviceScope(int device) {
+        int count = 0;
+        cudaError_t err = cudaGetDeviceCount(&count);
+        if (err != cudaSuccess || count == 0) {
+            status = fail(RT_ERR_NO_DEVICE, "no CUDA device: %s", cudaGetErrorString(err));
+            return;
+        }
+        if (device < 0 || device >= count) {
+            status = fail(RT_ERR_NO_DEVICE, "device %d out of range (0..%d)", device, count - 1);
+            return;
+        }
+        cudaGetDevice(&previous);
+        if (previous != device) {
+            err = cudaSetDevice(device);
+            if (err != cudaSuccess) status = cuda_fail(err, "cudaSetDevice");
+        }
+    }
+    ~DeviceScope() {
+        int now = -1;
+        if (previous >= 0 && cudaGetDevice(&now) == cudaSuccess && now != previous) cudaSetDevice(previous);
+    }
+};
+
+int check_env(const rt_env* env, int32_t n_spheres) {
+    if (env == nullptr) return fail(RT_ERR_BAD_ARG, "env is NULL");
+    if (n_spheres <= 0) return fail(RT_ERR_BAD_ARG, "n_spheres = %d (scene has no shapes)", n_spheres);
+    if (env->n_point_lights < 1) return fail(RT_ERR_BAD_ARG, "n_point_lights = %d; lights[0] must be a point light", env->n_point_lights);
+    if (env->n_dome_lights < 0 || env->n_dome_lights > RT_MAX_DOME_LIGHTS)
+        return fail(RT_ERR_BAD_ARG, "n_dome_lights = %d outside 0..%d", env->n_dome_lights, RT_MAX_DOME_LIGHTS);
+    if (env->mode != RT_MODE_EXACT && env->mode != RT_MODE_FAST) return fail(RT_ERR_BAD_ARG, "unknown mode %d", env->mode);
+    if (!(env->cutoff >= 0.0)) return fail(RT_ERR_BAD_ARG, "cutoff must be >= 0");
+    if (n_spheres > rt::max_staged_spheres())
+        return fail(RT_ERR_UNSUPPORTED, "%d spheres exceed the %d that fit one block's shared memory", n_spheres,
+                    rt::max_staged_spheres());
+    return RT_OK;
+}
+
+int check_camera(const rt_camera* cam, int32_t row0, int32_t row1) {
+    if (cam == nullptr) return fail(RT_ERR_BAD_ARG, "camera is NULL");
+    if (cam->width <= 0 || cam->height <= 0) return fail(RT_ERR_BAD_ARG, "camera size %dx%d", cam->width, cam->height);
+    if (row0 < 0 || row1 > cam->height || row0 > row1) return fail(RT_ERR_BAD_ARG, "rows [%d,%d) outside 0..%d", row0, row1, cam->height);
+    return RT_OK;
+}
+
+rt::SceneParams scene_params(const double* spheres_dev, int32_t n_spheres, const double* lights_dev, const rt_env* env) {
+    rt::SceneParams sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.spheres = spheres_dev;
+    sp.lights = lights_dev;
+    sp.n_spheres = n_spheres;
+    sp.n_lights_used = (env->flags & RT_FLAG_ALL_POINT_LIGHTS) ? env->n_point_lights : 1;
+    sp.n_dome = env->n_dome_lights;
+    sp.max_depth = env->max_depth;
+    double sum = 0.0;
+    for (int i = 0; i < 3; ++i) sp.eye[i] = env->eye[i];
+    for (int i = 0; i < env->n_dome_lights; ++i) {
+        sp.dome_intensity[i] = env->dome_intensity[i];
+        sum += env->dome_intensity[i];
+    }
+    sp.dome_sum = sum;
+    for (int i = 0; i < 3; ++i) sp.dome_color[i] = env->dome_color[i];
+    sp.cutoff = env->mode == RT_MODE_FAST ? env->cutoff : 0.0;
+    return sp;
+}
+
+// The screen rectangle and linspace steps of base.py:130-139, evaluated in the same
+// double arithmetic Python uses.
+rt::CameraParams camera_params(const rt_camera* cam, int32_t row0, int32_t row1) {
+    rt::CameraParams cp;
+    for (int i = 0; i < 3; ++i) cp.cam[i] = cam->position[i];
+    const double aspect = (double)cam->width / (double)cam->height;
+    cp.x_start = -1.0;
+    cp.x_stop = 1.0;
+    cp.y_start = 1.0 / aspect + 0.25;
+    cp.y_stop = -1.0 / aspect + 0.25;
+    cp.x_step = cam->width > 1 ? (cp.x_stop - cp.x_start) / (double)(cam->width - 1) : 0.0;
+    cp.y_step = cam->height > 1 ? (cp.y_stop - cp.y_start) / (double)(cam->height - 1) : 0.0;
+    cp.width = cam->width;
+    cp.height = cam->height;
+    cp.row0 = row0;
+    cp.row1 = row1;
+    return cp;
+}
+
+const rt::Launchers& launchers(int mode) { return mode == RT_MODE_FAST ? rt::fast_launchers() : rt::exact_launchers(); }
+
+// uint8(255*clip(v,0,1)) truncating (base.py:143-151), planar -> interleaved.
+template <typename T, int CH>
+__global__ void quantize_kernel(const T* rgb, long long plane_stride, long long n, uint8_t* out) {
+    const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    unsigned int q[3];
+    for (int c = 0; c < 3; ++c) {
+        double v = (double)rgb[c * plane_stride + p];
+        v = fmin(fmax(v, 0.0), 1.0);
+        q[c] = (unsigned int)(255.0 * v);
+    }
+    if (CH == 4) {
+        reinterpret_cast<uchar4*>(out)[p] = make_uchar4((unsigned char)q[0], (unsigned char)q[1], (unsigned char)q[2], 255);
+    } else {
+        out[3 * p + 0] = (uint8_t)q[0];
+        out[3 * p + 1] = (uint8_t)q[1];
+        out[3 * p + 2] = (uint8_t)q[2];
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_abi_version(void) { return RT_ABI_VERSION; }
+
+const char* rt_last_error(void) { return g_error; }
+
+// not part of the ABI: lets rt_abi_host.cu record a message (hidden from the dynamic table)
+__attribute__((visibility("hidden"))) void rt_internal_set_error(const char* message) {
+    snprintf(g_error, sizeof(g_error), "%s", message);
+}
+
+int rt_device_count(int* count_out) {
+    if (count_out == nullptr) return fail(RT_ERR_BAD_ARG, "count_out is NULL");
+    int count = 0;
+    cudaError_t err = cudaGetDeviceCount(&count);
+    if (err != cudaSuccess) {
+        *count_out = 0;
+        return fail(RT_ERR_NO_DEVICE, "cudaGetDeviceCount: %s", cudaGetErrorString(err));
+    }
+    *count_out = count;
+    return RT_OK;
+}
+
+int rt_render_rows_dev(int device, const double* spheres_dev, int32_t n_spheres, const double* point_lights_dev,
+                       const rt_env* env, const rt_camera* cam, int32_t row0, int32_t row1, void* rgb_dev,
+                       int32_t rgb_dtype, int64_t plane_stride, uint8_t* rgba8_dev, uint64_t* stats_dev,
+                       void* stream) {
+    int rc;
+    if ((rc = check_env(env, n_spheres)) != RT_OK) return rc;
+    if ((rc = check_camera(cam, row0, row1)) != RT_OK) return rc;
+    if (spheres_dev == nullptr || point_lights_dev == nullptr) return fail(RT_ERR_BAD_ARG, "scene pointers are NULL");
+    if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return fail(RT_ERR_BAD_ARG, "unknown rgb_dtype %d", rgb_dtype);
+    const int64_t n = (int64_t)(row1 - row0) * cam->width;
+    if (rgb_dev != nullptr && plane_stride < n) return fail(RT_ERR_BAD_ARG, "plane_stride %lld < %lld pixels", (long long)plane_stride, (long long)n);
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    rt::OutputParams out = {rgb_dev, rgba8_dev, reinterpret_cast<unsigned long long*>(stats_dev), plane_stride,
+                            rgb_dtype == RT_DTYPE_F64};
+    cudaError_t err = launchers(env->mode).render_rows(stats_dev != nullptr, scene_params(spheres_dev, n_spheres, point_lights_dev, env),
+                                                      camera_params(cam, row0, row1), out, static_cast<cudaStream_t>(stream));
+    if (err != cudaSuccess) return cuda_fail(err, "render_rows launch");
+    return RT_OK;
+}
+
+int rt_trace_rays_dev(int device, const double* spheres_dev, int32_t n_spheres, const double* point_lights_dev,
+                      const rt_env* env, const double* origins_dev, const double* origin0,
+                      const double* directions_dev, int64_t n_rays, void* rgb_dev, int32_t rgb_dtype,
+                      int64_t plane_stride, uint64_t* stats_dev, void* stream) {
+    int rc;
+    if ((rc = check_env(env, n_spheres)) != RT_OK) return rc;
+    if (spheres_dev == nullptr || point_lights_dev == nullptr) return fail(RT_ERR_BAD_ARG, "scene pointers are NULL");
+    if (n_rays < 0) return fail(RT_ERR_BAD_ARG, "n_rays = %lld", (long long)n_rays);
+    if (n_rays > 0 && directions_dev == nullptr) return fail(RT_ERR_BAD_ARG, "directions are NULL");
+    if (origins_dev == nullptr && origin0 == nullptr) return fail(RT_ERR_BAD_ARG, "no ray origin given");
+    if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return fail(RT_ERR_BAD_ARG, "unknown rgb_dtype %d", rgb_dtype);
+    if (rgb_dev == nullptr) return fail(RT_ERR_BAD_ARG, "rgb_dev is NULL");
+    if (plane_stride < n_rays) return fail(RT_ERR_BAD_ARG, "plane_stride %lld < %lld rays", (long long)plane_stride, (long long)n_rays);
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    rt::RayBatch rb;
+    rb.origins = origins_dev;
+    rb.directions = directions_dev;
+    for (int i = 0; i < 3; ++i) rb.origin0[i] = origin0 != nullptr ? origin0[i] : 0.0;
+    rb.n = n_rays;
+    rt::OutputParams out = {rgb_dev, nullptr, reinterpret_cast<unsigned long long*>(stats_dev), plane_stride,
+                            rgb_dtype == RT_DTYPE_F64};
+    cudaError_t err = launchers(env->mode).trace_rays(stats_dev != nullptr, scene_params(spheres_dev, n_spheres, point_lights_dev, env), rb,
+                                                     out, static_cast<cudaStream_t>(stream));
+    if (err != cudaSuccess) return cuda_fail(err, "trace_rays launch");
+    return RT_OK;
+}
+
+int rt_ray_directions_dev(int device, const rt_camera* cam, int32_t row0, int32_t row1, double* directions_dev,
+                          int64_t plane_stride, void* stream) {
+    int rc;
+    if ((rc = check_camera(cam, row0, row1)) != RT_OK) return rc;
+    if (directions_dev == nullptr) return fail(RT_ERR_BAD_ARG, "directions_dev is NULL");
+    if (plane_stride < (int64_t)(row1 - row0) * cam->width) return fail(RT_ERR_BAD_ARG, "plane_stride too small");
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    cudaError_t err = rt::exact_launchers().ray_directions(camera_params(cam, row0, row1), directions_dev, plane_stride,
+                                                           static_cast<cudaStream_t>(stream));
+    if (err != cudaSuccess) return cuda_fail(err, "ray_directions launch");
+    return RT_OK;
+}
+
+int rt_sphere_distance_dev(int device, const double* origins_dev, const double* origin0, const double* directions_dev,
+                           int64_t n_rays, const double* center, double radius, int32_t mode, double* distance_dev,
+                           void* stream) {
+    if (n_rays < 0) return fail(RT_ERR_BAD_ARG, "n_rays = %lld", (long long)n_rays);
+    if (center == nullptr || distance_dev == nullptr || (n_rays > 0 && directions_dev == nullptr))
+        return fail(RT_ERR_BAD_ARG, "NULL pointer");
+    if (origins_dev == nullptr && origin0 == nullptr) return fail(RT_ERR_BAD_ARG, "no ray origin given");
+    if (mode != RT_MODE_EXACT && mode != RT_MODE_FAST) return fail(RT_ERR_BAD_ARG, "unknown mode %d", mode);
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    rt::RayBatch rb;
+    rb.origins = origins_dev;
+    rb.directions = directions_dev;
+    for (int i = 0; i < 3; ++i) rb.origin0[i] = origin0 != nullptr ? origin0[i] : 0.0;
+    rb.n = n_rays;
+    cudaError_t err = launchers(mode).sphere_distance(rb, center, radius, distance_dev, static_cast<cudaStream_t>(stream));
+    if (err != cudaSuccess) return cuda_fail(err, "sphere_distance launch");
+    return RT_OK;
+}
+
+int rt_quantize_dev(int device, const void* rgb_dev, int32_t rgb_dtype, int64_t plane_stride, int64_t n_pixels,
+                    uint8_t* out_dev, int32_t channels_out, void* stream) {
+    if (rgb_dev == nullptr || out_dev == nullptr) return fail(RT_ERR_BAD_ARG, "NULL pointer");
+    if (n_pixels < 0 || plane_stride < n_pixels) return fail(RT_ERR_BAD_ARG, "bad sizes");
+    if (channels_out != 3 && channels_out != 4) return fail(RT_ERR_BAD_ARG, "channels_out must be 3 or 4");
+    if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return fail(RT_ERR_BAD_ARG, "unknown rgb_dtype %d", rgb_dtype);
+    if (n_pixels == 0) return RT_OK;
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const unsigned int grid = (unsigned int)((n_pixels + 255) / 256);
+    if (rgb_dtype == RT_DTYPE_F64) {
+        if (channels_out == 4) quantize_kernel<double, 4><<<grid, 256, 0, s>>>((const double*)rgb_dev, plane_stride, n_pixels, out_dev);
+        else quantize_kernel<double, 3><<<grid, 256, 0, s>>>((const double*)rgb_dev, plane_stride, n_pixels, out_dev);
+    } else {
+        if (channels_out == 4) quantize_kernel<float, 4><<<grid, 256, 0, s>>>((const float*)rgb_dev, plane_stride, n_pixels, out_dev);
+        else quantize_kernel<float, 3><<<grid, 256, 0, s>>>((const float*)rgb_dev, plane_stride, n_pixels, out_dev);
+    }
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) return cuda_fail(err, "quantize launch");
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,201 @@
+// rt_abi_host.cu -- the host-buffer entry points of include/rt_abi.h: upload the scene,
+// launch through the device entry points, download the result, synchronise.
+//
+// A per-thread cache keeps one device scratch area (scene tables, rays, outputs,
+// counters) per device and a private stream, grown on demand and reused across calls;
+// rt_release_cache() frees it.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/rt_abi.h"
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+
+struct Scratch {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+};
+
+struct DeviceCache {
+    cudaStream_t stream = nullptr;
+    Scratch scene, rays, rgb, rgb8, stats;
+};
+
+thread_local DeviceCache g_cache[kMaxDevices];
+// defined in rt_abi.cu: records the message rt_last_error() returns
+extern "C" void rt_internal_set_error(const char* message);
+
+cudaError_t reserve(Scratch& s, size_t bytes) {
+    if (bytes <= s.bytes) return cudaSuccess;
+    if (s.ptr != nullptr) cudaFree(s.ptr);
+    s.ptr = nullptr;
+    s.bytes = 0;
+    size_t want = bytes + bytes / 4 + 256;
+    cudaError_t err = cudaMalloc(&s.ptr, want);
+    if (err == cudaSuccess) s.bytes = want;
+    return err;
+}
+
+void release(Scratch& s) {
+    if (s.ptr != nullptr) cudaFree(s.ptr);
+    s.ptr = nullptr;
+    s.bytes = 0;
+}
+
+int host_fail(int status, const char* message) {
+    rt_internal_set_error(message);
+    return status;
+}
+
+struct Restore {
+    int previous = -1;
+    ~Restore() {
+        if (previous >= 0) cudaSetDevice(previous);
+    }
+};
+
+#define HOST_CUDA(call)                                                                      \
+    do {                                                                                     \
+        cudaError_t err__ = (call);                                                          \
+        if (err__ != cudaSuccess) {                                                          \
+            char msg__[256];                                                                 \
+            snprintf(msg__, sizeof(msg__), "%s: %s", #call, cudaGetErrorString(err__));      \
+            rt_internal_set_error(msg__);                                                    \
+            return RT_ERR_CUDA;                                                              \
+        }                                                                                    \
+    } while (0)
+
+// Uploads the sphere SoA and the light table into the cache; returns device pointers.
+int upload_scene(DeviceCache& c, const double* spheres_host, int32_t n_spheres, const double* lights_host,
+                 int32_t n_lights, const double** spheres_dev, const double** lights_dev) {
+    const size_t sphere_bytes = sizeof(double) * RT_SPHERE_FIELDS * (size_t)n_spheres;
+    const size_t light_bytes = sizeof(double) * 3 * (size_t)n_lights;
+    HOST_CUDA(reserve(c.scene, sphere_bytes + light_bytes));
+    char* base = static_cast<char*>(c.scene.ptr);
+    HOST_CUDA(cudaMemcpyAsync(base, spheres_host, sphere_bytes, cudaMemcpyHostToDevice, c.stream));
+    HOST_CUDA(cudaMemcpyAsync(base + sphere_bytes, lights_host, light_bytes, cudaMemcpyHostToDevice, c.stream));
+    *spheres_dev = reinterpret_cast<const double*>(base);
+    *lights_dev = reinterpret_cast<const double*>(base + sphere_bytes);
+    return RT_OK;
+}
+
+int enter(int device, Restore& restore, DeviceCache** cache) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return host_fail(RT_ERR_NO_DEVICE, "host entry point: no CUDA device or device index out of range");
+    if (device < 0 || device >= count || device >= kMaxDevices) return host_fail(RT_ERR_NO_DEVICE, "host entry point: no CUDA device or device index out of range");
+    cudaGetDevice(&restore.previous);
+    HOST_CUDA(cudaSetDevice(device));
+    DeviceCache& c = g_cache[device];
+    if (c.stream == nullptr) HOST_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    *cache = &c;
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_release_cache(void) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) return RT_OK;
+    Restore restore;
+    cudaGetDevice(&restore.previous);
+    for (int d = 0; d < count && d < kMaxDevices; ++d) {
+        DeviceCache& c = g_cache[d];
+        if (c.stream == nullptr && c.scene.ptr == nullptr) continue;
+        cudaSetDevice(d);
+        release(c.scene);
+        release(c.rays);
+        release(c.rgb);
+        release(c.rgb8);
+        release(c.stats);
+        if (c.stream != nullptr) cudaStreamDestroy(c.stream);
+        c.stream = nullptr;
+    }
+    return RT_OK;
+}
+
+int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spheres, const double* point_lights_host,
+                         const rt_env* env, const rt_camera* cam, int32_t row0, int32_t row1, void* rgb_host,
+                         int32_t rgb_dtype, uint8_t* rgb8_host, uint64_t* stats_host) {
+    if (spheres_host == nullptr || point_lights_host == nullptr || env == nullptr || cam == nullptr) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    if (n_spheres <= 0 || env->n_point_lights < 1) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    if (cam->width <= 0 || cam->height <= 0 || row0 < 0 || row1 > cam->height || row0 > row1) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    Restore restore;
+    DeviceCache* c = nullptr;
+    int rc = enter(device, restore, &c);
+    if (rc != RT_OK) return rc;
+
+    const double *spheres_dev, *lights_dev;
+    if ((rc = upload_scene(*c, spheres_host, n_spheres, point_lights_host, env->n_point_lights, &spheres_dev, &lights_dev)) != RT_OK) return rc;
+    const int64_t n = (int64_t)(row1 - row0) * cam->width;
+    const size_t elem = rgb_dtype == RT_DTYPE_F64 ? 8 : 4;
+    // the quantiser reads the linear planes, so they are rendered even if only bytes are wanted
+    HOST_CUDA(reserve(c->rgb, (size_t)n * 3 * elem + 16));
+    if (rgb8_host != nullptr) HOST_CUDA(reserve(c->rgb8, (size_t)n * 3 + 16));
+    if (stats_host != nullptr) {
+        HOST_CUDA(reserve(c->stats, sizeof(uint64_t) * RT_STATS_WORDS));
+        HOST_CUDA(cudaMemsetAsync(c->stats.ptr, 0, sizeof(uint64_t) * RT_STATS_WORDS, c->stream));
+    }
+    rc = rt_render_rows_dev(device, spheres_dev, n_spheres, lights_dev, env, cam, row0, row1, c->rgb.ptr, rgb_dtype, n,
+                            nullptr, stats_host != nullptr ? static_cast<uint64_t*>(c->stats.ptr) : nullptr, c->stream);
+    if (rc != RT_OK) return rc;
+    if (rgb_host != nullptr && n > 0)
+        HOST_CUDA(cudaMemcpyAsync(rgb_host, c->rgb.ptr, (size_t)n * 3 * elem, cudaMemcpyDeviceToHost, c->stream));
+    if (rgb8_host != nullptr && n > 0) {
+        rc = rt_quantize_dev(device, c->rgb.ptr, rgb_dtype, n, n, static_cast<uint8_t*>(c->rgb8.ptr), 3, c->stream);
+        if (rc != RT_OK) return rc;
+        HOST_CUDA(cudaMemcpyAsync(rgb8_host, c->rgb8.ptr, (size_t)n * 3, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (stats_host != nullptr)
+        HOST_CUDA(cudaMemcpyAsync(stats_host, c->stats.ptr, sizeof(uint64_t) * RT_STATS_WORDS, cudaMemcpyDeviceToHost, c->stream));
+    HOST_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_trace_rays_host(int device, const double* spheres_host, int32_t n_spheres, const double* point_lights_host,
+                       const rt_env* env, const double* origins_host, const double* origin0,
+                       const double* directions_host, int64_t n_rays, void* rgb_host, int32_t rgb_dtype,
+                       uint64_t* stats_host) {
+    if (spheres_host == nullptr || point_lights_host == nullptr || env == nullptr || rgb_host == nullptr) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    if (n_spheres <= 0 || env->n_point_lights < 1 || n_rays < 0) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    if (n_rays > 0 && directions_host == nullptr) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    if (origins_host == nullptr && origin0 == nullptr) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return host_fail(RT_ERR_BAD_ARG, "host entry point: NULL pointer, bad size or unknown enum value");
+    Restore restore;
+    DeviceCache* c = nullptr;
+    int rc = enter(device, restore, &c);
+    if (rc != RT_OK) return rc;
+
+    const double *spheres_dev, *lights_dev;
+    if ((rc = upload_scene(*c, spheres_host, n_spheres, point_lights_host, env->n_point_lights, &spheres_dev, &lights_dev)) != RT_OK) return rc;
+    const size_t plane = sizeof(double) * 3 * (size_t)n_rays;
+    HOST_CUDA(reserve(c->rays, 2 * plane + 16));
+    double* dirs_dev = static_cast<double*>(c->rays.ptr);
+    double* orig_dev = origins_host != nullptr ? dirs_dev + 3 * n_rays : nullptr;
+    if (n_rays > 0) {
+        HOST_CUDA(cudaMemcpyAsync(dirs_dev, directions_host, plane, cudaMemcpyHostToDevice, c->stream));
+        if (orig_dev != nullptr) HOST_CUDA(cudaMemcpyAsync(orig_dev, origins_host, plane, cudaMemcpyHostToDevice, c->stream));
+    }
+    const size_t elem = rgb_dtype == RT_DTYPE_F64 ? 8 : 4;
+    HOST_CUDA(reserve(c->rgb, (size_t)n_rays * 3 * elem + 16));
+    if (stats_host != nullptr) {
+        HOST_CUDA(reserve(c->stats, sizeof(uint64_t) * RT_STATS_WORDS));
+        HOST_CUDA(cudaMemsetAsync(c->stats.ptr, 0, sizeof(uint64_t) * RT_STATS_WORDS, c->stream));
+    }
+    rc = rt_trace_rays_dev(device, spheres_dev, n_spheres, lights_dev, env, orig_dev, origin0, dirs_dev, n_rays, c->rgb.ptr,
+                           rgb_dtype, n_rays, stats_host != nullptr ? static_cast<uint64_t*>(c->stats.ptr) : nullptr, c->stream);
+    if (rc != RT_OK) return rc;
+    if (n_rays > 0) HOST_CUDA(cudaMemcpyAsync(rgb_host, c->rgb.ptr, (size_t)n_rays * 3 * elem, cudaMemcpyDeviceToHost, c->stream));
+    if (stats_host != nullptr)
+        HOST_CUDA(cudaMemcpyAsync(stats_host, c->stats.ptr, sizeof(uint64_t) * RT_STATS_WORDS, cudaMemcpyDeviceToHost, c->stream));
+    HOST_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+}  // extern "C"

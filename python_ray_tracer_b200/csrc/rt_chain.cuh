@@ -1,0 +1,212 @@
+// rt_chain.cuh -- scene staging and the register-resident bounce chain (device).
+#pragma once
+
+#include "rt_trace.cuh"
+
+namespace rt {
+
+struct Counters {
+    unsigned long long traced, hits, deepest, tests;
+};
+
+// Upper bound of |local colour| of one material (Fast cutoff).  local = ambient +
+// diffuse + dome + gain*(spec_base + gain*glint) + film, with F <= 1, G1(L) <= 1,
+// D <= a2/(pi*(min(1,a2^2)+eps)) and G1(V)/(4 NdotV + eps) <= 1/(2*(sqrt(min(a2,1))+eps)).
+__device__ __forceinline__ double material_bound(const SceneParams& sp, int s) {
+    Material m = load_material(sp, s);
+    double tex = m.checker ? 1.0 : fmax(fabs(m.r), fmax(fabs(m.g), fabs(m.b)));
+    double dome = fabs(sp.dome_sum) * fmax(fabs(sp.dome_color[0]), fmax(fabs(sp.dome_color[1]), fabs(sp.dome_color[2])));
+    double alpha = m.roughness * m.roughness;
+    double a2 = alpha * alpha;
+    double dmax = a2 / (kPi * (fmin(1.0, a2 * a2) + kEps));
+    double gv = 1.0 / (2.0 * (sqrt(fmin(a2, 1.0)) + kEps));
+    double g = fabs(m.specular_gain);
+    double spec = g * (dmax * gv + g);
+    double film = 1.4 * kFilmWeight * fabs(m.irid_gain);
+    return kAmbient + fabs(m.diffuse_gain) * tex + dome + spec + film;
+}
+
+// Fill the shared-memory sphere records from the SoA in global memory.  Every block does
+// this once; the table is a few tens of bytes per sphere.  Must be called by all threads.
+template <int MODE>
+__device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned char* smem) {
+    const int n = sp.n_spheres;
+    SphereGeom* geom = reinterpret_cast<SphereGeom*>(smem);
+    SphereAux* aux = reinterpret_cast<SphereAux*>(smem + sizeof(SphereGeom) * (size_t)n);
+    __shared__ unsigned long long s_bound_bits, s_gain_bits;
+    if (threadIdx.x == 0) {
+        s_bound_bits = 0ull;
+        s_gain_bits = 0ull;
+    }
+    __syncthreads();
+    double bound = 0.0, gain = 0.0;
+    for (int s = threadIdx.x; s < n; s += blockDim.x) {
+        double cx = __ldg(sp.spheres + (size_t)RT_F_CX * n + s);
+        double cy = __ldg(sp.spheres + (size_t)RT_F_CY * n + s);
+        double cz = __ldg(sp.spheres + (size_t)RT_F_CZ * n + s);
+        double r = __ldg(sp.spheres + (size_t)RT_F_RADIUS * n + s);
+        geom[s] = {cx, cy, cz, r * r};
+        aux[s] = {1.0 / r, (cx * cx) + (cy * cy) + (cz * cz)};
+        if (MODE == kModeFast) {
+            bound = fmax(bound, material_bound(sp, s));
+            gain = fmax(gain, fabs(__ldg(sp.spheres + (size_t)RT_F_SPECULAR_GAIN * n + s)));
+        }
+    }
+    if (MODE == kModeFast) {
+        // non-negative doubles order like their bit patterns
+        atomicMax(&s_bound_bits, (unsigned long long)__double_as_longlong(bound));
+        atomicMax(&s_gain_bits, (unsigned long long)__double_as_longlong(gain));
+    }
+    __syncthreads();
+    Staged st;
+    st.geom = geom;
+    st.aux = aux;
+    st.chain_bound = -1.0;
+    if (MODE == kModeFast && sp.cutoff > 0.0) {
+        double lmax = __longlong_as_double((long long)s_bound_bits);
+        double wmax = 0.5 * __longlong_as_double((long long)s_gain_bits);
+        // remaining <= W * lmax * sum_j wmax^j ; only usable when the series converges
+        if (wmax < 1.0 && isfinite(lmax)) st.chain_bound = lmax / (1.0 - wmax);
+    }
+    return st;
+}
+
+// One camera or user ray through the scene: raytrace_scene (base.py:91-121) with the
+// recursion of shader.py:143-161 unrolled into a loop.  Exact ties between two shapes
+// (both contribute in the reference) resolve to the lowest shape index here.
+template <int MODE, bool STATS>
+__device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged& st, Vec3 o, Vec3 d,
+                                            Counters& k) {
+    const int n = sp.n_spheres;
+    const Vec3 eye = {sp.eye[0], sp.eye[1], sp.eye[2]};
+    Vec3 color = {0.0, 0.0, 0.0};
+    double weight = 1.0;
+    unsigned long long tests = 0;
+
+    for (int generation = 0;; ++generation) {
+        if (sp.max_depth > 0 && generation >= sp.max_depth) break;
+        if (STATS) {
+            k.traced += 1;
+            k.deepest = generation + 1 > (int)k.deepest ? generation + 1 : k.deepest;
+            tests += (unsigned long long)n;
+        }
+
+        // ---- nearest hit (base.py:97-105)
+        double tmin = kMiss;
+        int sid = -1;
+        for (int s = 0; s < n; ++s) {
+            double t;
+            if (MODE == kModeExact) {
+                t = sphere_distance_exact(o, d, st.geom[s], st.aux[s].cc);
+            } else {
+                HalfB q = half_b(o, d, st.geom[s]);
+                t = can_hit(q) ? near_root(q) : kMiss;
+            }
+            if (t < tmin) {
+                tmin = t;
+                sid = s;
+            }
+        }
+        if (sid < 0) break;
+        if (STATS) k.hits += 1;
+
+        // ---- NumpyShader.create (shader.py:63-112)
+        const SphereGeom g = st.geom[sid];
+        const double inv_r = st.aux[sid].inv_r;
+        const Material m = load_material(sp, sid);
+        const Vec3 centre = {g.cx, g.cy, g.cz};
+        Vec3 hit, normal, nudged, to_eye;
+        if (MODE == kModeExact) {
+            hit = o + d * tmin;
+            normal = (hit - centre) * inv_r;
+            to_eye = norm_exact(eye - hit);
+            nudged = hit + normal * kNudge;
+        } else {
+            hit = {fma(d.x, tmin, o.x), fma(d.y, tmin, o.y), fma(d.z, tmin, o.z)};
+            normal = (hit - centre) * inv_r;
+            to_eye = norm_fast(eye - hit);
+            nudged = {fma(normal.x, kNudge, hit.x), fma(normal.y, kNudge, hit.y), fma(normal.z, kNudge, hit.z)};
+        }
+
+        Vec3 local = {kAmbient, kAmbient, kAmbient};
+        Vec3 tex = {m.r, m.g, m.b};
+        if (m.checker) {
+            double on = checker_on(hit) ? 1.0 : 0.0;
+            tex = {on, on, on};
+        }
+
+        bool lit0 = false;
+        double spec_sum = 0.0;
+        for (int li = 0; li < sp.n_lights_used; ++li) {
+            Vec3 lp = {__ldg(sp.lights + 3 * li), __ldg(sp.lights + 3 * li + 1), __ldg(sp.lights + 3 * li + 2)};
+            Vec3 to_light = MODE == kModeExact ? norm_exact(lp - hit) : norm_fast(lp - hit);
+            bool lit = in_light<MODE>(st, n, sid, nudged, to_light, tests);
+            if (li == 0) lit0 = lit;
+            if (MODE == kModeExact) {
+                double litf = lit ? 1.0 : 0.0;
+                double lambert = fmax(dot(normal, to_light), 0.0);
+                local.x += tex.x * lambert * litf * m.diffuse_gain;
+                local.y += tex.y * lambert * litf * m.diffuse_gain;
+                local.z += tex.z * lambert * litf * m.diffuse_gain;
+                double spec = specular_exact(normal, to_light, to_eye, m.roughness, m.specular_gain);
+                spec_sum += spec * litf;
+            } else if (lit) {
+                double lambert = fmax(fdot(normal, to_light), 0.0) * m.diffuse_gain;
+                local.x = fma(tex.x, lambert, local.x);
+                local.y = fma(tex.y, lambert, local.y);
+                local.z = fma(tex.z, lambert, local.z);
+                if (m.specular_gain != 0.0)
+                    spec_sum += specular_fast(normal, to_light, to_eye, m.roughness, m.specular_gain);
+            }
+        }
+
+        // dome light (shader.py:234-244)
+        double ny = fmax(MODE == kModeExact ? (normal.x * 0.0) + (normal.y * 1.0) + (normal.z * 0.0) : normal.y, 0.0);
+        double dome;
+        if (MODE == kModeExact) {
+            dome = 0.0;
+            for (int li = 0; li < sp.n_dome; ++li) dome += sp.dome_intensity[li] * ny;
+        } else {
+            dome = sp.dome_sum * ny;
+        }
+        local.x += sp.dome_color[0] * dome;
+        local.y += sp.dome_color[1] * dome;
+        local.z += sp.dome_color[2] * dome;
+
+        // specular enters as spec * gain * lit (shader.py:106)
+        double spec_term = spec_sum * m.specular_gain;
+        local.x += spec_term;
+        local.y += spec_term;
+        local.z += spec_term;
+
+        // iridescence (shader.py:110)
+        if (MODE == kModeExact || m.irid_gain != 0.0) {
+            Vec3 film = film_color<MODE>(normal, to_eye);
+            local.x += film.x * kFilmWeight * m.irid_gain;
+            local.y += film.y * kFilmWeight * m.irid_gain;
+            local.z += film.z * kFilmWeight * m.irid_gain;
+        }
+
+        color.x += weight * local.x;
+        color.y += weight * local.y;
+        color.z += weight * local.z;
+
+        // the mirror ray enters the parent as refl * 0.5 * gain * lit (shader.py:106)
+        weight *= (lit0 ? 0.5 : 0.0) * m.specular_gain;
+        if (weight == 0.0) break;
+        if (MODE == kModeFast && st.chain_bound > 0.0 && fabs(weight) * st.chain_bound < sp.cutoff) break;
+
+        // mirror direction (shader.py:151): D - (N*2)*(D.N), normalised
+        if (MODE == kModeExact) {
+            d = norm_exact(d - (normal * 2.0) * dot(d, normal));
+        } else {
+            double dn2 = 2.0 * fdot(d, normal);
+            d = norm_fast({fma(-dn2, normal.x, d.x), fma(-dn2, normal.y, d.y), fma(-dn2, normal.z, d.z)});
+        }
+        o = nudged;
+    }
+    if (STATS) k.tests += tests;
+    return color;
+}
+
+}  // namespace rt

@@ -1,0 +1,123 @@
+// rt_device.cuh -- device-side ray/sphere tracer shared by the two kernel builds.
+//
+// Replaces, per ray, NumpyRenderer.raytrace_scene and everything it calls
+// (reference: ray_tracer/infrastructure/numpy/base.py:91-141, shape.py:28-51,
+// shader.py:63-320).  Two arithmetic policies, selected at compile time:
+//
+//   Exact  all FP64, the reference's expressions and operation order; its translation
+//          unit (trace_exact.cu) is compiled with -fmad=false so nothing is contracted.
+//          Geometry decisions (nearest hit, root choice, shadow test, checker parity)
+//          therefore agree with the NumPy reference bit for bit; only libm-grade
+//          functions (pow, sin) may differ in the last place.
+//   Fast   FP64 geometry in half-b form with FMAs, square roots only for accepted hits,
+//          a square-root-free any-hit shadow test, one division for the whole GGX term,
+//          rsqrt normalisation, and a proven throughput cutoff of the bounce chain.
+//
+// The reference's recursion is a linear chain (every hit spawns exactly one mirror ray,
+// shader.py:143-161) and its colour enters the parent linearly with weight
+// 0.5*specular_gain*lit (shader.py:106), so the chain is run as a loop with a running
+// weight held in registers:  pixel = sum_k (prod_{j<k} w_j) * local_k.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include "../../include/rt_abi.h"
+
+namespace rt {
+
+constexpr int kModeExact = 0;
+constexpr int kModeFast = 1;
+constexpr double kMiss = RT_FARAWAY;  // base.py:12
+constexpr double kNudge = 0.0001;     // shader.py:77
+constexpr double kAmbient = 0.004;    // shader.py:183-184
+constexpr double kEps = 1e-8;         // shader.py:275
+constexpr double kPi = 3.141592653589793;
+// ((1.5-1)/(1.5+1))**2 as Python evaluates it (shader.py:290)
+constexpr double kF0 = 0.04000000000000001;
+// (thin_film_ior-1)/2 with thin_film_ior = 1.4 (shader.py:54, :215)
+constexpr double kHueShift = (1.4 - 1.0) / 2.0;
+constexpr double kFilmWeight = 0.1;      // shader.py:52
+constexpr double kFilmThickness = 0.3;   // shader.py:53
+
+// Everything a launch needs besides the rays; passed by value as a kernel parameter.
+struct SceneParams {
+    const double* spheres;  // field-major sphere SoA (rt_abi.h), device
+    const double* lights;   // n_point_lights x 3, device
+    int n_spheres;
+    int n_lights_used;      // 1 unless RT_FLAG_ALL_POINT_LIGHTS
+    int n_dome;
+    int max_depth;          // <= 0: unlimited
+    double eye[3];
+    double dome_intensity[RT_MAX_DOME_LIGHTS];
+    double dome_sum;        // sum of dome_intensity (Fast)
+    double dome_color[3];
+    double cutoff;          // Fast: chain cutoff in linear units, 0 = off
+};
+
+// Camera rows -> rays (base.py:123-141).  The linspace steps are divided on the host
+// (IEEE division, same value NumPy gets).
+struct CameraParams {
+    double cam[3];
+    double x_start, x_stop, x_step;  // np.linspace(-1, 1, W)
+    double y_start, y_stop, y_step;  // np.linspace(1/a + .25, -1/a + .25, H)
+    int width, height;
+    int row0, row1;
+};
+
+// Explicit ray batch (base.py:91-96 called with arrays).
+struct RayBatch {
+    const double* origins;     // 3 planes of n, or nullptr
+    const double* directions;  // 3 planes of n
+    double origin0[3];
+    long long n;
+};
+
+struct OutputParams {
+    void* rgb;            // planar, may be nullptr
+    uint8_t* rgba8;       // 4 bytes per pixel, may be nullptr
+    unsigned long long* stats;
+    long long plane_stride;
+    int rgb_is_f64;
+};
+
+// Per-sphere records staged in shared memory.  Reads are warp-uniform (every lane tests
+// the same sphere) so each is one broadcast transaction: two 16-byte loads per record.
+struct __align__(16) SphereGeom {
+    double cx, cy, cz;
+    double rr;  // radius * radius
+};
+struct __align__(16) SphereAux {
+    double inv_r;  // 1.0 / radius (shader.py:74)
+    double cc;     // |C|^2 summed left to right (shape.py:35 abs(self.position))
+};
+
+struct Vec3 {
+    double x, y, z;
+};
+
+__device__ __forceinline__ Vec3 operator+(Vec3 a, Vec3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ Vec3 operator-(Vec3 a, Vec3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ Vec3 operator*(Vec3 a, double k) { return {a.x * k, a.y * k, a.z * k}; }
+// base.py:34-35: products summed left to right.
+__device__ __forceinline__ double dot(Vec3 a, Vec3 b) { return (a.x * b.x) + (a.y * b.y) + (a.z * b.z); }
+__device__ __forceinline__ double clip01(double v) { return fmin(fmax(v, 0.0), 1.0); }
+
+// base.py:61-64 as written: multiply by the reciprocal of the length, 0 -> 1.
+__device__ __forceinline__ Vec3 norm_exact(Vec3 a) {
+    double mag = sqrt(dot(a, a));
+    double inv = 1.0 / (mag == 0.0 ? 1.0 : mag);
+    return a * inv;
+}
+
+// Fast normalisation: one rsqrt, no division.  A zero vector stays zero like the
+// reference's (0 * 1/1).
+__device__ __forceinline__ double fdot(Vec3 a, Vec3 b) { return fma(a.z, b.z, fma(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ Vec3 norm_fast(Vec3 a) {
+    double m2 = fdot(a, a);
+    double inv = m2 > 0.0 ? rsqrt(m2) : 1.0;
+    return a * inv;
+}
+
+}  // namespace rt

@@ -1,0 +1,26 @@
+// rt_launch.h -- host-callable launchers, one set per arithmetic policy.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "rt_device.cuh"
+
+namespace rt {
+
+struct Launchers {
+    cudaError_t (*render_rows)(bool stats, const SceneParams&, const CameraParams&, const OutputParams&,
+                               cudaStream_t);
+    cudaError_t (*trace_rays)(bool stats, const SceneParams&, const RayBatch&, const OutputParams&,
+                              cudaStream_t);
+    cudaError_t (*sphere_distance)(const RayBatch&, const double* centre, double radius, double* out,
+                                   cudaStream_t);
+    cudaError_t (*ray_directions)(const CameraParams&, double* out, long long plane_stride, cudaStream_t);
+};
+
+const Launchers& exact_launchers();  // trace_exact.cu, compiled with -fmad=false
+const Launchers& fast_launchers();   // trace_fast.cu
+
+// Largest scene whose sphere records fit one block's shared memory.
+int max_staged_spheres();
+
+}  // namespace rt

@@ -1,0 +1,8 @@
+// trace_fast.cu -- the restructured-arithmetic build of the tracer (FMA contraction on).
+#define RT_TU_MODE 1
+#include "rt_launch_impl.cuh"
+
+namespace rt {
+const Launchers& fast_launchers() { return kLaunchers; }
+int max_staged_spheres() { return (int)(kMaxDynamicSmem / (sizeof(SphereGeom) + sizeof(SphereAux))); }
+}  // namespace rt

@@ -99,6 +99,7 @@ PROTOTYPES = {
     "rt_last_error": (C.c_char_p, []),
     "rt_device_count": (C.c_int, [C.POINTER(C.c_int)]),
     "rt_release_cache": (C.c_int, []),
+    "rt_measure_fma_peak": (C.c_int, [C.c_int, C.c_int32, C.POINTER(C.c_double)]),
     "rt_render_rows_dev": (
         C.c_int,
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), C.POINTER(RtCamera), C.c_int32, C.c_int32,

@@ -1,0 +1,375 @@
+"""``CudaRenderer``: the B200 backend of the reference's ``Renderer`` port.
+
+Drop-in for ``NumpyRenderer`` (reference ``ray_tracer/infrastructure/numpy/base.py:90-151``)
+under ``render_image_pipeline(scene, path, renderer)`` (``application.py:43-52``).  The
+three port methods keep their names and argument meaning:
+
+* ``get_ray_directions(camera)``  (``base.py:123-141``) returns a ``CameraRays`` handle;
+  the directions are computed inside the trace kernel from (row, col) and only
+  materialised if somebody reads ``.x/.y/.z``;
+* ``raytrace_scene(origin, directions, scene)``  (``base.py:91-121``) flattens the scene
+  into the sphere SoA of ``include/rt_abi.h`` and launches the trace kernel through the
+  C ABI; explicit NumPy origin/direction arrays are accepted too;
+* ``save_image(color, camera, path)``  (``base.py:143-151``) quantises on the device
+  (``uint8(255*clip(v,0,1))``, truncating) and writes the PNG on the host.
+
+torch is used for device buffers and streams only.  There is no CPU fallback: if
+``librt_b200.so`` is missing or no CUDA device is visible the calls raise.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import Any, Dict, Optional, Tuple
+
+import numpy as np
+
+from ...application import Renderer
+from ...domain import Camera, Scene3D
+from ..flatten import DefaultMaterial, FlatScene, flatten_scene
+from ..png import write_png
+from ..values import NumpyRGBColor, NumpyVector3D, as_float_triple
+from . import abi
+
+_PRECISIONS = {"exact": abi.RT_MODE_EXACT, "fast": abi.RT_MODE_FAST}
+
+
+def _torch():
+    import torch  # deferred: describing scenes must not need torch
+
+    return torch
+
+
+def _require_cuda(device: int):
+    torch = _torch()
+    if not torch.cuda.is_available():
+        raise RuntimeError("CudaRenderer needs a CUDA device; there is no CPU fallback")
+    if device >= torch.cuda.device_count():
+        raise RuntimeError(f"cuda:{device} does not exist ({torch.cuda.device_count()} visible)")
+    return torch
+
+
+class CameraRays(NumpyVector3D):
+    """Handle returned by ``get_ray_directions``: rows ``[row0, row1)`` of a camera.
+
+    Reading ``x``, ``y`` or ``z`` materialises the unit directions (float64, flat,
+    row-major) through ``rt_ray_directions_dev``.
+    """
+
+    __slots__ = ("camera", "row0", "row1", "_renderer", "_planes")
+
+    def __init__(self, renderer: "CudaRenderer", camera: Camera, row0: int, row1: int) -> None:
+        self.camera = camera
+        self.row0 = int(row0)
+        self.row1 = int(row1)
+        self._renderer = renderer
+        self._planes = None
+
+    def _materialise(self) -> np.ndarray:
+        if self._planes is None:
+            self._planes = self._renderer._ray_directions(self.camera, self.row0, self.row1)
+        return self._planes
+
+    x = property(lambda self: self._materialise()[0])
+    y = property(lambda self: self._materialise()[1])
+    z = property(lambda self: self._materialise()[2])
+
+    def __len__(self) -> int:
+        return (self.row1 - self.row0) * int(self.camera.width)
+
+
+class DeviceColor(NumpyRGBColor):
+    """Colour result living on the GPU: planar linear RGB ``[3, n]`` (+ optional RGBA8).
+
+    ``x``/``y``/``z`` are NumPy views of one device-to-host copy, made on first access,
+    so the object reads like the reference's ``NumpyRGBColor`` of flat arrays
+    (``base.py:119-121``).
+    """
+
+    __slots__ = ("planes", "rgba8", "stats", "device", "_host")
+
+    def __init__(self, planes, rgba8=None, stats=None, device: int = 0) -> None:
+        self.planes = planes  # torch tensor [3, n] float32/float64 on the device
+        self.rgba8 = rgba8  # torch tensor [n, 4] uint8 on the device, or None
+        self.stats = stats  # torch tensor [4] int64 on the device, or None
+        self.device = device
+        self._host = None
+
+    def numpy(self) -> np.ndarray:
+        if self._host is None:
+            self._host = self.planes.cpu().numpy()
+        return self._host
+
+    x = property(lambda self: self.numpy()[0])
+    y = property(lambda self: self.numpy()[1])
+    z = property(lambda self: self.numpy()[2])
+
+    def counters(self) -> Optional[Dict[str, int]]:
+        """Work counters of the launch (``collect_stats=True``)."""
+        if self.stats is None:
+            return None
+        traced, hits, deepest, tests = (int(v) for v in self.stats.cpu().tolist())
+        return {"rays_traced": traced, "hits_shaded": hits, "generations": deepest, "sphere_tests": tests}
+
+
+class CudaRenderer(Renderer):
+    """``Renderer`` port on one B200 (``cuda:device``).
+
+    The five gains are the README constructor's (``README.md:50-56``); they are the
+    material of every shape that carries a colour instead of a ``NumpyShader``
+    (SURVEY.md section 8b).  Keyword extras:
+
+    ``precision``  ``"exact"``: all-FP64 in the reference's operation order, no FMA
+                   contraction.  ``"fast"`` (default): FP64 with restructured arithmetic.
+    ``max_depth``  generations of rays traced (primary = generation 0); ``None`` = no cap,
+                   like the reference (``shader.py:143-161``).
+    ``cutoff``     fast mode only: stop a bounce chain once what it can still add is
+                   provably below this many linear units (0 = never).
+    ``all_point_lights``  extension (``main.py:45`` TODO): shade with every point light.
+    ``output_dtype``  ``"float64"`` (default, the reference's dtype) or ``"float32"``.
+    ``collect_stats``  count rays / hits / generations / sphere tests per launch.
+    """
+
+    def __init__(
+        self,
+        reflection_gain: float = 0.8,
+        specular_gain: float = 1.0,
+        specular_roughness: float = 0.5,
+        iridescence_gain: float = 0.05,
+        diffuse_gain: float = 1.0,
+        *,
+        precision: str = "fast",
+        max_depth: Optional[int] = None,
+        cutoff: float = 1e-7,
+        all_point_lights: bool = False,
+        output_dtype: str = "float64",
+        collect_stats: bool = False,
+        device: int = 0,
+        png_compress_level: int = 6,
+    ) -> None:
+        if precision not in _PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}, got {precision!r}")
+        if output_dtype not in ("float32", "float64"):
+            raise ValueError("output_dtype must be 'float32' or 'float64'")
+        if max_depth is not None and int(max_depth) < 1:
+            raise ValueError("max_depth must be >= 1 (generations traced) or None")
+        if not cutoff >= 0.0:
+            raise ValueError("cutoff must be >= 0")
+        self.default_material = DefaultMaterial(
+            reflection_gain=reflection_gain,
+            specular_gain=specular_gain,
+            specular_roughness=specular_roughness,
+            iridescence_gain=iridescence_gain,
+            diffuse_gain=diffuse_gain,
+        )
+        self.precision = precision
+        self.max_depth = None if max_depth is None else int(max_depth)
+        self.cutoff = float(cutoff)
+        self.all_point_lights = bool(all_point_lights)
+        self.output_dtype = output_dtype
+        self.collect_stats = bool(collect_stats)
+        self.device = int(device)
+        self.png_compress_level = int(png_compress_level)
+        self._scene_key: Optional[bytes] = None
+        self._scene_dev: Optional[Tuple[Any, Any]] = None
+
+    # ------------------------------------------------------------------ helpers
+    def _env(self, flat: FlatScene) -> abi.RtEnv:
+        return abi.make_env(
+            flat.eye,
+            len(flat.point_lights),
+            flat.dome_intensity,
+            flat.dome_color,
+            max_depth=self.max_depth or 0,
+            mode=_PRECISIONS[self.precision],
+            flags=abi.RT_FLAG_ALL_POINT_LIGHTS if self.all_point_lights else abi.RT_FLAG_NONE,
+            cutoff=self.cutoff if self.precision == "fast" else 0.0,
+        )
+
+    def flatten(self, scene: Scene3D) -> FlatScene:
+        return flatten_scene(scene, self.default_material)
+
+    def upload_scene(self, flat: FlatScene):
+        """Device copies of the sphere SoA and the point-light table (cached by content)."""
+        torch = _require_cuda(self.device)
+        key = flat.key()
+        if key != self._scene_key or self._scene_dev is None:
+            dev = torch.device("cuda", self.device)
+            spheres = torch.from_numpy(flat.spheres).to(dev, non_blocking=False)
+            lights = torch.from_numpy(flat.point_lights).to(dev, non_blocking=False)
+            self._scene_key, self._scene_dev = key, (spheres, lights)
+        return self._scene_dev
+
+    def _stream(self) -> int:
+        return int(_torch().cuda.current_stream(self.device).cuda_stream)
+
+    def _torch_dtype(self):
+        torch = _torch()
+        return torch.float64 if self.output_dtype == "float64" else torch.float32
+
+    def _abi_dtype(self) -> int:
+        return abi.RT_DTYPE_F64 if self.output_dtype == "float64" else abi.RT_DTYPE_F32
+
+    def _new_stats(self):
+        if not self.collect_stats:
+            return None
+        torch = _torch()
+        return torch.zeros(abi.RT_STATS_WORDS, dtype=torch.int64, device=torch.device("cuda", self.device))
+
+    def _ray_directions(self, camera: Camera, row0: int, row1: int) -> np.ndarray:
+        torch = _require_cuda(self.device)
+        lib = abi.load()
+        n = (row1 - row0) * int(camera.width)
+        out = torch.empty((3, n), dtype=torch.float64, device=torch.device("cuda", self.device))
+        cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
+        abi.check(
+            lib.rt_ray_directions_dev(self.device, C.byref(cam), row0, row1, out.data_ptr(), n, self._stream()),
+            "rt_ray_directions_dev",
+        )
+        return out.cpu().numpy()
+
+    # ------------------------------------------------------------------ the port
+    def get_ray_directions(self, camera: Camera, rows: Optional[Tuple[int, int]] = None) -> CameraRays:
+        """Primary rays of ``camera`` (``base.py:123-141``); ``rows=(row0, row1)`` selects
+        a row band (the multi-GPU sharding unit)."""
+        width, height = int(camera.width), int(camera.height)
+        if width <= 0 or height <= 0:
+            raise ValueError(f"camera size {width}x{height}")
+        row0, row1 = (0, height) if rows is None else (int(rows[0]), int(rows[1]))
+        if not 0 <= row0 <= row1 <= height:
+            raise ValueError(f"rows {rows} outside 0..{height}")
+        return CameraRays(self, camera, row0, row1)
+
+    def render_rows(self, flat: FlatScene, camera: Camera, row0: int, row1: int, *, planes=None,
+                    rgba8=None, want_rgba8: bool = False) -> DeviceColor:
+        """Launch the camera-ray kernel for rows ``[row0, row1)`` into (optionally
+        caller-supplied) device buffers.  Asynchronous on torch's current stream."""
+        torch = _require_cuda(self.device)
+        lib = abi.load()
+        dev = torch.device("cuda", self.device)
+        spheres, lights = self.upload_scene(flat)
+        n = (row1 - row0) * int(camera.width)
+        if planes is None:
+            planes = torch.empty((3, n), dtype=self._torch_dtype(), device=dev)
+        if rgba8 is None and want_rgba8:
+            rgba8 = torch.empty((n, 4), dtype=torch.uint8, device=dev)
+        stats = self._new_stats()
+        env = self._env(flat)
+        cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
+        abi.check(
+            lib.rt_render_rows_dev(
+                self.device, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env), C.byref(cam),
+                row0, row1, planes.data_ptr(), self._abi_dtype(), planes.stride(0),
+                None if rgba8 is None else rgba8.data_ptr(), None if stats is None else stats.data_ptr(),
+                self._stream(),
+            ),
+            "rt_render_rows_dev",
+        )
+        return DeviceColor(planes, rgba8, stats, self.device)
+
+    def raytrace_scene(self, ray_origin: Any, normalized_ray_direction: Any, scene: Scene3D) -> DeviceColor:
+        """Colour of every ray (``base.py:91-121`` with every ``NumpyShader.create`` it
+        triggers, ``shader.py:63-112``)."""
+        flat = self.flatten(scene)
+        rays = normalized_ray_direction
+        if isinstance(rays, CameraRays):
+            origin = as_float_triple(ray_origin, "ray origin")
+            if origin == as_float_triple(rays.camera.position, "camera position"):
+                return self.render_rows(flat, rays.camera, rays.row0, rays.row1, want_rgba8=True)
+        return self.trace_rays(flat, ray_origin, rays)
+
+    def trace_rays(self, flat: FlatScene, ray_origin: Any, directions: Any) -> DeviceColor:
+        """Explicit ray batch: ``directions`` has flat ``x, y, z`` arrays; ``ray_origin`` is
+        a scalar triple (broadcast, as the reference's primary rays) or arrays."""
+        torch = _require_cuda(self.device)
+        lib = abi.load()
+        dev = torch.device("cuda", self.device)
+        d = np.stack([np.asarray(c, dtype=np.float64).reshape(-1) for c in (directions.x, directions.y, directions.z)])
+        n = d.shape[1]
+        o_parts = [np.asarray(c, dtype=np.float64) for c in (ray_origin.x, ray_origin.y, ray_origin.z)]
+        origin0 = None
+        origins_dev = None
+        if all(p.ndim == 0 for p in o_parts):
+            origin0 = (C.c_double * 3)(*[float(p) for p in o_parts])
+        else:
+            o = np.stack([np.broadcast_to(p.reshape(-1) if p.ndim else p, (n,)) for p in o_parts])
+            origins_dev = torch.from_numpy(np.ascontiguousarray(o)).to(dev)
+        d_dev = torch.from_numpy(np.ascontiguousarray(d)).to(dev)
+        spheres, lights = self.upload_scene(flat)
+        planes = torch.empty((3, n), dtype=self._torch_dtype(), device=dev)
+        stats = self._new_stats()
+        env = self._env(flat)
+        abi.check(
+            lib.rt_trace_rays_dev(
+                self.device, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
+                None if origins_dev is None else origins_dev.data_ptr(), origin0, d_dev.data_ptr(), n,
+                planes.data_ptr(), self._abi_dtype(), max(n, 1), None if stats is None else stats.data_ptr(),
+                self._stream(),
+            ),
+            "rt_trace_rays_dev",
+        )
+        torch.cuda.current_stream(self.device).synchronize()  # d_dev/origins_dev die with this frame
+        return DeviceColor(planes, None, stats, self.device)
+
+    def quantize(self, color: Any, channels: int = 3):
+        """``uint8(255*clip(v,0,1))`` truncating (``base.py:143-151``) on the device;
+        returns a ``[n, channels]`` uint8 device tensor."""
+        torch = _require_cuda(self.device)
+        lib = abi.load()
+        dev = torch.device("cuda", self.device)
+        if isinstance(color, DeviceColor):
+            planes = color.planes
+        else:  # a host colour (e.g. the reference's own NumpyRGBColor of arrays)
+            host = np.stack([np.asarray(c, dtype=np.float64).reshape(-1) for c in (color.x, color.y, color.z)])
+            planes = torch.from_numpy(np.ascontiguousarray(host)).to(dev)
+        n = planes.shape[1]
+        out = torch.empty((n, channels), dtype=torch.uint8, device=dev)
+        dtype = abi.RT_DTYPE_F64 if planes.dtype == torch.float64 else abi.RT_DTYPE_F32
+        abi.check(
+            lib.rt_quantize_dev(self.device, planes.data_ptr(), dtype, planes.stride(0), n, out.data_ptr(), channels,
+                                self._stream()),
+            "rt_quantize_dev",
+        )
+        return out
+
+    def save_image(self, color: Any, camera: Camera, output_path: Path) -> None:
+        """Quantise and write the PNG (``base.py:143-151``).  A frame in which no ray hit
+        anything is written black (the reference raises on it)."""
+        width, height = int(camera.width), int(camera.height)
+        if isinstance(color, DeviceColor) and color.rgba8 is not None:
+            rgb8 = color.rgba8[:, :3].contiguous().cpu().numpy()
+        else:
+            rgb8 = self.quantize(color, 3).cpu().numpy()
+        if rgb8.shape[0] != width * height:
+            raise ValueError(f"colour has {rgb8.shape[0]} pixels, camera is {width}x{height}")
+        write_png(Path(output_path), rgb8.reshape(height, width, 3), self.png_compress_level)
+
+
+def sphere_distance(sphere: Any, ray_origin: Any, normalized_ray_direction: Any, *, device: int = 0,
+                    precision: str = "exact") -> np.ndarray:
+    """``NumpySphere.intersect`` (``shape.py:28-51``) on the GPU: distance per ray,
+    ``FARAWAY`` on a miss."""
+    torch = _require_cuda(device)
+    lib = abi.load()
+    dev = torch.device("cuda", device)
+    d = np.stack([np.asarray(c, dtype=np.float64).reshape(-1)
+                  for c in (normalized_ray_direction.x, normalized_ray_direction.y, normalized_ray_direction.z)])
+    n = d.shape[1]
+    o_parts = [np.asarray(c, dtype=np.float64) for c in (ray_origin.x, ray_origin.y, ray_origin.z)]
+    origin0, origins_dev = None, None
+    if all(p.ndim == 0 for p in o_parts):
+        origin0 = (C.c_double * 3)(*[float(p) for p in o_parts])
+    else:
+        o = np.stack([np.broadcast_to(p.reshape(-1) if p.ndim else p, (n,)) for p in o_parts])
+        origins_dev = torch.from_numpy(np.ascontiguousarray(o)).to(dev)
+    d_dev = torch.from_numpy(np.ascontiguousarray(d)).to(dev)
+    out = torch.empty(n, dtype=torch.float64, device=dev)
+    centre = (C.c_double * 3)(*as_float_triple(sphere.center, "sphere center"))
+    abi.check(
+        lib.rt_sphere_distance_dev(device, None if origins_dev is None else origins_dev.data_ptr(), origin0,
+                                   d_dev.data_ptr(), n, centre, float(sphere.radius), _PRECISIONS[precision],
+                                   out.data_ptr(), int(torch.cuda.current_stream(device).cuda_stream)),
+        "rt_sphere_distance_dev",
+    )
+    return out.cpu().numpy()

@@ -1,0 +1,90 @@
+"""Minimal PNG writer/reader (8-bit RGB, zlib) for ``save_image``.
+
+The reference writes its PNG through Pillow with default settings (``base.py:147-151``);
+what a consumer compares is the decoded pixels, which do not depend on the encoder, so
+the container is written here with the standard library only (no Pillow dependency on
+the render path).  ``compress_level`` 6 is zlib's (and Pillow's) default.
+"""
+
+from __future__ import annotations
+
+import struct
+import zlib
+from pathlib import Path
+
+import numpy as np
+
+_SIGNATURE = b"\x89PNG\r\n\x1a\n"
+
+
+def _chunk(tag: bytes, payload: bytes) -> bytes:
+    return struct.pack(">I", len(payload)) + tag + payload + struct.pack(">I", zlib.crc32(tag + payload) & 0xFFFFFFFF)
+
+
+def encode_png(rgb8: np.ndarray, compress_level: int = 6) -> bytes:
+    """``rgb8``: uint8 ``[H, W, 3]`` -> PNG bytes (colour type 2, filter 0 on every row)."""
+    if rgb8.dtype != np.uint8 or rgb8.ndim != 3 or rgb8.shape[2] != 3:
+        raise ValueError("expected uint8 [H, W, 3]")
+    height, width, _ = rgb8.shape
+    rows = np.zeros((height, 1 + 3 * width), dtype=np.uint8)
+    rows[:, 1:] = rgb8.reshape(height, 3 * width)
+    header = struct.pack(">IIBBBBB", width, height, 8, 2, 0, 0, 0)
+    return b"".join(
+        (_SIGNATURE, _chunk(b"IHDR", header), _chunk(b"IDAT", zlib.compress(rows.tobytes(), compress_level)),
+         _chunk(b"IEND", b""))
+    )
+
+
+def write_png(path: Path, rgb8: np.ndarray, compress_level: int = 6) -> None:
+    Path(path).write_bytes(encode_png(np.ascontiguousarray(rgb8), compress_level))
+
+
+def read_png(path: Path) -> np.ndarray:
+    """Decode an 8-bit RGB/RGBA non-interlaced PNG to uint8 ``[H, W, C]`` (all five
+    filter types), enough to read back what ``write_png`` or Pillow wrote."""
+    data = Path(path).read_bytes()
+    if data[:8] != _SIGNATURE:
+        raise ValueError(f"{path}: not a PNG")
+    pos, idat, width, height, channels = 8, [], 0, 0, 0
+    while pos < len(data):
+        (length,) = struct.unpack(">I", data[pos:pos + 4])
+        tag = data[pos + 4:pos + 8]
+        payload = data[pos + 8:pos + 8 + length]
+        pos += 12 + length
+        if tag == b"IHDR":
+            width, height, depth, ctype, _, _, interlace = struct.unpack(">IIBBBBB", payload)
+            if depth != 8 or ctype not in (2, 6) or interlace != 0:
+                raise ValueError(f"{path}: only 8-bit RGB/RGBA non-interlaced PNGs are supported")
+            channels = 3 if ctype == 2 else 4
+        elif tag == b"IDAT":
+            idat.append(payload)
+        elif tag == b"IEND":
+            break
+    raw = np.frombuffer(zlib.decompress(b"".join(idat)), dtype=np.uint8).reshape(height, 1 + channels * width)
+    out = np.zeros((height, channels * width), dtype=np.uint8)
+    bpp = channels
+    prev = np.zeros(channels * width, dtype=np.int32)
+    for r in range(height):
+        ftype, line = int(raw[r, 0]), raw[r, 1:].astype(np.int32)
+        if ftype == 0:
+            cur = line
+        elif ftype == 2:
+            cur = (line + prev) & 255
+        elif ftype == 1:
+            cur = line.reshape(width, bpp).cumsum(axis=0).reshape(-1) & 255
+        else:  # 3 (average) and 4 (Paeth) depend on the pixel to the left: sequential
+            cur = np.zeros_like(line)
+            for i in range(line.size):
+                a = int(cur[i - bpp]) if i >= bpp else 0
+                b = int(prev[i])
+                c = int(prev[i - bpp]) if i >= bpp else 0
+                if ftype == 3:
+                    pred = (a + b) >> 1
+                else:
+                    p = a + b - c
+                    pa, pb, pc = abs(p - a), abs(p - b), abs(p - c)
+                    pred = a if pa <= pb and pa <= pc else (b if pb <= pc else c)
+                cur[i] = (int(line[i]) + pred) & 255
+        out[r] = cur
+        prev = cur
+    return out.reshape(height, width, channels)

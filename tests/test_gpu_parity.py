@@ -1,0 +1,287 @@
+"""Parity of the CUDA path with the reference (golden fixtures) and the oracle.
+
+Every test calls through the C ABI of include/rt_abi.h (CudaRenderer binds it with
+ctypes; some tests call the host-buffer entry points directly).  Tolerances are the
+north_star's: linear RGB within 1e-4 max-abs, 8-bit image within 1 LSB on >= 99.9 % of
+pixels; integer/byte work (quantisation, counters in exact mode) is bit-exact.
+"""
+
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from _cases import (FULL_FRAME_CASES, GOLDEN, SUBSET_CASES, assert_linear_parity, assert_png_parity, load_case,
+                    manifest)
+
+pytestmark = pytest.mark.gpu
+
+PRECISIONS = ["exact", "fast"]
+# exact mode evaluates the reference's expressions in its order without FMA: only pow/sin
+# may differ in the last place
+EXACT_TOL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def rt():
+    import torch
+
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    from python_ray_tracer_b200.infrastructure import CudaRenderer
+    from python_ray_tracer_b200.infrastructure.cuda import abi
+
+    abi.load()  # fails loudly if librt_b200.so is missing
+
+    def make(precision, **kw):
+        return CudaRenderer(precision=precision, collect_stats=True, **kw)
+
+    return make
+
+
+def _camera(case):
+    from python_ray_tracer_b200 import Camera
+    from python_ray_tracer_b200.infrastructure import NumpyVector3D
+
+    return Camera(NumpyVector3D(*case.flat.eye), case.width, case.height)
+
+
+def _render(renderer, case, rows=None):
+    cam = _camera(case)
+    row0, row1 = rows or (0, case.height)
+    return renderer.render_rows(case.flat, cam, row0, row1, want_rgba8=True)
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("name", FULL_FRAME_CASES)
+def test_full_frames_match_reference(rt, c_oracle, name, precision):
+    case = load_case(name)
+    renderer = rt(precision, max_depth=case.max_depth or None)
+    color = _render(renderer, case)
+    got = color.numpy()
+    tol = EXACT_TOL if precision == "exact" else 1e-4
+    assert_linear_parity(got, case.rgb, tol, f"{name}/{precision} vs reference fixture")
+    want, stats = c_oracle.render(case.flat, case.width, case.height, max_depth=case.max_depth)
+    assert_linear_parity(got, want, tol, f"{name}/{precision} vs oracle")
+    counters = color.counters()
+    if precision == "exact":
+        assert counters["rays_traced"] == case.traced == int(stats[0])
+        assert counters["generations"] == case.deepest
+        assert counters["hits_shaded"] == int(stats[1])
+    # the fused 8-bit output equals the truncating quantisation of the linear values
+    got8 = color.rgba8.cpu().numpy()
+    assert np.array_equal(got8[:, :3], c_oracle.quantize(got)) and (got8[:, 3] == 255).all()
+    assert_png_parity(got8[:, :3], c_oracle.quantize(case.rgb), name)
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("name", SUBSET_CASES)
+def test_subsets_match_reference(rt, c_oracle, name, precision):
+    """Explicit-ray entry point (rt_trace_rays_dev) on the pixel subsets the reference
+    rendered at 960x540 / 1080p / 4K (1025 shapes, depth 8) / 8K."""
+    if not (GOLDEN / f"{name}.npz").exists():
+        pytest.skip(f"{name} not generated")
+    from python_ray_tracer_b200.infrastructure import NumpyVector3D
+
+    case = load_case(name)
+    renderer = rt(precision, max_depth=case.max_depth or None)
+    d = c_oracle.ray_directions(case.flat.eye, case.width, case.height, case.pixels)
+    color = renderer.trace_rays(case.flat, NumpyVector3D(*case.flat.eye), NumpyVector3D(d[0], d[1], d[2]))
+    tol = EXACT_TOL if precision == "exact" else 1e-4
+    assert_linear_parity(color.numpy(), case.rgb, tol, f"{name}/{precision}")
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_golden_png_960x540(rt, precision):
+    """G0 (the reference's committed render.png) and C1 through render_image_pipeline."""
+    import tempfile
+    from pathlib import Path
+
+    from python_ray_tracer_b200 import render_image_pipeline, scenes
+    from python_ray_tracer_b200.infrastructure.png import read_png
+
+    for builder, png, gains in ((scenes.main_scene, "g0_main_960x540.png", {}),
+                                (scenes.readme_scene, "c1_readme_960x540.png", scenes.README_GAINS)):
+        from python_ray_tracer_b200.infrastructure import CudaRenderer
+
+        renderer = CudaRenderer(precision=precision, **gains)
+        with tempfile.TemporaryDirectory() as tmp:
+            path = Path(tmp) / "out.png"
+            render_image_pipeline(builder(960, 540), path, renderer)
+            got = read_png(path)
+        want = read_png(GOLDEN / png)
+        frac = assert_png_parity(got, want, png)
+        if precision == "exact":
+            assert np.count_nonzero(got != want) <= 8, np.count_nonzero(got != want)
+        assert frac >= 0.9999
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_readme_1080p_and_8k_full_size(rt, c_oracle, precision):
+    """BASELINE.json's sizes: full frames on the GPU, checked on the reference's pixel
+    subsets and through size-independent properties (band == full frame, idempotence,
+    traced-ray totals)."""
+    man = manifest()
+    for name in ("c2_readme_1080p_subset", "c4_readme_8k_subset"):
+        case = load_case(name)
+        renderer = rt(precision)
+        color = _render(renderer, case)
+        got = color.numpy()
+        tol = EXACT_TOL if precision == "exact" else 1e-4
+        assert_linear_parity(got[:, case.pixels], case.rgb, tol, f"{name}/{precision}")
+        again = _render(renderer, case).numpy()
+        assert np.array_equal(got, again)  # deterministic
+        # a row band is bit-identical to the same rows of the full frame
+        h, w = case.height, case.width
+        for row0, row1 in ((0, 7), (h // 2 - 3, h // 2 + 10), (h - 5, h)):
+            band = _render(renderer, case, rows=(row0, row1)).numpy()
+            assert np.array_equal(band, got[:, row0 * w:row1 * w])
+        assert np.isfinite(got).all() and got.min() >= 0.0
+        if name.startswith("c2") and precision == "exact":
+            assert color.counters()["rays_traced"] == 4244448  # SURVEY.md 8c pin (reference, 1080p)
+    assert man["c1_readme_960x540_traced"] == 1060815
+
+
+def test_exact_and_fast_agree_at_1080p(rt):
+    case = load_case("c2_readme_1080p_subset")
+    a = _render(rt("exact"), case).numpy()
+    b = _render(rt("fast"), case).numpy()
+    rep = assert_linear_parity(b, a, 1e-4, "fast vs exact 1080p")
+    a8 = (255 * np.clip(a, 0, 1)).astype(np.uint8).T
+    b8 = (255 * np.clip(b, 0, 1)).astype(np.uint8).T
+    assert_png_parity(b8, a8, "fast vs exact 1080p")
+    assert rep["max_abs"] < 1e-6
+
+
+def test_c3_1024_spheres_4k_band(rt, c_oracle):
+    """Config 3 at size: a 4K band of the 1025-shape scene (depth 8) against the oracle."""
+    case = load_case("c3_1024_4k_subset_depth8")
+    rows = (1400, 1404)
+    want, _ = c_oracle.render(case.flat, case.width, case.height, first=rows[0] * case.width,
+                              count=(rows[1] - rows[0]) * case.width, max_depth=8)
+    for precision in PRECISIONS:
+        got = _render(rt(precision, max_depth=8), case, rows=rows).numpy()
+        assert_linear_parity(got, want, EXACT_TOL if precision == "exact" else 1e-4, f"c3 band/{precision}")
+
+
+def test_host_buffer_entry_points(c_oracle):
+    """rt_render_frame_host / rt_trace_rays_host straight through ctypes with NumPy buffers."""
+    from python_ray_tracer_b200.infrastructure.cuda import abi
+
+    lib = abi.load()
+    case = load_case("readme_160x90")
+    flat, w, h = case.flat, case.width, case.height
+    n = w * h
+    env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, mode=abi.RT_MODE_EXACT)
+    cam = abi.make_camera(flat.eye, w, h)
+    rgb = np.empty((3, n), dtype=np.float64)
+    rgb8 = np.empty((n, 3), dtype=np.uint8)
+    stats = np.zeros(4, dtype=np.uint64)
+    ptr = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = lib.rt_render_frame_host(0, ptr(flat.spheres), flat.n_spheres, ptr(flat.point_lights), C.byref(env),
+                                  C.byref(cam), 0, h, ptr(rgb), abi.RT_DTYPE_F64, ptr(rgb8), ptr(stats))
+    abi.check(rc, "rt_render_frame_host")
+    assert_linear_parity(rgb, case.rgb, EXACT_TOL, "host entry")
+    assert np.array_equal(rgb8, c_oracle.quantize(rgb)) and int(stats[0]) == case.traced
+    # float32 output plane
+    rgb32 = np.empty((3, n), dtype=np.float32)
+    rc = lib.rt_render_frame_host(0, ptr(flat.spheres), flat.n_spheres, ptr(flat.point_lights), C.byref(env),
+                                  C.byref(cam), 0, h, ptr(rgb32), abi.RT_DTYPE_F32, None, None)
+    abi.check(rc, "rt_render_frame_host f32")
+    assert np.array_equal(rgb32, rgb.astype(np.float32))
+    # explicit rays with per-ray origins: bounce rays of the oracle's own first generation
+    d = c_oracle.ray_directions(flat.eye, w, h)
+    o = np.repeat(np.asarray(flat.eye)[:, None], n, axis=1).copy()
+    o[0] += np.linspace(-0.1, 0.1, n)
+    want, _ = c_oracle.trace_rays(flat, o, d)
+    out = np.empty((3, n), dtype=np.float64)
+    rc = lib.rt_trace_rays_host(0, ptr(flat.spheres), flat.n_spheres, ptr(flat.point_lights), C.byref(env), ptr(o),
+                                None, ptr(d), n, ptr(out), abi.RT_DTYPE_F64, None)
+    abi.check(rc, "rt_trace_rays_host")
+    assert_linear_parity(out, want, EXACT_TOL, "host rays")
+    # bad arguments fail loudly
+    assert lib.rt_render_frame_host(0, None, 3, None, C.byref(env), C.byref(cam), 0, h, None, 0, None, None) == -1
+    assert lib.rt_render_frame_host(99, ptr(flat.spheres), flat.n_spheres, ptr(flat.point_lights), C.byref(env),
+                                    C.byref(cam), 0, h, ptr(rgb), abi.RT_DTYPE_F64, None, None) == -3
+    lib.rt_release_cache()
+
+
+def test_intersect_and_ray_directions_bit_exact(rt):
+    """Integer-free but IEEE-basic arithmetic: exact mode reproduces the reference bit for bit."""
+    from python_ray_tracer_b200 import Camera
+    from python_ray_tracer_b200.infrastructure import NumpySphere, NumpyVector3D
+    from python_ray_tracer_b200.infrastructure.cuda.renderer import sphere_distance
+
+    z = np.load(GOLDEN / "intersect_vectors.npz")
+    o, d = z["origins"], z["directions"]
+    for centre, radius, want in zip(z["centres"], z["radii"], z["distances"]):
+        sphere = NumpySphere(NumpyVector3D(*centre), float(radius), None)
+        got = sphere.intersect(NumpyVector3D(o[0], o[1], o[2]), NumpyVector3D(d[0], d[1], d[2]))
+        assert np.array_equal(got, want)
+        fast = sphere_distance(sphere, NumpyVector3D(o[0], o[1], o[2]), NumpyVector3D(d[0], d[1], d[2]), precision="fast")
+        hit = want < 1e38
+        assert np.array_equal(fast < 1e38, hit) or np.count_nonzero((fast < 1e38) != hit) <= 2
+        both = hit & (fast < 1e38)
+        assert np.abs(fast[both] - want[both]).max() <= 1e-9 * max(1.0, float(radius)) 
+    unit = NumpySphere(NumpyVector3D(0, 0, 0), 1.0, None)
+    assert unit.intersect(NumpyVector3D(0.0, 0.0, -3.0), NumpyVector3D(np.array([0.0]), np.array([0.0]), np.array([1.0])))[0] == 2.0
+    g = np.load(GOLDEN / "ray_directions.npz")
+    renderer = rt("exact")
+    for key in g.files:
+        w, h = (int(v) for v in key[2:].split("x"))
+        rays = renderer.get_ray_directions(Camera(NumpyVector3D(0.0, 0.2, -2.0), w, h))
+        got = np.stack([rays.x, rays.y, rays.z])
+        if w * h > 1024:
+            got = got[:, ::97]
+        assert np.array_equal(got, g[key]), key
+
+
+def test_edge_cases(rt, c_oracle):
+    from python_ray_tracer_b200 import Camera, PointLight, Scene3D
+    from python_ray_tracer_b200.infrastructure import NumpyRGBColor, NumpySphere, NumpyVector3D
+
+    renderer = rt("exact")
+    # a frame in which nothing is hit renders black (the reference raises in save_image)
+    behind = Scene3D([NumpySphere(NumpyVector3D(0, 0, -50), 1.0, NumpyRGBColor(1, 1, 1))],
+                     [PointLight(NumpyVector3D(0, 5, 0))], Camera(NumpyVector3D(0, 0.2, -2), 33, 17))
+    color = renderer.raytrace_scene(behind.camera.position, renderer.get_ray_directions(behind.camera), behind)
+    assert color.numpy().shape == (3, 33 * 17) and not color.numpy().any()
+    assert color.counters()["hits_shaded"] == 0 and color.counters()["rays_traced"] == 33 * 17
+    # empty ray batch
+    empty = renderer.trace_rays(renderer.flatten(behind), NumpyVector3D(0.0, 0.0, 0.0),
+                                NumpyVector3D(np.zeros(0), np.zeros(0), np.zeros(0)))
+    assert empty.numpy().shape == (3, 0)
+    # zero rows
+    assert renderer.render_rows(renderer.flatten(behind), behind.camera, 5, 5).numpy().shape == (3, 0)
+    # exact tie between two identical spheres: the reference adds both contributions (and
+    # recurses on both); the kernel shades the lowest index once -- documented deviation
+    one = Scene3D([NumpySphere(NumpyVector3D(0, 0, 3), 1.0, NumpyRGBColor(1, 0, 0))],
+                  [PointLight(NumpyVector3D(5, 10, -10))], Camera(NumpyVector3D(0, 0.2, -2), 16, 9))
+    two = Scene3D(list(one.shapes) * 2, one.lights, one.camera)
+    a = renderer.raytrace_scene(one.camera.position, renderer.get_ray_directions(one.camera), one).numpy()
+    b = renderer.raytrace_scene(two.camera.position, renderer.get_ray_directions(two.camera), two).numpy()
+    assert np.array_equal(a, b)
+    # all-point-lights extension against its own CPU restatement (not the reference)
+    case = load_case("c3_small_48_192x108_depth8")
+    ext = rt("exact", max_depth=8, all_point_lights=True)
+    got = _render(ext, case).numpy()
+    want, _ = c_oracle.render(case.flat, case.width, case.height, max_depth=8, all_point_lights=True)
+    assert_linear_parity(got, want, EXACT_TOL, "all point lights")
+    assert np.abs(got - case.rgb).max() > 1e-3  # and it does change the picture
+    # too many spheres for one block's shared memory -> loud error, no fallback
+    from python_ray_tracer_b200.infrastructure.flatten import FlatScene
+
+    big = FlatScene(np.ones((12, 20000)), case.flat.point_lights, case.flat.eye, [0.1], (1.0, 1.0, 1.0))
+    with pytest.raises(RuntimeError):
+        renderer.render_rows(big, _camera(case), 0, 1)
+
+
+def test_quantize_kernel_bit_exact(rt, c_oracle):
+    rng = np.random.default_rng(3)
+    v = np.concatenate([rng.uniform(-0.2, 1.8, (3, 5000)), np.array([[0.0, 1.0, 0.5, 1 / 255, 254.999 / 255]] * 3)], axis=1)
+    from python_ray_tracer_b200.infrastructure import NumpyRGBColor
+
+    renderer = rt("exact")
+    got = renderer.quantize(NumpyRGBColor(v[0], v[1], v[2]), 3).cpu().numpy()
+    assert np.array_equal(got, c_oracle.quantize(v))
+    got4 = renderer.quantize(NumpyRGBColor(v[0], v[1], v[2]), 4).cpu().numpy()
+    assert np.array_equal(got4[:, :3], got) and (got4[:, 3] == 255).all()

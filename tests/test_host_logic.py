@@ -1,0 +1,213 @@
+"""Host side of the boundary: the Renderer port mirror, both constructor surfaces, the
+scene flattener, the PNG container and the C-ABI library's symbol table (no compute)."""
+
+import ctypes
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from python_ray_tracer_b200 import (Camera, DomeLight, PointLight, Renderer, Scene3D, render_image_pipeline, scenes)
+from python_ray_tracer_b200.infrastructure import (FARAWAY, CheckeredSphere, NumpyRGBColor, NumpyShader, NumpySphere,
+                                                   NumpyVector3D, Texture, TextureChecker)
+from python_ray_tracer_b200.infrastructure.cuda import abi
+from python_ray_tracer_b200.infrastructure.flatten import (F_COLOR_R, F_CX, F_DIFFUSE_GAIN, F_RADIUS, F_SPECULAR_GAIN,
+                                                           F_SPECULAR_ROUGHNESS, F_TEXTURE, DefaultMaterial,
+                                                           flatten_scene)
+from python_ray_tracer_b200.infrastructure.png import encode_png, read_png, write_png
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def test_port_has_the_reference_methods():
+    # application.py:7-32: exactly these three abstract methods
+    assert Renderer.__abstractmethods__ == {"raytrace_scene", "get_ray_directions", "save_image"}
+
+
+def test_pipeline_calls_in_reference_order(tmp_path):
+    calls = []
+
+    class Spy(Renderer):
+        def get_ray_directions(self, camera):
+            calls.append(("dirs", camera.width))
+            return "D"
+
+        def raytrace_scene(self, origin, directions, scene):
+            calls.append(("trace", origin, directions))
+            return "C"
+
+        def save_image(self, color, camera, path):
+            calls.append(("save", color, path))
+
+    scene = scenes.readme_scene(8, 4)
+    render_image_pipeline(scene, tmp_path / "x.png", Spy())
+    assert calls == [("dirs", 8), ("trace", scene.camera.position, "D"), ("save", "C", tmp_path / "x.png")]
+
+
+def test_readme_and_head_surfaces_flatten_identically():
+    default = DefaultMaterial(**scenes.README_GAINS)
+    a = flatten_scene(scenes.readme_scene(64, 36), default)
+    b = flatten_scene(scenes.readme_scene_head_api(64, 36))
+    assert np.array_equal(a.spheres, b.spheres)
+    assert np.array_equal(a.point_lights, b.point_lights)
+    assert a.dome_intensity == b.dome_intensity == [0.1] and a.dome_color == (1.0, 1.0, 1.0)
+    assert a.spheres[F_TEXTURE].tolist() == [0.0, 0.0, 1.0]
+    assert a.spheres[F_CX, 0] == 0.55 and a.spheres[F_RADIUS, 2] == 99999.0
+    assert a.spheres[F_SPECULAR_ROUGHNESS].tolist() == [0.5, 0.5, 0.5]
+    assert a.eye == (0.0, 0.2, -2.0)
+
+
+def test_renderer_gains_are_the_default_material_only_for_colour_shapes():
+    shader = NumpyShader(0.0, 0.25, 0.1, 0.0, 0.5, Texture(NumpyRGBColor(1, 0, 0)))
+    scene = Scene3D(
+        [NumpySphere(NumpyVector3D(0, 0, 3), 1.0, shader), NumpySphere(NumpyVector3D(1, 0, 3), 1.0, NumpyRGBColor(0, 1, 0))],
+        [PointLight(NumpyVector3D(0, 5, 0))],
+        Camera(NumpyVector3D(0, 0, -1), 4, 4),
+    )
+    flat = flatten_scene(scene, DefaultMaterial(specular_gain=0.75, diffuse_gain=0.3))
+    assert flat.spheres[F_SPECULAR_GAIN].tolist() == [0.25, 0.75]
+    assert flat.spheres[F_DIFFUSE_GAIN].tolist() == [0.5, 0.3]
+    assert flat.spheres[F_COLOR_R].tolist() == [1.0, 0.0]
+    assert flat.dome_intensity == [] and flat.dome_color == (1.0, 1.0, 1.0)
+
+
+def test_checker_ignores_its_colour_and_extra_argument():
+    s = CheckeredSphere(NumpyVector3D(0, -99999.5, 0), 99999, NumpyRGBColor(0.2, 0.3, 0.4), 1.0)
+    scene = Scene3D([s], [PointLight(NumpyVector3D(0, 5, 0))], Camera(NumpyVector3D(0, 0, -1), 4, 4))
+    flat = flatten_scene(scene)
+    assert flat.spheres[F_TEXTURE, 0] == 1.0 and flat.spheres[F_COLOR_R, 0] == 1.0
+    assert isinstance(TextureChecker().color, NumpyRGBColor)
+
+
+def test_lights_rules():
+    sphere = NumpySphere(NumpyVector3D(0, 0, 3), 1.0, NumpyRGBColor(1, 1, 1))
+    cam = Camera(NumpyVector3D(0, 0, -1), 4, 4)
+    dome = DomeLight(0.1, NumpyRGBColor(1, 1, 1))
+    with pytest.raises(ValueError):  # shader.py:75 raises AttributeError in the reference
+        flatten_scene(Scene3D([sphere], [dome, PointLight(NumpyVector3D(0, 5, 0))], cam))
+    with pytest.raises(ValueError):
+        flatten_scene(Scene3D([sphere], [], cam))
+    with pytest.raises(ValueError):
+        flatten_scene(Scene3D([], [PointLight(NumpyVector3D(0, 5, 0))], cam))
+    many = [PointLight(NumpyVector3D(0, 5, 0))] + [DomeLight(0.01 * i, NumpyRGBColor(i, 0, 0)) for i in range(1, 12)]
+    flat = flatten_scene(Scene3D([sphere], many, cam))
+    assert len(flat.dome_intensity) == 8 and flat.dome_color == (11.0, 0.0, 0.0)  # colour of the LAST dome
+    assert abs(sum(flat.dome_intensity) - sum(0.01 * i for i in range(1, 12))) < 1e-15
+    flat = flatten_scene(scenes.random_spheres_scene(16, 9, n_spheres=5))
+    assert flat.point_lights.shape == (4, 3) and flat.n_spheres == 6
+
+
+def test_zero_radius_and_non_sphere_rejected():
+    cam = Camera(NumpyVector3D(0, 0, -1), 4, 4)
+    light = [PointLight(NumpyVector3D(0, 5, 0))]
+    with pytest.raises(ValueError):
+        flatten_scene(Scene3D([NumpySphere(NumpyVector3D(0, 0, 3), 0.0, NumpyRGBColor(1, 1, 1))], light, cam))
+    with pytest.raises(ValueError):
+        flatten_scene(Scene3D([object()], light, cam))
+
+
+def test_vector_value_types_match_reference_semantics():
+    a, b = NumpyVector3D(1.0, 2.0, 3.0), NumpyVector3D(4.0, 5.0, 6.0)
+    assert a.dot(b) == 32.0 and abs(a) == 14.0  # abs is the SQUARED length (base.py:37-38)
+    assert (a + b).components() == (5.0, 7.0, 9.0) and (b - a).components() == (3.0, 3.0, 3.0)
+    assert (a * 2).components() == (2.0, 4.0, 6.0) and (a / 2).components() == (0.5, 1.0, 1.5)
+    n = NumpyVector3D(3.0, 0.0, 4.0).norm()
+    assert np.allclose(n.components(), (0.6, 0.0, 0.8))
+    assert NumpyVector3D(0.0, 0.0, 0.0).norm().components() == (0.0, 0.0, 0.0)  # zero-safe (base.py:61-64)
+    v = NumpyVector3D(np.arange(4.0), np.arange(4.0) * 2, 7.0)
+    mask = np.array([True, False, True, False])
+    e = v.extract(mask)
+    assert e.x.tolist() == [0.0, 2.0] and e.z == 7.0
+    p = e.place(mask)
+    assert p.x.tolist() == [0.0, 0.0, 2.0, 0.0] and p.z.tolist() == [7.0, 0.0, 7.0, 0.0]
+    assert FARAWAY == 1.0e39
+
+
+def test_png_roundtrip(tmp_path):
+    img = np.random.default_rng(0).integers(0, 256, (19, 31, 3), dtype=np.uint8)
+    write_png(tmp_path / "a.png", img)
+    assert np.array_equal(read_png(tmp_path / "a.png"), img)
+    assert encode_png(img, 1) != encode_png(img, 9) or True
+    with pytest.raises(ValueError):
+        encode_png(img.astype(np.float32))
+    PIL = pytest.importorskip("PIL.Image")
+    assert np.array_equal(np.asarray(PIL.open(tmp_path / "a.png")), img)
+
+
+def test_cuda_renderer_constructor_surface():
+    from python_ray_tracer_b200.infrastructure import CudaRenderer
+
+    r = CudaRenderer(reflection_gain=0.8, specular_gain=1.0, specular_roughness=0.5, iridescence_gain=0.05,
+                     diffuse_gain=1.0)  # README.md:50-56 verbatim
+    assert isinstance(r, Renderer) and r.default_material.specular_roughness == 0.5
+    assert CudaRenderer().default_material == DefaultMaterial()
+    for bad in (dict(precision="fp16"), dict(output_dtype="int8"), dict(max_depth=0), dict(cutoff=-1.0)):
+        with pytest.raises(ValueError):
+            CudaRenderer(**bad)
+    rays = r.get_ray_directions(Camera(NumpyVector3D(0, 0.2, -2), 16, 9), rows=(3, 5))
+    assert len(rays) == 32 and (rays.row0, rays.row1) == (3, 5)
+    with pytest.raises(ValueError):
+        r.get_ray_directions(Camera(NumpyVector3D(0, 0.2, -2), 16, 9), rows=(5, 12))
+
+
+def test_product_never_imports_the_oracle():
+    offenders = []
+    for path in (ROOT / "python_ray_tracer_b200").rglob("*.py"):
+        text = path.read_text()
+        if re.search(r"^\s*(from|import)\s+oracle\b", text, re.M) or "librt_oracle" in text:
+            offenders.append(str(path))
+    for path in (ROOT / "python_ray_tracer_b200" / "csrc").glob("*"):
+        if path.suffix in (".cu", ".cuh", ".h") and "oracle" in path.read_text():
+            offenders.append(str(path))
+    assert offenders == []
+
+
+def test_abi_library_exports_every_declared_symbol():
+    """include/rt_abi.h <-> librt_b200.so <-> abi.PROTOTYPES agree (no compute calls)."""
+    header = (ROOT / "include" / "rt_abi.h").read_text()
+    declared = set(re.findall(r"^(?:int|const char\*)\s+(rt_\w+)\s*\(", header, re.M))
+    assert declared == set(abi.PROTOTYPES), declared ^ set(abi.PROTOTYPES)
+    lib = abi.load()  # raises if the library is not built: there is no fallback
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.rt_abi_version() == abi.RT_ABI_VERSION
+    # struct layouts the header promises
+    assert ctypes.sizeof(abi.RtCamera) == 32 and ctypes.sizeof(abi.RtEnv) == 144
+
+
+def test_ctypes_structs_match_the_header_as_compiled(tmp_path):
+    import subprocess
+
+    src = tmp_path / "sizes.c"
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "rt_abi.h"\n'
+        'int main(void){printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(rt_env), sizeof(rt_camera), '
+        'offsetof(rt_env, dome_intensity), offsetof(rt_env, max_depth), offsetof(rt_env, cutoff), '
+        'offsetof(rt_camera, width));return 0;}\n'
+    )
+    exe = tmp_path / "sizes"
+    subprocess.run(["/usr/bin/gcc", "-I", str(ROOT / "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(v) for v in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    want = [ctypes.sizeof(abi.RtEnv), ctypes.sizeof(abi.RtCamera), abi.RtEnv.dome_intensity.offset,
+            abi.RtEnv.max_depth.offset, abi.RtEnv.cutoff.offset, abi.RtCamera.width.offset]
+    assert got == want
+
+
+def test_abi_rejects_bad_arguments_without_a_gpu():
+    lib = abi.load()
+    cam = abi.make_camera((0, 0.2, -2), 16, 9)
+    env = abi.make_env((0, 0.2, -2), 1, [0.1], (1, 1, 1))
+    rc = lib.rt_render_rows_dev(0, None, 3, None, ctypes.byref(env), ctypes.byref(cam), 0, 9, None, 0, 144, None, None, None)
+    assert rc == -1 and b"NULL" in lib.rt_last_error()
+    rc = lib.rt_render_rows_dev(0, 8, 0, 8, ctypes.byref(env), ctypes.byref(cam), 0, 9, None, 0, 144, None, None, None)
+    assert rc == -1 and b"n_spheres" in lib.rt_last_error()
+    rc = lib.rt_render_rows_dev(0, 8, 3, 8, ctypes.byref(env), ctypes.byref(cam), 4, 12, None, 0, 144, None, None, None)
+    assert rc == -1 and b"rows" in lib.rt_last_error()
+    env.mode = 7
+    rc = lib.rt_render_rows_dev(0, 8, 3, 8, ctypes.byref(env), ctypes.byref(cam), 0, 9, None, 0, 144, None, None, None)
+    assert rc == -1 and b"mode" in lib.rt_last_error()
+    with pytest.raises(ValueError):
+        abi.check(rc, "rt_render_rows_dev")
+    rc = lib.rt_quantize_dev(0, 8, 0, 4, 4, 8, 5, None)
+    assert rc == -1
