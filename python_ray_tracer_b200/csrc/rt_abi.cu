@@ -201,7 +201,7 @@ int rt_trace_rays_dev(int device, const double* spheres_dev, int32_t n_spheres, 
     if (n_rays > 0 && directions_dev == nullptr) return fail(RT_ERR_BAD_ARG, "directions are NULL");
     if (origins_dev == nullptr && origin0 == nullptr) return fail(RT_ERR_BAD_ARG, "no ray origin given");
     if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return fail(RT_ERR_BAD_ARG, "unknown rgb_dtype %d", rgb_dtype);
-    if (rgb_dev == nullptr) return fail(RT_ERR_BAD_ARG, "rgb_dev is NULL");
+    if (n_rays > 0 && rgb_dev == nullptr) return fail(RT_ERR_BAD_ARG, "rgb_dev is NULL");
     if (plane_stride < n_rays) return fail(RT_ERR_BAD_ARG, "plane_stride %lld < %lld rays", (long long)plane_stride, (long long)n_rays);
     DeviceScope scope(device);
     if (scope.status != RT_OK) return scope.status;

@@ -193,7 +193,9 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
 
         // the mirror ray enters the parent as refl * 0.5 * gain * lit (shader.py:106)
         weight *= (lit0 ? 0.5 : 0.0) * m.specular_gain;
-        if (weight == 0.0) break;
+        // Exact keeps tracing a weightless chain, as the reference's unconditional recursion
+        // does (shader.py:90): its children add exactly 0 but count in the ray totals.
+        if (MODE != kModeExact && weight == 0.0) break;
         if (MODE == kModeFast && st.chain_bound > 0.0 && fabs(weight) * st.chain_bound < sp.cutoff) break;
 
         // mirror direction (shader.py:151): D - (N*2)*(D.N), normalised
