@@ -3,10 +3,12 @@
 // per-thread staging cache used by the *_host entry points.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 
 #include "../../include/rt_abi.h"
 #include "rt_launch.h"
@@ -121,6 +123,57 @@ rt::CameraParams camera_params(const rt_camera* cam, int32_t row0, int32_t row1)
     cp.row1 = row1;
     return cp;
 }
+
+// Ring of ticket counters per device (rt_launch.h).  A counter is zero whenever no launch
+// is using it: the kernels put it back to zero themselves.
+constexpr int kMaxDevices = 64;
+constexpr unsigned int kRingSlots = 1024;
+struct CounterRing {
+    unsigned int* base = nullptr;
+    std::atomic<unsigned int> next{0};
+};
+CounterRing g_rings[kMaxDevices];
+std::mutex g_ring_mutex;
+
+}  // namespace
+
+namespace rt {
+cudaError_t ticket_counter(unsigned int** counter_out) {
+    int device = 0;
+    cudaError_t err = cudaGetDevice(&device);
+    if (err != cudaSuccess) return err;
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    CounterRing& ring = g_rings[device];
+    if (ring.base == nullptr) {
+        std::lock_guard<std::mutex> lock(g_ring_mutex);
+        if (ring.base == nullptr) {
+            unsigned int* p = nullptr;
+            if ((err = cudaMalloc(&p, sizeof(unsigned int) * kRingSlots)) != cudaSuccess) return err;
+            if ((err = cudaMemset(p, 0, sizeof(unsigned int) * kRingSlots)) != cudaSuccess) {
+                cudaFree(p);
+                return err;
+            }
+            ring.base = p;
+        }
+    }
+    *counter_out = ring.base + (ring.next.fetch_add(1u) % kRingSlots);
+    return cudaSuccess;
+}
+
+void release_ticket_counters() {
+    std::lock_guard<std::mutex> lock(g_ring_mutex);
+    int previous = -1;
+    cudaGetDevice(&previous);
+    for (int d = 0; d < kMaxDevices; ++d) {
+        if (g_rings[d].base == nullptr) continue;
+        if (cudaSetDevice(d) == cudaSuccess) cudaFree(g_rings[d].base);
+        g_rings[d].base = nullptr;
+    }
+    if (previous >= 0) cudaSetDevice(previous);
+}
+}  // namespace rt
+
+namespace {
 
 const rt::Launchers& launchers(int mode) { return mode == RT_MODE_FAST ? rt::fast_launchers() : rt::exact_launchers(); }
 

@@ -10,6 +10,7 @@
 #include <cstring>
 
 #include "../../include/rt_abi.h"
+#include "rt_launch.h"
 
 namespace {
 
@@ -100,6 +101,7 @@ int enter(int device, Restore& restore, DeviceCache** cache) {
 extern "C" {
 
 int rt_release_cache(void) {
+    rt::release_ticket_counters();
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess) return RT_OK;
     Restore restore;

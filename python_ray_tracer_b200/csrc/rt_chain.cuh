@@ -26,13 +26,15 @@ __device__ __forceinline__ double material_bound(const SceneParams& sp, int s) {
     return kAmbient + fabs(m.diffuse_gain) * tex + dome + spec + film;
 }
 
-// Fill the shared-memory sphere records from the SoA in global memory.  Every block does
-// this once; the table is a few tens of bytes per sphere.  Must be called by all threads.
+// Fill the shared-memory sphere records from the SoA in global memory.  The kernels are
+// persistent (one resident block per slot, looping over tiles), so every block does this
+// once per launch; the table is 80 bytes per sphere.  Must be called by all threads.
 template <int MODE>
-__device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned char* smem) {
+__device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned char* smem, const double* origin0) {
     const int n = sp.n_spheres;
     SphereGeom* geom = reinterpret_cast<SphereGeom*>(smem);
-    SphereAux* aux = reinterpret_cast<SphereAux*>(smem + sizeof(SphereGeom) * (size_t)n);
+    SpherePrimary* prim = reinterpret_cast<SpherePrimary*>(smem + sizeof(SphereGeom) * (size_t)n);
+    SphereAux* aux = reinterpret_cast<SphereAux*>(smem + (sizeof(SphereGeom) + sizeof(SpherePrimary)) * (size_t)n);
     __shared__ unsigned long long s_bound_bits, s_gain_bits;
     if (threadIdx.x == 0) {
         s_bound_bits = 0ull;
@@ -47,6 +49,11 @@ __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned ch
         double r = __ldg(sp.spheres + (size_t)RT_F_RADIUS * n + s);
         geom[s] = {cx, cy, cz, r * r};
         aux[s] = {1.0 / r, (cx * cx) + (cy * cy) + (cz * cz)};
+        {
+            // rays of generation 0 of the camera kernel all start at origin0
+            double lx = origin0[0] - cx, ly = origin0[1] - cy, lz = origin0[2] - cz;
+            prim[s] = {lx, ly, lz, fma(lz, lz, fma(ly, ly, fma(lx, lx, -(r * r))))};
+        }
         if (MODE == kModeFast) {
             bound = fmax(bound, material_bound(sp, s));
             gain = fmax(gain, fabs(__ldg(sp.spheres + (size_t)RT_F_SPECULAR_GAIN * n + s)));
@@ -59,8 +66,9 @@ __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned ch
     }
     __syncthreads();
     Staged st;
-    st.geom = geom;
-    st.aux = aux;
+    st.geom = (unsigned int)__cvta_generic_to_shared(geom);
+    st.prim = (unsigned int)__cvta_generic_to_shared(prim);
+    st.aux = (unsigned int)__cvta_generic_to_shared(aux);
     st.chain_bound = -1.0;
     if (MODE == kModeFast && sp.cutoff > 0.0) {
         double lmax = __longlong_as_double((long long)s_bound_bits);
@@ -74,7 +82,9 @@ __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned ch
 // One camera or user ray through the scene: raytrace_scene (base.py:91-121) with the
 // recursion of shader.py:143-161 unrolled into a loop.  Exact ties between two shapes
 // (both contribute in the reference) resolve to the lowest shape index here.
-template <int MODE, bool STATS>
+// CAMERA: generation 0 starts at sp.eye (the camera kernel), so the fast policy uses the
+// staged per-sphere constants of that origin.
+template <int MODE, bool STATS, bool CAMERA>
 __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged& st, Vec3 o, Vec3 d,
                                             Counters& k) {
     const int n = sp.n_spheres;
@@ -94,25 +104,53 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
         // ---- nearest hit (base.py:97-105)
         double tmin = kMiss;
         int sid = -1;
-        for (int s = 0; s < n; ++s) {
-            double t;
-            if (MODE == kModeExact) {
-                t = sphere_distance_exact(o, d, st.geom[s], st.aux[s].cc);
-            } else {
-                HalfB q = half_b(o, d, st.geom[s]);
-                t = can_hit(q) ? near_root(q) : kMiss;
+        if (MODE == kModeExact) {
+            for (int s = 0; s < n; ++s) {
+                double t = sphere_distance_exact(o, d, load_geom(st, s), load_aux(st, s).cc);
+                if (t < tmin) {
+                    tmin = t;
+                    sid = s;
+                }
             }
-            if (t < tmin) {
-                tmin = t;
-                sid = s;
+        } else {
+            // two spheres per trip: their FP64 chains are independent and interleave
+            const bool primary = CAMERA && generation == 0;
+            int s = 0;
+            for (; s + 1 < n; s += 2) {
+                HalfB q0 = primary ? half_b_primary(d, load_prim(st, s)) : half_b(o, d, load_geom(st, s));
+                HalfB q1 = primary ? half_b_primary(d, load_prim(st, s + 1)) : half_b(o, d, load_geom(st, s + 1));
+                if (can_hit(q0)) {
+                    double t = near_root(q0);
+                    if (t < tmin) {
+                        tmin = t;
+                        sid = s;
+                    }
+                }
+                if (can_hit(q1)) {
+                    double t = near_root(q1);
+                    if (t < tmin) {
+                        tmin = t;
+                        sid = s + 1;
+                    }
+                }
+            }
+            if (s < n) {
+                HalfB q = primary ? half_b_primary(d, load_prim(st, s)) : half_b(o, d, load_geom(st, s));
+                if (can_hit(q)) {
+                    double t = near_root(q);
+                    if (t < tmin) {
+                        tmin = t;
+                        sid = s;
+                    }
+                }
             }
         }
         if (sid < 0) break;
         if (STATS) k.hits += 1;
 
         // ---- NumpyShader.create (shader.py:63-112)
-        const SphereGeom g = st.geom[sid];
-        const double inv_r = st.aux[sid].inv_r;
+        const SphereGeom g = load_geom(st, sid);
+        const double inv_r = load_aux(st, sid).inv_r;
         const Material m = load_material(sp, sid);
         const Vec3 centre = {g.cx, g.cy, g.cz};
         Vec3 hit, normal, nudged, to_eye;
@@ -151,7 +189,7 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
                 double spec = specular_exact(normal, to_light, to_eye, m.roughness, m.specular_gain);
                 spec_sum += spec * litf;
             } else if (lit) {
-                double lambert = fmax(fdot(normal, to_light), 0.0) * m.diffuse_gain;
+                double lambert = pos_part(fdot(normal, to_light)) * m.diffuse_gain;
                 local.x = fma(tex.x, lambert, local.x);
                 local.y = fma(tex.y, lambert, local.y);
                 local.z = fma(tex.z, lambert, local.z);
@@ -161,7 +199,7 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
         }
 
         // dome light (shader.py:234-244)
-        double ny = fmax(MODE == kModeExact ? (normal.x * 0.0) + (normal.y * 1.0) + (normal.z * 0.0) : normal.y, 0.0);
+        double ny = MODE == kModeExact ? fmax((normal.x * 0.0) + (normal.y * 1.0) + (normal.z * 0.0), 0.0) : pos_part(normal.y);
         double dome;
         if (MODE == kModeExact) {
             dome = 0.0;

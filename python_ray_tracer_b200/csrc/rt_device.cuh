@@ -111,12 +111,52 @@ __device__ __forceinline__ Vec3 norm_exact(Vec3 a) {
     return a * inv;
 }
 
-// Fast normalisation: one rsqrt, no division.  A zero vector stays zero like the
-// reference's (0 * 1/1).
+// ---------------------------------------------------------------------------------------
+// Fast-policy special functions.  CUDA's double sqrt / rsqrt / division are IEEE-rounded
+// and each carries a range-checked slow path (a branch plus a subroutine call).  The fast
+// policy only needs results good to a few ulp, so it seeds from the 64-bit MUFU
+// approximations (rel. error <= 2^-22, whole exponent range) and refines with two Newton
+// steps: branch-free, 5-8 FP64 instructions each.  Arguments must be positive, normal
+// and finite; callers guard the zero case with a select.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ double rsqrt_fast(double x) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double hx = 0.5 * x;
+    double e = fma(-hx * y, y, 0.5);  // (1 - x*y*y)/2
+    y = fma(y, e, y);
+    e = fma(-hx * y, y, 0.5);
+    return fma(y, e, y);
+}
+__device__ __forceinline__ double rcp_fast(double x) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-x, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    return fma(y, e, y);
+}
+// sqrt(x) for x > 0: one Newton step on the reciprocal root, then one on the root itself.
+__device__ __forceinline__ double sqrt_pos_fast(double x) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-(0.5 * x) * y, y, 0.5);
+    y = fma(y, e, y);            // ~2^-44
+    double s = x * y;
+    double r = fma(-s, s, x);    // x - s*s
+    return fma(r, 0.5 * y, s);
+}
+__device__ __forceinline__ double sqrt_fast(double x) { return x > 0.0 ? sqrt_pos_fast(x) : 0.0; }
+// max(v,0) / clip without the NaN plumbing of fmax()/fmin() (inputs here are never NaN).
+__device__ __forceinline__ double pos_part(double v) { return v > 0.0 ? v : 0.0; }
+__device__ __forceinline__ double clip01_fast(double v) { return v > 0.0 ? (v < 1.0 ? v : 1.0) : 0.0; }
+
+// Fast normalisation: one reciprocal square root, no division.  A zero vector stays zero
+// like the reference's (0 * 1/1).
 __device__ __forceinline__ double fdot(Vec3 a, Vec3 b) { return fma(a.z, b.z, fma(a.y, b.y, a.x * b.x)); }
 __device__ __forceinline__ Vec3 norm_fast(Vec3 a) {
     double m2 = fdot(a, a);
-    double inv = m2 > 0.0 ? rsqrt(m2) : 1.0;
+    double inv = m2 > 1e-290 ? rsqrt_fast(m2) : 1.0;  // (flushes vectors shorter than 1e-145)
     return a * inv;
 }
 

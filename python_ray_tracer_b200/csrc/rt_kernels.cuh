@@ -6,14 +6,44 @@
 
 namespace rt {
 
-constexpr int kTileW = 32;        // pixels per block, x
-constexpr int kTileH = 4;         // pixels per block, y
-constexpr int kBlockThreads = kTileW * kTileH;
-constexpr int kWarpTileW = 8;     // each warp owns an 8x4 patch: bounce coherence, and
-                                  // every row segment it stores is one full 32-byte sector
+// Tuning knobs (overridable with -D for the variant sweeps of profiles/).
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 5  // resident 128-thread blocks per SM the register allocator must allow
+#endif
+#ifndef RT_STATIC_PCT
+#define RT_STATIC_PCT 70  // share of the work items handed out statically (no atomics)
+#endif
+
+constexpr int kWarpTileW = 8;     // each warp renders 8x4 pixel patches: bounce coherence, and
+constexpr int kWarpTileH = 4;     // every row segment it stores is one full 32-byte sector
+constexpr int kBlockThreads = 128;
+constexpr int kBlockWarps = kBlockThreads / 32;
 
 __host__ __device__ inline size_t staged_bytes(int n_spheres) {
-    return (sizeof(SphereGeom) + sizeof(SphereAux)) * (size_t)n_spheres;
+    return (sizeof(SphereGeom) + sizeof(SpherePrimary) + sizeof(SphereAux)) * (size_t)n_spheres;
+}
+
+// Work distribution of the persistent kernels.  A work item is one 8x4 patch (or 32 rays).
+// The first static_rounds * n_warps items are dealt round-robin (warp w takes items w,
+// w + n_warps, ...: a stratified sample of the frame, no atomics); the rest are drawn one
+// at a time from a device counter (lane 0, one atomicAdd per ticket), so the tail of the
+// launch is balanced at the granularity of a single patch.  Every warp keeps its next
+// ticket in flight while it works, and draws exactly one ticket >= n_tickets before it
+// leaves, so the draw that returns n_tickets + n_warps - 1 is the last of the launch and
+// puts the counter back to zero for the next launch that uses it.
+struct Tickets {
+    unsigned int* counter;
+    unsigned int n_tickets;      // items handed out dynamically
+    unsigned int n_warps;        // gridDim.x * kBlockWarps
+    unsigned int static_rounds;  // items [0, static_rounds * n_warps) are dealt statically
+};
+__device__ __forceinline__ unsigned int draw_ticket(const Tickets& tk, int lane) {
+    unsigned int t = 0;
+    if (lane == 0) {
+        t = atomicAdd(tk.counter, 1u);
+        if (t == tk.n_tickets + tk.n_warps - 1u) atomicExch(tk.counter, 0u);
+    }
+    return __shfl_sync(0xffffffffu, t, 0);
 }
 
 // np.linspace sample i (base.py:132-139): i*step + start, last sample = stop exactly.
@@ -77,42 +107,75 @@ __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p
     }
 }
 
-// Camera rows [row0,row1): ray generation + trace + stores, one thread per pixel.
+// Camera rows [row0,row1): ray generation + trace + stores, one thread per pixel of a
+// patch.  Persistent: the grid is sized to the resident block slots of the GPU.
 template <int MODE, bool STATS>
-__global__ void __launch_bounds__(kBlockThreads) render_rows_kernel(SceneParams sp, CameraParams cp,
-                                                                   OutputParams out) {
+__global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_rows_kernel(SceneParams sp, CameraParams cp,
+                                                                   OutputParams out, Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const Staged st = stage_scene<MODE>(sp, smem);
+    const Staged st = stage_scene<MODE>(sp, smem, cp.cam);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int col = blockIdx.x * kTileW + warp * kWarpTileW + (lane & (kWarpTileW - 1));
-    const int row = cp.row0 + blockIdx.y * kTileH + (lane >> 3);
-    const bool inside = col < cp.width && row < cp.row1;
-
+    const int lane = threadIdx.x & 31;
+    const int px = lane & (kWarpTileW - 1), py = lane >> 3;
+    const unsigned int tiles_x = (unsigned int)(cp.width + kWarpTileW - 1) / kWarpTileW;
+    const unsigned int warp_id = blockIdx.x * kBlockWarps + (threadIdx.x >> 5);
+    const Vec3 eye = {cp.cam[0], cp.cam[1], cp.cam[2]};
     Counters k = {0, 0, 0, 0};
-    if (inside) {
-        Vec3 o = {cp.cam[0], cp.cam[1], cp.cam[2]};
-        Vec3 d = primary_direction<MODE>(cp, col, row);
-        Vec3 c = trace_chain<MODE, STATS>(sp, st, o, d, k);
-        store_pixel(out, (long long)(row - cp.row0) * cp.width + col, c);
+
+    auto render_patch = [&](unsigned int item) {
+        const unsigned int ty = item / tiles_x, tx = item - ty * tiles_x;
+        const int row = cp.row0 + (int)ty * kWarpTileH + py;
+        const int col = (int)tx * kWarpTileW + px;
+        if (col < cp.width && row < cp.row1) {
+            Vec3 d = primary_direction<MODE>(cp, col, row);
+            Vec3 c = trace_chain<MODE, STATS, true>(sp, st, eye, d, k);
+            store_pixel(out, (long long)(row - cp.row0) * cp.width + col, c);
+        }
+    };
+
+    unsigned int next = draw_ticket(tk, lane);  // in flight during the static rounds
+#pragma unroll 1
+    for (unsigned int r = 0; r < tk.static_rounds; ++r) render_patch(r * tk.n_warps + warp_id);
+    const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
+#pragma unroll 1
+    while (next < tk.n_tickets) {
+        const unsigned int item = first_dynamic + next;
+        next = draw_ticket(tk, lane);
+        render_patch(item);
     }
     flush_counters<STATS>(k, out.stats);
 }
 
-// Explicit ray batch, one thread per ray.
+// Explicit ray batch, one thread per ray, same work distribution (an item = 32 rays).
 template <int MODE, bool STATS>
-__global__ void __launch_bounds__(kBlockThreads) trace_rays_kernel(SceneParams sp, RayBatch rb,
-                                                                  OutputParams out) {
+__global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) trace_rays_kernel(SceneParams sp, RayBatch rb,
+                                                                  OutputParams out, Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const Staged st = stage_scene<MODE>(sp, smem);
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const Staged st = stage_scene<MODE>(sp, smem, sp.eye);
+    const int lane = threadIdx.x & 31;
+    const unsigned int warp_id = blockIdx.x * kBlockWarps + (threadIdx.x >> 5);
     Counters k = {0, 0, 0, 0};
-    if (i < rb.n) {
-        Vec3 o = {rb.origin0[0], rb.origin0[1], rb.origin0[2]};
-        if (rb.origins != nullptr) o = {rb.origins[i], rb.origins[rb.n + i], rb.origins[2 * rb.n + i]};
-        Vec3 d = {rb.directions[i], rb.directions[rb.n + i], rb.directions[2 * rb.n + i]};
-        Vec3 c = trace_chain<MODE, STATS>(sp, st, o, d, k);
-        store_pixel(out, i, c);
+
+    auto trace_item = [&](unsigned int item) {
+        const long long i = (long long)item * 32 + lane;
+        if (i < rb.n) {
+            Vec3 o = {rb.origin0[0], rb.origin0[1], rb.origin0[2]};
+            if (rb.origins != nullptr) o = {rb.origins[i], rb.origins[rb.n + i], rb.origins[2 * rb.n + i]};
+            Vec3 d = {rb.directions[i], rb.directions[rb.n + i], rb.directions[2 * rb.n + i]};
+            Vec3 c = trace_chain<MODE, STATS, false>(sp, st, o, d, k);
+            store_pixel(out, i, c);
+        }
+    };
+
+    unsigned int next = draw_ticket(tk, lane);
+#pragma unroll 1
+    for (unsigned int r = 0; r < tk.static_rounds; ++r) trace_item(r * tk.n_warps + warp_id);
+    const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
+#pragma unroll 1
+    while (next < tk.n_tickets) {
+        const unsigned int item = first_dynamic + next;
+        next = draw_ticket(tk, lane);
+        trace_item(item);
     }
     flush_counters<STATS>(k, out.stats);
 }

@@ -20,6 +20,12 @@ struct Launchers {
 const Launchers& exact_launchers();  // trace_exact.cu, compiled with -fmad=false
 const Launchers& fast_launchers();   // trace_fast.cu
 
+// One zeroed ticket counter (device memory of the current device) for the next persistent
+// launch; see rt_kernels.cuh:Tickets.  Counters come from a per-device ring so launches
+// in flight on different streams never share one.  Defined in rt_abi.cu.
+cudaError_t ticket_counter(unsigned int** counter_out);
+void release_ticket_counters();
+
 // Largest scene whose sphere records fit one block's shared memory.
 int max_staged_spheres();
 

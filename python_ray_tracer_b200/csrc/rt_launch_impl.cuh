@@ -11,44 +11,66 @@ namespace {
 constexpr int kMode = RT_TU_MODE;
 constexpr size_t kMaxDynamicSmem = 227 * 1024 - 64;  // per-block limit on sm_100a minus statics
 
+// Persistent launch shape: as many blocks as the device keeps resident for this kernel at
+// this shared-memory size, but no more than there are tickets to hand out.
 template <typename Kernel>
-cudaError_t prepare(Kernel kernel, size_t smem) {
+cudaError_t persistent_grid(Kernel kernel, size_t smem, unsigned int n_tickets, unsigned int* grid_out) {
     if (smem > kMaxDynamicSmem) return cudaErrorInvalidValue;
-    if (smem > 48 * 1024) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // one entry per kernel instantiation and host thread: the answer of the last query
+    static thread_local struct { int device; size_t smem; unsigned int slots; } cached = {-1, 0, 0};
+    cudaError_t err;
+    int device = 0;
+    if ((err = cudaGetDevice(&device)) != cudaSuccess) return err;
+    if (cached.device != device || cached.smem != smem) {
+        if (smem > 48 * 1024 &&
+            (err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+            return err;
+        int sms = 0, per_sm = 0;
+        if ((err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return err;
+        if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlockThreads, smem)) != cudaSuccess) return err;
+        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+        cached = {device, smem, (unsigned int)sms * (unsigned int)per_sm};
+    }
+    const unsigned int slots = cached.slots;
+    const unsigned int wanted = (n_tickets + kBlockWarps - 1) / kBlockWarps;
+    *grid_out = wanted < slots ? wanted : slots;
     return cudaSuccess;
+}
+
+template <typename Kernel, typename Work>
+cudaError_t launch_persistent(Kernel kernel, const SceneParams& sp, const Work& work, const OutputParams& out,
+                              unsigned long long n_items64, cudaStream_t stream) {
+    if (n_items64 > 0xfffffff0ull) return cudaErrorInvalidValue;
+    const unsigned int n_items = (unsigned int)n_items64;
+    const size_t smem = staged_bytes(sp.n_spheres);
+    unsigned int grid = 0;
+    cudaError_t err = persistent_grid(kernel, smem, n_items, &grid);
+    if (err != cudaSuccess) return err;
+    Tickets tk;
+    if ((err = ticket_counter(&tk.counter)) != cudaSuccess) return err;
+    tk.n_warps = grid * kBlockWarps;
+    tk.static_rounds = (unsigned int)((unsigned long long)n_items * RT_STATIC_PCT / 100ull / tk.n_warps);
+    tk.n_tickets = n_items - tk.static_rounds * tk.n_warps;
+    kernel<<<grid, kBlockThreads, smem, stream>>>(sp, work, out, tk);
+    return cudaGetLastError();
 }
 
 cudaError_t render_rows(bool stats, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
                         cudaStream_t stream) {
     const int rows = cp.row1 - cp.row0;
     if (rows <= 0 || cp.width <= 0) return cudaSuccess;
-    const size_t smem = staged_bytes(sp.n_spheres);
-    dim3 grid((cp.width + kTileW - 1) / kTileW, (rows + kTileH - 1) / kTileH);
-    cudaError_t err;
-    if (stats) {
-        if ((err = prepare(render_rows_kernel<kMode, true>, smem)) != cudaSuccess) return err;
-        render_rows_kernel<kMode, true><<<grid, kBlockThreads, smem, stream>>>(sp, cp, out);
-    } else {
-        if ((err = prepare(render_rows_kernel<kMode, false>, smem)) != cudaSuccess) return err;
-        render_rows_kernel<kMode, false><<<grid, kBlockThreads, smem, stream>>>(sp, cp, out);
-    }
-    return cudaGetLastError();
+    const unsigned long long tiles_x = (unsigned long long)(cp.width + kWarpTileW - 1) / kWarpTileW;
+    const unsigned long long tiles_y = (unsigned long long)(rows + kWarpTileH - 1) / kWarpTileH;
+    if (stats) return launch_persistent(render_rows_kernel<kMode, true>, sp, cp, out, tiles_x * tiles_y, stream);
+    return launch_persistent(render_rows_kernel<kMode, false>, sp, cp, out, tiles_x * tiles_y, stream);
 }
 
 cudaError_t trace_rays(bool stats, const SceneParams& sp, const RayBatch& rb, const OutputParams& out,
                        cudaStream_t stream) {
     if (rb.n <= 0) return cudaSuccess;
-    const size_t smem = staged_bytes(sp.n_spheres);
-    const unsigned int grid = (unsigned int)((rb.n + kBlockThreads - 1) / kBlockThreads);
-    cudaError_t err;
-    if (stats) {
-        if ((err = prepare(trace_rays_kernel<kMode, true>, smem)) != cudaSuccess) return err;
-        trace_rays_kernel<kMode, true><<<grid, kBlockThreads, smem, stream>>>(sp, rb, out);
-    } else {
-        if ((err = prepare(trace_rays_kernel<kMode, false>, smem)) != cudaSuccess) return err;
-        trace_rays_kernel<kMode, false><<<grid, kBlockThreads, smem, stream>>>(sp, rb, out);
-    }
-    return cudaGetLastError();
+    const unsigned long long n_items = ((unsigned long long)rb.n + 31ull) / 32ull;
+    if (stats) return launch_persistent(trace_rays_kernel<kMode, true>, sp, rb, out, n_items, stream);
+    return launch_persistent(trace_rays_kernel<kMode, false>, sp, rb, out, n_items, stream);
 }
 
 cudaError_t sphere_distance(const RayBatch& rb, const double* c, double radius, double* out,

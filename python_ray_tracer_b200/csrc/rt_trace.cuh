@@ -7,11 +7,40 @@
 namespace rt {
 
 // Shared-memory view of the staged scene (filled by stage_scene()).
+// Per-sphere records staged in shared memory are addressed through 32-bit shared-window
+// addresses and read with explicit ld.shared.v2.f64: every lane reads the same record
+// (one broadcast wavefront), the address is base + index * 32 with no per-use
+// generic-to-shared conversion.
+struct __align__(16) SpherePrimary {
+    double lx, ly, lz;  // origin0 - centre
+    double c;           // |origin0 - centre|^2 - r^2
+};
 struct Staged {
-    const SphereGeom* geom;
-    const SphereAux* aux;
+    unsigned int geom;   // SphereGeom[n]
+    unsigned int prim;   // SpherePrimary[n]: constants of rays that start at the camera
+    unsigned int aux;    // SphereAux[n]
     double chain_bound;  // Fast: sup of |local colour| over materials / (1 - sup w), or < 0
 };
+__device__ __forceinline__ void lds_f64x2(unsigned int addr, double& a, double& b) {
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "r"(addr));
+}
+__device__ __forceinline__ SphereGeom load_geom(const Staged& st, int s) {
+    SphereGeom g;
+    lds_f64x2(st.geom + (unsigned int)s * 32u, g.cx, g.cy);
+    lds_f64x2(st.geom + (unsigned int)s * 32u + 16u, g.cz, g.rr);
+    return g;
+}
+__device__ __forceinline__ SpherePrimary load_prim(const Staged& st, int s) {
+    SpherePrimary p;
+    lds_f64x2(st.prim + (unsigned int)s * 32u, p.lx, p.ly);
+    lds_f64x2(st.prim + (unsigned int)s * 32u + 16u, p.lz, p.c);
+    return p;
+}
+__device__ __forceinline__ SphereAux load_aux(const Staged& st, int s) {
+    SphereAux a;
+    lds_f64x2(st.aux + (unsigned int)s * 16u, a.inv_r, a.cc);
+    return a;
+}
 
 // ---------------------------------------------------------------------------------------
 // NumpySphere.intersect (shape.py:28-51)
@@ -44,12 +73,29 @@ __device__ __forceinline__ HalfB half_b(Vec3 o, Vec3 d, const SphereGeom& g) {
     q.disc = fma(q.b, q.b, -q.c);
     return q;
 }
-__device__ __forceinline__ bool can_hit(const HalfB& q) { return q.disc > 0.0 && (q.b < 0.0 || q.c < 0.0); }
+// Camera rays all start at the eye: O-C and |O-C|^2 - r^2 are per-sphere constants of the
+// launch (staged once per block), leaving one dot product and one FMA per test.
+__device__ __forceinline__ HalfB half_b_primary(Vec3 d, const SpherePrimary& p) {
+    HalfB q;
+    q.b = fma(d.z, p.lz, fma(d.y, p.ly, d.x * p.lx));
+    q.c = p.c;
+    q.disc = fma(q.b, q.b, -q.c);
+    return q;
+}
+// The sign and "is positive" tests read the high word of the double on the integer pipe
+// instead of spending FP64-pipe slots on DSETP: hi < 0 <=> sign bit set; hi > 0 <=> the
+// value is positive and above 2^-1022 * 2^20 (smaller discriminants/roots count as a miss;
+// the reference's own expression carries ~1e-6 absolute noise there).
+__device__ __forceinline__ bool is_neg(double v) { return __double2hiint(v) < 0; }
+__device__ __forceinline__ bool is_pos(double v) { return __double2hiint(v) > 0; }
+__device__ __forceinline__ bool can_hit(const HalfB& q) {
+    return ((__double2hiint(q.b) | __double2hiint(q.c)) < 0) && is_pos(q.disc);
+}
 __device__ __forceinline__ double near_root(const HalfB& q) {
-    double sq = sqrt(q.disc);
+    double sq = sqrt_pos_fast(q.disc);  // callers checked disc > 0
     double h0 = -q.b - sq;
-    double h = h0 > 0.0 ? h0 : sq - q.b;
-    return h > 0.0 ? h : kMiss;
+    double h = is_pos(h0) ? h0 : sq - q.b;
+    return is_pos(h) ? h : kMiss;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -61,28 +107,28 @@ __device__ __forceinline__ bool in_light(const Staged& st, int n, int s, Vec3 p,
                                          unsigned long long& tests) {
     tests += (unsigned long long)n;
     if (MODE == kModeExact) {
-        double own = sphere_distance_exact(p, l, st.geom[s], st.aux[s].cc);
+        double own = sphere_distance_exact(p, l, load_geom(st, s), load_aux(st, s).cc);
         bool lit = true;
         for (int j = 0; j < n; ++j) {
-            double u = sphere_distance_exact(p, l, st.geom[j], st.aux[j].cc);
+            double u = sphere_distance_exact(p, l, load_geom(st, j), load_aux(st, j).cc);
             lit = lit && !(u < own);
         }
         return lit;
     } else {
-        HalfB qo = half_b(p, l, st.geom[s]);
-        double own = can_hit(qo) ? near_root(qo) : kMiss;
-        for (int j = 0; j < n; ++j) {
-            if (j == s) continue;
-            HalfB q = half_b(p, l, st.geom[j]);
-            if (can_hit(q)) {
-                if (own == kMiss) {
-                    // any positive root occludes; near_root() > 0 is implied by can_hit()
-                    // except when rounding puts the root at <= 0, so confirm it.
-                    if (near_root(q) != kMiss) return false;
-                } else if (near_root(q) < own) {
-                    return false;
-                }
-            }
+        HalfB qo = half_b(p, l, load_geom(st, s));
+        const double own = can_hit(qo) ? near_root(qo) : kMiss;
+        // any sphere hit closer than `own` occludes (a root that rounds to <= 0 comes back
+        // as kMiss and never does).  Two spheres per trip: independent FP64 chains.
+        int j = 0;
+        for (; j + 1 < n; j += 2) {
+            HalfB q0 = half_b(p, l, load_geom(st, j));
+            HalfB q1 = half_b(p, l, load_geom(st, j + 1));
+            if (j != s && can_hit(q0) && near_root(q0) < own) return false;
+            if (j + 1 != s && can_hit(q1) && near_root(q1) < own) return false;
+        }
+        if (j < n && j != s) {
+            HalfB q = half_b(p, l, load_geom(st, j));
+            if (can_hit(q) && near_root(q) < own) return false;
         }
         return true;
     }
@@ -146,17 +192,18 @@ __device__ __forceinline__ double specular_exact(Vec3 n, Vec3 to_light, Vec3 to_
 }
 
 // Fast: l and v arrive normalised (re-normalising a unit vector changes the last bit
-// only); the four quotients F*D*G1*G1/(4 NdotV + eps) share one division; x^5 and x^2.5
-// are products and one square root.
+// only); the four quotients F*D*G1*G1/(4 NdotV + eps) share one reciprocal; x^5 and x^2.5
+// are products and one square root; roots and the reciprocal are the branch-free
+// Newton forms of rt_device.cuh.
 __device__ __forceinline__ double specular_fast(Vec3 n, Vec3 l, Vec3 v, double rough, double gain) {
-    double ndv = clip01(fdot(n, v));
+    double ndv = clip01_fast(fdot(n, v));
     if (ndv <= 0.0) return 0.0;
     Vec3 hv = l + v;
     double h2 = fdot(hv, hv);
-    double ih = h2 > 0.0 ? rsqrt(h2) : 1.0;
-    double ndh = clip01(fdot(n, hv) * ih);
-    double vdh = clip01(fdot(v, hv) * ih);
-    double ndl = clip01(fdot(n, l));
+    double ih = h2 > 1e-290 ? rsqrt_fast(h2) : 1.0;
+    double ndh = clip01_fast(fdot(n, hv) * ih);
+    double vdh = clip01_fast(fdot(v, hv) * ih);
+    double ndl = clip01_fast(fdot(n, l));
     double omv = 1.0 - vdh;
     double omv2 = omv * omv;
     double fres = fma(1.0 - kF0, omv2 * omv2 * omv, kF0);
@@ -164,13 +211,13 @@ __device__ __forceinline__ double specular_fast(Vec3 n, Vec3 l, Vec3 v, double r
     double a2 = alpha * alpha;
     double oma2 = 1.0 - a2;
     double den = fma(ndh * ndh, a2 - 1.0, 1.0);
-    double sl = sqrt(fma(oma2, ndl * ndl, a2));
-    double sv = sqrt(fma(oma2, ndv * ndv, a2));
+    double sl = sqrt_fast(fma(oma2, ndl * ndl, a2));
+    double sv = sqrt_fast(fma(oma2, ndv * ndv, a2));
     double num = fres * a2 * (4.0 * ndl * ndv);
-    double dn = kPi * fma(den, den, kEps) * (ndl + sl + kEps) * (ndv + sv + kEps) * fma(4.0, ndv, kEps);
-    double base = num / dn;
+    double dn = (kPi * fma(den, den, kEps)) * ((ndl + sl + kEps) * (ndv + sv + kEps)) * fma(4.0, ndv, kEps);
+    double base = num * rcp_fast(dn);  // dn >= pi*eps*eps*eps > 0
     double x = 1.0 - ndv;
-    double glint = x * x * sqrt(x) * ndl;
+    double glint = (x * x) * sqrt_fast(x) * ndl;
     return fma(gain, glint, base);
 }
 
@@ -179,14 +226,29 @@ __device__ __forceinline__ double specular_fast(Vec3 n, Vec3 l, Vec3 v, double r
 // ---------------------------------------------------------------------------------------
 template <int MODE>
 __device__ __forceinline__ Vec3 film_color(Vec3 n, Vec3 to_eye) {
-    double va = clip01(MODE == kModeExact ? dot(n, to_eye) : fdot(n, to_eye));
-    double af = fabs(va - 0.5) * 2.0;
-    double phase = af * kPi * kFilmThickness * 10.0;
-    double ip = sin(phase);
-    double r = ip * kHueShift + (1.0 - kHueShift) * (1.0 - ip);
-    double g = ip * (1.0 - kHueShift) + kHueShift * (1.0 - ip);
-    double b = 0.5 + 0.5 * ip;
-    return {r, g, b};
+    if (MODE == kModeExact) {
+        double va = clip01(dot(n, to_eye));
+        double af = fabs(va - 0.5) * 2.0;
+        double phase = af * kPi * kFilmThickness * 10.0;
+        double ip = sin(phase);
+        double r = ip * kHueShift + (1.0 - kHueShift) * (1.0 - ip);
+        double g = ip * (1.0 - kHueShift) + kHueShift * (1.0 - ip);
+        double b = 0.5 + 0.5 * ip;
+        return {r, g, b};
+    }
+    // Fast: the tint is a smooth function of N.V, bounded by 1 and scaled by
+    // 0.1 * iridescence_gain afterwards, so single precision (abs. error < 1e-6 before the
+    // scale) is far inside the 1e-4 budget.  phase = af * 3*pi: reduce to one period in
+    // turns, then the hardware sine on [-pi, pi].
+    float va = (float)clip01_fast(fdot(n, to_eye));
+    float turns = fabsf(va - 0.5f) * 3.0f;  // phase / (2 pi), in [0, 1.5]
+    turns -= rintf(turns);                    // [-0.5, 0.5]
+    float ip = __sinf(turns * 6.283185307179586f);
+    const float hs = (float)kHueShift;
+    float r = fmaf(ip, hs, (1.0f - hs) * (1.0f - ip));
+    float g = fmaf(ip, 1.0f - hs, hs * (1.0f - ip));
+    float b = fmaf(0.5f, ip, 0.5f);
+    return {(double)r, (double)g, (double)b};
 }
 
 }  // namespace rt

@@ -4,5 +4,5 @@
 
 namespace rt {
 const Launchers& fast_launchers() { return kLaunchers; }
-int max_staged_spheres() { return (int)(kMaxDynamicSmem / (sizeof(SphereGeom) + sizeof(SphereAux))); }
+int max_staged_spheres() { return (int)(kMaxDynamicSmem / staged_bytes(1)); }
 }  // namespace rt

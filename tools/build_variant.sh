@@ -1,0 +1,21 @@
+#!/bin/bash
+# Build a tuning variant of librt_b200.so into build/variants/<name>/ (git-ignored; travels to
+# the GPU box).  usage: tools/build_variant.sh <name> [extra nvcc flags...]
+# Select it at run time with RT_B200_LIBRARY=build/variants/<name>/librt_b200.so
+set -euo pipefail
+name=$1; shift
+root=$(cd "$(dirname "$0")/.." && pwd)
+src=$root/python_ray_tracer_b200/csrc
+out=$root/build/variants/$name
+mkdir -p "$out"
+NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function --expt-relaxed-constexpr"
+pids=()
+for f in trace_exact trace_fast rt_abi rt_abi_host rt_peaks; do
+  extra=""; [ "$f" = trace_exact ] && extra="-fmad=false"
+  $NVCC $FLAGS $extra "$@" -c "$src/$f.cu" -o "$out/$f.o" &
+  pids+=($!)
+done
+for p in "${pids[@]}"; do wait "$p"; done
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "$out/librt_b200.so" "$out"/*.o
+$NVCC $FLAGS "$@" -Xptxas -v -c "$src/trace_fast.cu" -o /dev/null 2>&1 | grep -A2 "render_rows_kernelILi1ELb0" | grep -E "Used|spill" | sed "s/^/[$name] /"
