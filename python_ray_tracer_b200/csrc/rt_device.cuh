@@ -146,10 +146,15 @@ __device__ __forceinline__ double sqrt_pos_fast(double x) {
     double r = fma(-s, s, x);    // x - s*s
     return fma(r, 0.5 * y, s);
 }
-__device__ __forceinline__ double sqrt_fast(double x) { return x > 0.0 ? sqrt_pos_fast(x) : 0.0; }
+__device__ __forceinline__ double sqrt_fast(double x) { return __double2hiint(x) > 0 ? sqrt_pos_fast(x) : 0.0; }
 // max(v,0) / clip without the NaN plumbing of fmax()/fmin() (inputs here are never NaN).
-__device__ __forceinline__ double pos_part(double v) { return v > 0.0 ? v : 0.0; }
-__device__ __forceinline__ double clip01_fast(double v) { return v > 0.0 ? (v < 1.0 ? v : 1.0) : 0.0; }
+// The tests read the sign / exponent from the high word on the integer pipe (a written
+// "v < 1.0 ? v : 1.0" is turned back into the DSETP.MIN + fix-up sequence of fmin()).
+__device__ __forceinline__ double pos_part(double v) { return __double2hiint(v) < 0 ? 0.0 : v; }
+__device__ __forceinline__ double clip01_fast(double v) {
+    const int hi = __double2hiint(v);
+    return hi < 0 ? 0.0 : (hi >= 0x3ff00000 ? 1.0 : v);
+}
 
 // Fast normalisation: one reciprocal square root, no division.  A zero vector stays zero
 // like the reference's (0 * 1/1).

@@ -16,12 +16,13 @@ constexpr size_t kMaxDynamicSmem = 227 * 1024 - 64;  // per-block limit on sm_10
 template <typename Kernel>
 cudaError_t persistent_grid(Kernel kernel, size_t smem, unsigned int n_tickets, unsigned int* grid_out) {
     if (smem > kMaxDynamicSmem) return cudaErrorInvalidValue;
-    // one entry per kernel instantiation and host thread: the answer of the last query
-    static thread_local struct { int device; size_t smem; unsigned int slots; } cached = {-1, 0, 0};
+    // the answer of the last query per host thread (kernels of one signature share this
+    // function instance, so the kernel address is part of the key)
+    static thread_local struct { const void* kernel; int device; size_t smem; unsigned int slots; } cached = {nullptr, -1, 0, 0};
     cudaError_t err;
     int device = 0;
     if ((err = cudaGetDevice(&device)) != cudaSuccess) return err;
-    if (cached.device != device || cached.smem != smem) {
+    if (cached.kernel != (const void*)kernel || cached.device != device || cached.smem != smem) {
         if (smem > 48 * 1024 &&
             (err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
             return err;
@@ -29,7 +30,7 @@ cudaError_t persistent_grid(Kernel kernel, size_t smem, unsigned int n_tickets, 
         if ((err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return err;
         if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlockThreads, smem)) != cudaSuccess) return err;
         if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-        cached = {device, smem, (unsigned int)sms * (unsigned int)per_sm};
+        cached = {(const void*)kernel, device, smem, (unsigned int)sms * (unsigned int)per_sm};
     }
     const unsigned int slots = cached.slots;
     const unsigned int wanted = (n_tickets + kBlockWarps - 1) / kBlockWarps;

@@ -196,14 +196,17 @@ __device__ __forceinline__ double specular_exact(Vec3 n, Vec3 to_light, Vec3 to_
 // are products and one square root; roots and the reciprocal are the branch-free
 // Newton forms of rt_device.cuh.
 __device__ __forceinline__ double specular_fast(Vec3 n, Vec3 l, Vec3 v, double rough, double gain) {
-    double ndv = clip01_fast(fdot(n, v));
-    if (ndv <= 0.0) return 0.0;
+    // n, l, v, h are unit vectors to within rounding: a cosine can exceed 1 only by a few
+    // ulp, which moves no term below by more than that, so only the lower clip is applied
+    // (sqrt_fast() returns 0 for a 1 - cos that rounds negative).
+    double ndv = fdot(n, v);
+    if (__double2hiint(ndv) <= 0) return 0.0;  // NdotV <= 0 (or denormal)
     Vec3 hv = l + v;
     double h2 = fdot(hv, hv);
     double ih = h2 > 1e-290 ? rsqrt_fast(h2) : 1.0;
-    double ndh = clip01_fast(fdot(n, hv) * ih);
-    double vdh = clip01_fast(fdot(v, hv) * ih);
-    double ndl = clip01_fast(fdot(n, l));
+    double ndh = pos_part(fdot(n, hv) * ih);
+    double vdh = pos_part(fdot(v, hv) * ih);
+    double ndl = pos_part(fdot(n, l));
     double omv = 1.0 - vdh;
     double omv2 = omv * omv;
     double fres = fma(1.0 - kF0, omv2 * omv2 * omv, kF0);
@@ -240,7 +243,7 @@ __device__ __forceinline__ Vec3 film_color(Vec3 n, Vec3 to_eye) {
     // 0.1 * iridescence_gain afterwards, so single precision (abs. error < 1e-6 before the
     // scale) is far inside the 1e-4 budget.  phase = af * 3*pi: reduce to one period in
     // turns, then the hardware sine on [-pi, pi].
-    float va = (float)clip01_fast(fdot(n, to_eye));
+    float va = (float)pos_part(fdot(n, to_eye));  // <= 1 + a few ulp: the upper clip is moot
     float turns = fabsf(va - 0.5f) * 3.0f;  // phase / (2 pi), in [0, 1.5]
     turns -= rintf(turns);                    // [-0.5, 0.5]
     float ip = __sinf(turns * 6.283185307179586f);
