@@ -154,6 +154,26 @@ int rt_render_rows_dev(int device, const double* spheres_dev, int32_t n_spheres,
                        uint64_t* stats_dev, void* stream);
 
 /*
+ * rt_render_strips_dev -- the same, for an interleaved shard of the frame: the image is
+ * cut into strips of strip_rows rows (strip k = rows [k*strip_rows, (k+1)*strip_rows),
+ * the last one possibly shorter) and this call renders strips strip_first,
+ * strip_first + strip_step, ...  The multi-GPU row-band partition (rank r of G renders
+ * strips r, r+G, ...: every shard is a stratified sample of the frame, so shards cost
+ * the same without a cost model).  Pixels are independent in the reference
+ * (base.py:102-119 masks per pixel), so any partition is exact.
+ *   rgb_dev / rgba8_dev  the shard's rows packed in strip order: local row r is image
+ *                        row (strip_first + (r / strip_rows) * strip_step) * strip_rows
+ *                        + r % strip_rows;  rt_strip_shard_rows() rows in total.
+ */
+int64_t rt_strip_shard_rows(int32_t height, int32_t strip_rows, int32_t strip_first, int32_t strip_step);
+int rt_render_strips_dev(int device, const double* spheres_dev, int32_t n_spheres,
+                         const double* point_lights_dev, const rt_env* env,
+                         const rt_camera* cam, int32_t strip_rows, int32_t strip_first,
+                         int32_t strip_step, void* rgb_dev, int32_t rgb_dtype,
+                         int64_t plane_stride, uint8_t* rgba8_dev, uint64_t* stats_dev,
+                         void* stream);
+
+/*
  * rt_trace_rays_dev -- an arbitrary batch of n rays.
  * Replaces NumpyRenderer.raytrace_scene(ray_origin, normalized_ray_direction, scene)
  * (base.py:91-121) for callers that bring their own rays.

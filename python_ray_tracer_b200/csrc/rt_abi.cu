@@ -120,7 +120,9 @@ rt::CameraParams camera_params(const rt_camera* cam, int32_t row0, int32_t row1)
     cp.width = cam->width;
     cp.height = cam->height;
     cp.row0 = row0;
-    cp.row1 = row1;
+    cp.n_rows = row1 - row0;
+    cp.strip_rows = cp.n_rows > 0 ? cp.n_rows : 1;
+    cp.strip_step = 1;
     return cp;
 }
 
@@ -222,6 +224,25 @@ int rt_device_count(int* count_out) {
     return RT_OK;
 }
 
+namespace {
+int render_camera(int device, const double* spheres_dev, int32_t n_spheres, const double* point_lights_dev,
+                  const rt_env* env, const rt::CameraParams& cp, void* rgb_dev, int32_t rgb_dtype,
+                  int64_t plane_stride, uint8_t* rgba8_dev, uint64_t* stats_dev, void* stream) {
+    if (spheres_dev == nullptr || point_lights_dev == nullptr) return fail(RT_ERR_BAD_ARG, "scene pointers are NULL");
+    if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return fail(RT_ERR_BAD_ARG, "unknown rgb_dtype %d", rgb_dtype);
+    const int64_t n = (int64_t)cp.n_rows * cp.width;
+    if (rgb_dev != nullptr && plane_stride < n) return fail(RT_ERR_BAD_ARG, "plane_stride %lld < %lld pixels", (long long)plane_stride, (long long)n);
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    rt::OutputParams out = {rgb_dev, rgba8_dev, reinterpret_cast<unsigned long long*>(stats_dev), plane_stride,
+                            rgb_dtype == RT_DTYPE_F64};
+    cudaError_t err = launchers(env->mode).render_rows(stats_dev != nullptr, scene_params(spheres_dev, n_spheres, point_lights_dev, env),
+                                                      cp, out, static_cast<cudaStream_t>(stream));
+    if (err != cudaSuccess) return cuda_fail(err, "render_rows launch");
+    return RT_OK;
+}
+}  // namespace
+
 int rt_render_rows_dev(int device, const double* spheres_dev, int32_t n_spheres, const double* point_lights_dev,
                        const rt_env* env, const rt_camera* cam, int32_t row0, int32_t row1, void* rgb_dev,
                        int32_t rgb_dtype, int64_t plane_stride, uint8_t* rgba8_dev, uint64_t* stats_dev,
@@ -229,18 +250,36 @@ int rt_render_rows_dev(int device, const double* spheres_dev, int32_t n_spheres,
     int rc;
     if ((rc = check_env(env, n_spheres)) != RT_OK) return rc;
     if ((rc = check_camera(cam, row0, row1)) != RT_OK) return rc;
-    if (spheres_dev == nullptr || point_lights_dev == nullptr) return fail(RT_ERR_BAD_ARG, "scene pointers are NULL");
-    if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return fail(RT_ERR_BAD_ARG, "unknown rgb_dtype %d", rgb_dtype);
-    const int64_t n = (int64_t)(row1 - row0) * cam->width;
-    if (rgb_dev != nullptr && plane_stride < n) return fail(RT_ERR_BAD_ARG, "plane_stride %lld < %lld pixels", (long long)plane_stride, (long long)n);
-    DeviceScope scope(device);
-    if (scope.status != RT_OK) return scope.status;
-    rt::OutputParams out = {rgb_dev, rgba8_dev, reinterpret_cast<unsigned long long*>(stats_dev), plane_stride,
-                            rgb_dtype == RT_DTYPE_F64};
-    cudaError_t err = launchers(env->mode).render_rows(stats_dev != nullptr, scene_params(spheres_dev, n_spheres, point_lights_dev, env),
-                                                      camera_params(cam, row0, row1), out, static_cast<cudaStream_t>(stream));
-    if (err != cudaSuccess) return cuda_fail(err, "render_rows launch");
-    return RT_OK;
+    return render_camera(device, spheres_dev, n_spheres, point_lights_dev, env, camera_params(cam, row0, row1), rgb_dev,
+                         rgb_dtype, plane_stride, rgba8_dev, stats_dev, stream);
+}
+
+int64_t rt_strip_shard_rows(int32_t height, int32_t strip_rows, int32_t strip_first, int32_t strip_step) {
+    if (height <= 0 || strip_rows <= 0 || strip_first < 0 || strip_step <= 0) return -1;
+    int64_t rows = 0;
+    for (int64_t k = strip_first; k * strip_rows < height; k += strip_step) {
+        const int64_t left = (int64_t)height - k * strip_rows;
+        rows += left < strip_rows ? left : strip_rows;
+    }
+    return rows;
+}
+
+int rt_render_strips_dev(int device, const double* spheres_dev, int32_t n_spheres, const double* point_lights_dev,
+                         const rt_env* env, const rt_camera* cam, int32_t strip_rows, int32_t strip_first,
+                         int32_t strip_step, void* rgb_dev, int32_t rgb_dtype, int64_t plane_stride,
+                         uint8_t* rgba8_dev, uint64_t* stats_dev, void* stream) {
+    int rc;
+    if ((rc = check_env(env, n_spheres)) != RT_OK) return rc;
+    if ((rc = check_camera(cam, 0, cam != nullptr ? cam->height : 0)) != RT_OK) return rc;
+    if (strip_rows <= 0 || strip_step <= 0 || strip_first < 0 || strip_first >= strip_step)
+        return fail(RT_ERR_BAD_ARG, "strips: rows %d, first %d, step %d", strip_rows, strip_first, strip_step);
+    rt::CameraParams cp = camera_params(cam, 0, cam->height);
+    cp.row0 = strip_first * strip_rows;
+    cp.n_rows = (int)rt_strip_shard_rows(cam->height, strip_rows, strip_first, strip_step);
+    cp.strip_rows = strip_rows;
+    cp.strip_step = strip_step;
+    return render_camera(device, spheres_dev, n_spheres, point_lights_dev, env, cp, rgb_dev, rgb_dtype, plane_stride,
+                         rgba8_dev, stats_dev, stream);
 }
 
 int rt_trace_rays_dev(int device, const double* spheres_dev, int32_t n_spheres, const double* point_lights_dev,

@@ -63,8 +63,17 @@ struct CameraParams {
     double x_start, x_stop, x_step;  // np.linspace(-1, 1, W)
     double y_start, y_stop, y_step;  // np.linspace(1/a + .25, -1/a + .25, H)
     int width, height;
-    int row0, row1;
+    // Local row r of the launch (r in [0, n_rows)) is image row
+    //   row0 + r + (r / strip_rows) * (strip_step - 1) * strip_rows:
+    // a contiguous band has strip_step = 1; an interleaved shard owns every
+    // strip_step-th strip of strip_rows rows (a multiple of the patch height).
+    int row0, n_rows;
+    int strip_rows, strip_step;
 };
+__host__ __device__ inline int image_row(const CameraParams& cp, int local_row) {
+    return cp.strip_step == 1 ? cp.row0 + local_row
+                              : cp.row0 + local_row + (local_row / cp.strip_rows) * (cp.strip_step - 1) * cp.strip_rows;
+}
 
 // Explicit ray batch (base.py:91-96 called with arrays).
 struct RayBatch {

@@ -16,8 +16,13 @@ namespace rt {
 
 constexpr int kWarpTileW = 8;     // each warp renders 8x4 pixel patches: bounce coherence, and
 constexpr int kWarpTileH = 4;     // every row segment it stores is one full 32-byte sector
+// Two block shapes.  Small scenes: 128-thread blocks, RT_MIN_BLOCKS resident per SM, each
+// with its own copy of the (small) sphere table.  Scenes whose table would not fit that
+// many times in an SM's shared memory: one 640-thread block per SM sharing one copy, the
+// same 20 warps per SM.
 constexpr int kBlockThreads = 128;
-constexpr int kBlockWarps = kBlockThreads / 32;
+constexpr int kBigBlockThreads = 640;
+constexpr size_t kSmemPerSm = 227 * 1024;
 
 __host__ __device__ inline size_t staged_bytes(int n_spheres) {
     return (sizeof(SphereGeom) + sizeof(SpherePrimary) + sizeof(SphereAux)) * (size_t)n_spheres;
@@ -34,7 +39,7 @@ __host__ __device__ inline size_t staged_bytes(int n_spheres) {
 struct Tickets {
     unsigned int* counter;
     unsigned int n_tickets;      // items handed out dynamically
-    unsigned int n_warps;        // gridDim.x * kBlockWarps
+    unsigned int n_warps;        // gridDim.x * (block threads / 32)
     unsigned int static_rounds;  // items [0, static_rounds * n_warps) are dealt statically
 };
 __device__ __forceinline__ unsigned int draw_ticket(const Tickets& tk, int lane) {
@@ -107,29 +112,29 @@ __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p
     }
 }
 
-// Camera rows [row0,row1): ray generation + trace + stores, one thread per pixel of a
+// Camera rows of one band or interleaved shard (CameraParams): ray generation + trace + stores, one thread per pixel of a
 // patch.  Persistent: the grid is sized to the resident block slots of the GPU.
-template <int MODE, bool STATS>
-__global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_rows_kernel(SceneParams sp, CameraParams cp,
-                                                                   OutputParams out, Tickets tk) {
+template <int MODE, bool STATS, int BLOCK>
+__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS : 1)
+    render_rows_kernel(SceneParams sp, CameraParams cp, OutputParams out, Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
     const Staged st = stage_scene<MODE>(sp, smem, cp.cam);
 
     const int lane = threadIdx.x & 31;
     const int px = lane & (kWarpTileW - 1), py = lane >> 3;
     const unsigned int tiles_x = (unsigned int)(cp.width + kWarpTileW - 1) / kWarpTileW;
-    const unsigned int warp_id = blockIdx.x * kBlockWarps + (threadIdx.x >> 5);
+    const unsigned int warp_id = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
     const Vec3 eye = {cp.cam[0], cp.cam[1], cp.cam[2]};
     Counters k = {0, 0, 0, 0};
 
     auto render_patch = [&](unsigned int item) {
         const unsigned int ty = item / tiles_x, tx = item - ty * tiles_x;
-        const int row = cp.row0 + (int)ty * kWarpTileH + py;
+        const int local_row = (int)ty * kWarpTileH + py;
         const int col = (int)tx * kWarpTileW + px;
-        if (col < cp.width && row < cp.row1) {
-            Vec3 d = primary_direction<MODE>(cp, col, row);
+        if (col < cp.width && local_row < cp.n_rows) {
+            Vec3 d = primary_direction<MODE>(cp, col, image_row(cp, local_row));
             Vec3 c = trace_chain<MODE, STATS, true>(sp, st, eye, d, k);
-            store_pixel(out, (long long)(row - cp.row0) * cp.width + col, c);
+            store_pixel(out, (long long)local_row * cp.width + col, c);
         }
     };
 
@@ -147,13 +152,13 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_rows_kern
 }
 
 // Explicit ray batch, one thread per ray, same work distribution (an item = 32 rays).
-template <int MODE, bool STATS>
-__global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) trace_rays_kernel(SceneParams sp, RayBatch rb,
-                                                                  OutputParams out, Tickets tk) {
+template <int MODE, bool STATS, int BLOCK>
+__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS : 1)
+    trace_rays_kernel(SceneParams sp, RayBatch rb, OutputParams out, Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
     const Staged st = stage_scene<MODE>(sp, smem, sp.eye);
     const int lane = threadIdx.x & 31;
-    const unsigned int warp_id = blockIdx.x * kBlockWarps + (threadIdx.x >> 5);
+    const unsigned int warp_id = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
     Counters k = {0, 0, 0, 0};
 
     auto trace_item = [&](unsigned int item) {
@@ -199,10 +204,10 @@ __global__ void sphere_distance_kernel(RayBatch rb, SphereGeom g, double cc, dou
 // get_ray_directions (base.py:123-141) materialised as three planes.
 template <int MODE>
 __global__ void ray_directions_kernel(CameraParams cp, double* out, long long plane_stride) {
-    const long long n = (long long)(cp.row1 - cp.row0) * cp.width;
+    const long long n = (long long)cp.n_rows * cp.width;
     const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    const int row = cp.row0 + (int)(p / cp.width), col = (int)(p % cp.width);
+    const int row = image_row(cp, (int)(p / cp.width)), col = (int)(p % cp.width);
     Vec3 d = primary_direction<MODE>(cp, col, row);
     out[p] = d.x;
     out[plane_stride + p] = d.y;

@@ -11,10 +11,14 @@ namespace {
 constexpr int kMode = RT_TU_MODE;
 constexpr size_t kMaxDynamicSmem = 227 * 1024 - 64;  // per-block limit on sm_100a minus statics
 
+// One big block per SM once RT_MIN_BLOCKS private copies of the sphere table (plus the 1 KB
+// the driver reserves per block) no longer fit an SM's shared memory.
+inline bool big_blocks(int n_spheres) { return (staged_bytes(n_spheres) + 1024 + 16) * RT_MIN_BLOCKS > kSmemPerSm; }
+
 // Persistent launch shape: as many blocks as the device keeps resident for this kernel at
 // this shared-memory size, but no more than there are tickets to hand out.
 template <typename Kernel>
-cudaError_t persistent_grid(Kernel kernel, size_t smem, unsigned int n_tickets, unsigned int* grid_out) {
+cudaError_t persistent_grid(Kernel kernel, int block_threads, size_t smem, unsigned int n_tickets, unsigned int* grid_out) {
     if (smem > kMaxDynamicSmem) return cudaErrorInvalidValue;
     // the answer of the last query per host thread (kernels of one signature share this
     // function instance, so the kernel address is part of the key)
@@ -28,50 +32,60 @@ cudaError_t persistent_grid(Kernel kernel, size_t smem, unsigned int n_tickets, 
             return err;
         int sms = 0, per_sm = 0;
         if ((err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return err;
-        if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlockThreads, smem)) != cudaSuccess) return err;
+        if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block_threads, smem)) != cudaSuccess) return err;
         if (per_sm < 1) return cudaErrorLaunchOutOfResources;
         cached = {(const void*)kernel, device, smem, (unsigned int)sms * (unsigned int)per_sm};
     }
     const unsigned int slots = cached.slots;
-    const unsigned int wanted = (n_tickets + kBlockWarps - 1) / kBlockWarps;
+    const unsigned int block_warps = (unsigned int)block_threads / 32u;
+    const unsigned int wanted = (n_tickets + block_warps - 1) / block_warps;
     *grid_out = wanted < slots ? wanted : slots;
     return cudaSuccess;
 }
 
 template <typename Kernel, typename Work>
-cudaError_t launch_persistent(Kernel kernel, const SceneParams& sp, const Work& work, const OutputParams& out,
-                              unsigned long long n_items64, cudaStream_t stream) {
+cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParams& sp, const Work& work,
+                              const OutputParams& out, unsigned long long n_items64, cudaStream_t stream) {
     if (n_items64 > 0xfffffff0ull) return cudaErrorInvalidValue;
     const unsigned int n_items = (unsigned int)n_items64;
     const size_t smem = staged_bytes(sp.n_spheres);
     unsigned int grid = 0;
-    cudaError_t err = persistent_grid(kernel, smem, n_items, &grid);
+    cudaError_t err = persistent_grid(kernel, block_threads, smem, n_items, &grid);
     if (err != cudaSuccess) return err;
     Tickets tk;
     if ((err = ticket_counter(&tk.counter)) != cudaSuccess) return err;
-    tk.n_warps = grid * kBlockWarps;
+    tk.n_warps = grid * ((unsigned int)block_threads / 32u);
     tk.static_rounds = (unsigned int)((unsigned long long)n_items * RT_STATIC_PCT / 100ull / tk.n_warps);
     tk.n_tickets = n_items - tk.static_rounds * tk.n_warps;
-    kernel<<<grid, kBlockThreads, smem, stream>>>(sp, work, out, tk);
+    kernel<<<grid, block_threads, smem, stream>>>(sp, work, out, tk);
     return cudaGetLastError();
 }
 
 cudaError_t render_rows(bool stats, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
                         cudaStream_t stream) {
-    const int rows = cp.row1 - cp.row0;
+    const int rows = cp.n_rows;
     if (rows <= 0 || cp.width <= 0) return cudaSuccess;
     const unsigned long long tiles_x = (unsigned long long)(cp.width + kWarpTileW - 1) / kWarpTileW;
     const unsigned long long tiles_y = (unsigned long long)(rows + kWarpTileH - 1) / kWarpTileH;
-    if (stats) return launch_persistent(render_rows_kernel<kMode, true>, sp, cp, out, tiles_x * tiles_y, stream);
-    return launch_persistent(render_rows_kernel<kMode, false>, sp, cp, out, tiles_x * tiles_y, stream);
+    const unsigned long long n = tiles_x * tiles_y;
+    if (big_blocks(sp.n_spheres)) {
+        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads>, kBigBlockThreads, sp, cp, out, n, stream);
+        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads>, kBigBlockThreads, sp, cp, out, n, stream);
+    }
+    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads>, kBlockThreads, sp, cp, out, n, stream);
+    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads>, kBlockThreads, sp, cp, out, n, stream);
 }
 
 cudaError_t trace_rays(bool stats, const SceneParams& sp, const RayBatch& rb, const OutputParams& out,
                        cudaStream_t stream) {
     if (rb.n <= 0) return cudaSuccess;
     const unsigned long long n_items = ((unsigned long long)rb.n + 31ull) / 32ull;
-    if (stats) return launch_persistent(trace_rays_kernel<kMode, true>, sp, rb, out, n_items, stream);
-    return launch_persistent(trace_rays_kernel<kMode, false>, sp, rb, out, n_items, stream);
+    if (big_blocks(sp.n_spheres)) {
+        if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBigBlockThreads>, kBigBlockThreads, sp, rb, out, n_items, stream);
+        return launch_persistent(trace_rays_kernel<kMode, false, kBigBlockThreads>, kBigBlockThreads, sp, rb, out, n_items, stream);
+    }
+    if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBlockThreads>, kBlockThreads, sp, rb, out, n_items, stream);
+    return launch_persistent(trace_rays_kernel<kMode, false, kBlockThreads>, kBlockThreads, sp, rb, out, n_items, stream);
 }
 
 cudaError_t sphere_distance(const RayBatch& rb, const double* c, double radius, double* out,
@@ -85,7 +99,7 @@ cudaError_t sphere_distance(const RayBatch& rb, const double* c, double radius, 
 }
 
 cudaError_t ray_directions(const CameraParams& cp, double* out, long long plane_stride, cudaStream_t stream) {
-    const long long n = (long long)(cp.row1 - cp.row0) * cp.width;
+    const long long n = (long long)cp.n_rows * cp.width;
     if (n <= 0) return cudaSuccess;
     const unsigned int grid = (unsigned int)((n + 255) / 256);
     ray_directions_kernel<kMode><<<grid, 256, 0, stream>>>(cp, out, plane_stride);

@@ -105,6 +105,12 @@ PROTOTYPES = {
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), C.POINTER(RtCamera), C.c_int32, C.c_int32,
          _P, C.c_int32, C.c_int64, _P, _P, _P],
     ),
+    "rt_strip_shard_rows": (C.c_int64, [C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+    "rt_render_strips_dev": (
+        C.c_int,
+        [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), C.POINTER(RtCamera), C.c_int32, C.c_int32, C.c_int32,
+         _P, C.c_int32, C.c_int64, _P, _P, _P],
+    ),
     "rt_trace_rays_dev": (
         C.c_int,
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), _P, C.POINTER(C.c_double), _P, C.c_int64,

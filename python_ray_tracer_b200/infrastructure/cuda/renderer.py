@@ -268,6 +268,56 @@ class CudaRenderer(Renderer):
         )
         return DeviceColor(planes, rgba8, stats, self.device)
 
+    def render_strips(self, flat: FlatScene, camera: Camera, shard: Any, *, planes=None, rgba8=None,
+                      want_rgba8: bool = False) -> DeviceColor:
+        """Launch the camera-ray kernel for an interleaved shard of the frame
+        (``sharding.StripShard``: strips ``rank, rank + world, ...`` of ``strip_rows`` rows)
+        through ``rt_render_strips_dev``.  The result holds the shard's rows packed in strip
+        order.  Asynchronous on torch's current stream."""
+        torch = _require_cuda(self.device)
+        lib = abi.load()
+        dev = torch.device("cuda", self.device)
+        if int(camera.height) != shard.height:
+            raise ValueError(f"shard is for {shard.height} rows, camera has {camera.height}")
+        spheres, lights = self.upload_scene(flat)
+        rows = int(lib.rt_strip_shard_rows(int(camera.height), shard.strip_rows, shard.rank, shard.world))
+        if rows != shard.n_rows:
+            raise RuntimeError(f"host and library disagree on the shard size: {shard.n_rows} vs {rows}")
+        n = rows * int(camera.width)
+        if planes is None:
+            planes = torch.empty((3, n), dtype=self._torch_dtype(), device=dev)
+        if rgba8 is None and want_rgba8:
+            rgba8 = torch.empty((n, 4), dtype=torch.uint8, device=dev)
+        stats = self._new_stats()
+        env = self._env(flat)
+        cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
+        abi.check(
+            lib.rt_render_strips_dev(
+                self.device, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env), C.byref(cam),
+                shard.strip_rows, shard.rank, shard.world, planes.data_ptr(), self._abi_dtype(), max(planes.stride(0), 1),
+                None if rgba8 is None else rgba8.data_ptr(), None if stats is None else stats.data_ptr(),
+                self._stream(),
+            ),
+            "rt_render_strips_dev",
+        )
+        return DeviceColor(planes, rgba8, stats, self.device)
+
+    def render_frame_sharded(self, scene: Scene3D, rank: int, world: int, *, strip_rows: Optional[int] = None,
+                             dst: int = 0, group: Any = None):
+        """One frame over ``world`` ranks (one process per GPU, ``torch.distributed``
+        initialised by the caller): this rank renders its strips, the 8-bit shards are
+        gathered to rank ``dst``.  Returns the ``[height, width, 4]`` RGBA8 device tensor in
+        image order on ``dst`` and ``None`` elsewhere."""
+        from . import sharding
+
+        flat = self.flatten(scene)
+        camera = scene.camera
+        width = int(camera.width)
+        shard = sharding.StripShard(int(camera.height), world, rank, strip_rows or sharding.DEFAULT_STRIP_ROWS)
+        color = self.render_strips(flat, camera, shard, want_rgba8=True)
+        local = color.rgba8.view(shard.n_rows, width, 4)
+        return sharding.gather_frame(local, shard, dst=dst, group=group)
+
     def raytrace_scene(self, ray_origin: Any, normalized_ray_direction: Any, scene: Scene3D) -> DeviceColor:
         """Colour of every ray (``base.py:91-121`` with every ``NumpyShader.create`` it
         triggers, ``shader.py:63-112``)."""

@@ -1,0 +1,148 @@
+"""Multi-GPU sharding of the hot path: one process per GPU, ``torch.distributed`` plumbing.
+
+Pixels are independent in the reference (``base.py:102-119`` masks per pixel; a row band
+or any pixel subset renders bit-identically), so the path
+shards without a data-path collective.  Two partitions:
+
+* **one frame over G ranks** (BASELINE config 4): the image is cut into strips of
+  ``strip_rows`` rows and rank ``r`` renders strips ``r, r+G, r+2G, ...``
+  (``rt_render_strips_dev``).  Every shard is a stratified sample of the frame, so the
+  shards cost the same without a cost model (contiguous bands do not: the sky rows of the
+  README scene are nearly free).  The one exchange step is a gather of the shards to
+  rank 0 (``torch.distributed.gather``: NCCL over NVLink on GPUs, gloo in the CPU tests)
+  followed by a row permutation into image order.
+* **many frames over G ranks** (config 5, the turntable): frame ``k`` belongs to rank
+  ``k mod G``; no exchange at all.
+
+Nothing here computes pixels: the local render is a callable supplied by the caller
+(``CudaRenderer.render_strips`` in the product; the CPU tests plug in a stand-in).
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, Callable, List, Optional, Sequence
+
+import numpy as np
+
+DEFAULT_STRIP_ROWS = 16  # four 8x4 patches high: keeps warps of a block on adjacent rows
+
+
+@dataclass(frozen=True)
+class StripShard:
+    """Rows of a ``height``-row frame owned by ``rank`` of ``world`` (interleaved strips)."""
+
+    height: int
+    world: int
+    rank: int
+    strip_rows: int = DEFAULT_STRIP_ROWS
+
+    def __post_init__(self) -> None:
+        if self.height <= 0 or self.world <= 0 or self.strip_rows <= 0:
+            raise ValueError(f"bad shard {self}")
+        if not 0 <= self.rank < self.world:
+            raise ValueError(f"rank {self.rank} outside 0..{self.world - 1}")
+
+    @property
+    def image_rows(self) -> np.ndarray:
+        """Image row of every local row, in local order (what ``rt_render_strips_dev`` packs)."""
+        n_strips = -(-self.height // self.strip_rows)
+        mine = np.arange(self.rank, n_strips, self.world, dtype=np.int64)
+        rows = (mine[:, None] * self.strip_rows + np.arange(self.strip_rows, dtype=np.int64)[None, :]).reshape(-1)
+        return rows[rows < self.height]
+
+    @property
+    def n_rows(self) -> int:
+        return int(self.image_rows.size)
+
+
+def strip_shards(height: int, world: int, strip_rows: int = DEFAULT_STRIP_ROWS) -> List[StripShard]:
+    return [StripShard(height, world, r, strip_rows) for r in range(world)]
+
+
+def band_rows(height: int, world: int, rank: int, align: int = 4) -> tuple:
+    """Contiguous alternative: rows ``[row0, row1)`` of rank ``rank``, boundaries aligned to
+    the patch height (for callers that need contiguous bands, e.g. tiled image writers)."""
+    if not 0 <= rank < world:
+        raise ValueError(f"rank {rank} outside 0..{world - 1}")
+    units = -(-height // align)
+    lo = (units * rank // world) * align
+    hi = (units * (rank + 1) // world) * align
+    return min(lo, height), min(hi, height)
+
+
+def frames_of_rank(n_frames: int, world: int, rank: int) -> range:
+    """Frame-sharding of an animation batch: frame ``k`` is rendered by rank ``k mod world``."""
+    if not 0 <= rank < world:
+        raise ValueError(f"rank {rank} outside 0..{world - 1}")
+    return range(rank, n_frames, world)
+
+
+def image_order(height: int, world: int, strip_rows: int = DEFAULT_STRIP_ROWS) -> np.ndarray:
+    """Index ``idx`` such that ``gathered.reshape(world * max_rows, ...)[idx]`` is the frame in
+    image row order, where ``gathered[r, :n_r]`` holds rank ``r``'s packed shard and every
+    rank's block is padded to ``max_rows`` rows."""
+    shards = strip_shards(height, world, strip_rows)
+    max_rows = max(s.n_rows for s in shards)
+    idx = np.empty(height, dtype=np.int64)
+    for s in shards:
+        idx[s.image_rows] = s.rank * max_rows + np.arange(s.n_rows, dtype=np.int64)
+    return idx
+
+
+def gather_frame(local: Any, shard: StripShard, dst: int = 0, group: Any = None) -> Optional[Any]:
+    """Gather the packed shards (``local``: tensor ``[shard.n_rows, ...]``) to rank ``dst``
+    and return the frame in image row order there (``None`` on the other ranks).
+
+    ``torch.distributed.gather`` needs equal shapes, so each rank pads its block to the
+    largest shard (they differ by at most ``strip_rows`` rows).
+    """
+    import torch
+    import torch.distributed as dist
+
+    if local.shape[0] != shard.n_rows:
+        raise ValueError(f"local block has {local.shape[0]} rows, shard owns {shard.n_rows}")
+    world = shard.world
+    if world == 1:
+        return local
+    max_rows = max(s.n_rows for s in strip_shards(shard.height, world, shard.strip_rows))
+    block = local
+    if local.shape[0] != max_rows:
+        block = local.new_zeros((max_rows,) + tuple(local.shape[1:]))
+        block[: shard.n_rows] = local
+    block = block.contiguous()
+    if shard.rank != dst:
+        dist.gather(block, None, dst=dst, group=group)
+        return None
+    gathered = local.new_empty((world, max_rows) + tuple(local.shape[1:]))
+    dist.gather(block, list(gathered.unbind(0)), dst=dst, group=group)
+    order = torch.from_numpy(image_order(shard.height, world, shard.strip_rows)).to(local.device)
+    return gathered.reshape((world * max_rows,) + tuple(local.shape[1:])).index_select(0, order)
+
+
+def render_frame_sharded(render_local: Callable[[StripShard], Any], height: int, rank: int, world: int,
+                         strip_rows: int = DEFAULT_STRIP_ROWS, dst: int = 0, group: Any = None) -> Optional[Any]:
+    """One frame over ``world`` ranks: ``render_local(shard)`` returns this rank's packed rows
+    (``[shard.n_rows, ...]``); the assembled frame comes back on rank ``dst``."""
+    shard = StripShard(height, world, rank, strip_rows)
+    return gather_frame(render_local(shard), shard, dst=dst, group=group)
+
+
+def render_frames_sharded(render_frame: Callable[[int], Any], n_frames: int, rank: int, world: int) -> dict:
+    """An animation batch over ``world`` ranks: calls ``render_frame(k)`` for this rank's
+    frames and returns ``{k: result}``; nothing is exchanged."""
+    return {k: render_frame(k) for k in frames_of_rank(n_frames, world, rank)}
+
+
+def covered_exactly_once(height: int, world: int, strip_rows: int = DEFAULT_STRIP_ROWS) -> bool:
+    """Partition check used by the tests and by ``bench.py`` before timing."""
+    seen = np.zeros(height, dtype=np.int64)
+    for s in strip_shards(height, world, strip_rows):
+        seen[s.image_rows] += 1
+    return bool((seen == 1).all())
+
+
+__all__: Sequence[str] = (
+    "DEFAULT_STRIP_ROWS", "StripShard", "strip_shards", "band_rows", "frames_of_rank", "image_order",
+    "gather_frame", "render_frame_sharded", "render_frames_sharded", "covered_exactly_once",
+)

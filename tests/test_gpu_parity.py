@@ -285,3 +285,34 @@ def test_quantize_kernel_bit_exact(rt, c_oracle):
     assert np.array_equal(got, c_oracle.quantize(v))
     got4 = renderer.quantize(NumpyRGBColor(v[0], v[1], v[2]), 4).cpu().numpy()
     assert np.array_equal(got4[:, :3], got) and (got4[:, 3] == 255).all()
+
+
+def test_strip_shards_reassemble_to_the_full_frame(rt):
+    """Multi-GPU partition on one GPU: every rank's interleaved shard (rt_render_strips_dev)
+    is rendered in turn and permuted back with the host's image_order(); the result is
+    bit-identical to the single-launch frame (pixels are independent)."""
+    from python_ray_tracer_b200.infrastructure.cuda import sharding
+
+    for name, world, strip_rows in (("readme_160x90", 3, 4), ("c2_readme_1080p_subset", 8, 16),
+                                    ("readme_37x23", 2, 16), ("readme_1x7", 4, 4)):
+        case = load_case(name)
+        for precision in PRECISIONS:
+            renderer = rt(precision)
+            cam = _camera(case)
+            full = _render(renderer, case)
+            want, want8 = full.numpy(), full.rgba8.cpu().numpy()
+            w, h = case.width, case.height
+            shards = sharding.strip_shards(h, world, strip_rows)
+            max_rows = max(s.n_rows for s in shards)
+            stacked = np.zeros((world * max_rows, w, 3))
+            stacked8 = np.zeros((world * max_rows, w, 4), dtype=np.uint8)
+            traced = 0
+            for s in shards:
+                color = renderer.render_strips(case.flat, cam, s, want_rgba8=True)
+                stacked[s.rank * max_rows:s.rank * max_rows + s.n_rows] = color.numpy().T.reshape(s.n_rows, w, 3)
+                stacked8[s.rank * max_rows:s.rank * max_rows + s.n_rows] = color.rgba8.cpu().numpy().reshape(s.n_rows, w, 4)
+                traced += color.counters()["rays_traced"]
+            order = sharding.image_order(h, world, strip_rows)
+            assert np.array_equal(stacked[order].reshape(-1, 3).T, want), (name, precision)
+            assert np.array_equal(stacked8[order].reshape(-1, 4), want8)
+            assert traced == full.counters()["rays_traced"]
