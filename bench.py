@@ -76,7 +76,7 @@ class ClockSampler(threading.Thread):
 
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index: int, period: float = 0.01) -> None:
+    def __init__(self, index: int, period: float = 0.002) -> None:
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
@@ -221,7 +221,7 @@ def run_b200_arm(args) -> None:
     import torch
     import torch.distributed as dist
 
-    from python_ray_tracer_b200.infrastructure.cuda import abi
+    from python_ray_tracer_b200.infrastructure.cuda import abi, sharding
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -241,8 +241,11 @@ def run_b200_arm(args) -> None:
     total = args.warmup + args.steps
     frames = [workload(args.workload, rank, s, world) for s in range(total)]
     label, _, width, height, max_depth = frames[0]
-    row0, row1 = (rank * height // world, (rank + 1) * height // world) if banded else (0, height)
-    n = (row1 - row0) * width
+    # one frame over all ranks: interleaved strips (sharding.StripShard) for the device path,
+    # contiguous bands for the host-buffer path
+    shard = sharding.StripShard(height, world, rank) if banded else None
+    row0, row1 = sharding.band_rows(height, world, rank) if banded else (0, height)
+    n = shard.n_rows * width if banded else (row1 - row0) * width
     cam = abi.make_camera(frames[0][1].eye, width, height)
 
     # scene tables of every step resident in HBM before the timed region
@@ -254,17 +257,22 @@ def run_b200_arm(args) -> None:
     planes = torch.empty((3, n), dtype=torch.float32, device=dev)
     rgba8 = torch.empty((n, 4), dtype=torch.uint8, device=dev)
     stats = torch.zeros(4, dtype=torch.int64, device=dev)
-    gathered = torch.empty((world, n, 4), dtype=torch.uint8, device=dev) if banded and rank == 0 else None
     flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def launch(step: int, with_stats: bool = False) -> None:
         spheres, lights, env, flat = tables[step]
-        abi.check(lib.rt_render_rows_dev(local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
-                                         C.byref(cam), row0, row1, planes.data_ptr(), abi.RT_DTYPE_F32, n,
-                                         rgba8.data_ptr(), stats.data_ptr() if with_stats else None, sptr),
-                  "rt_render_rows_dev")
-        if banded:  # the one exchange step of the path: row bands -> rank 0 (8-bit image)
-            dist.gather(rgba8, list(gathered.unbind(0)) if rank == 0 else None, dst=0)
+        if banded:
+            abi.check(lib.rt_render_strips_dev(local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
+                                               C.byref(cam), shard.strip_rows, rank, world, planes.data_ptr(),
+                                               abi.RT_DTYPE_F32, n, rgba8.data_ptr(),
+                                               stats.data_ptr() if with_stats else None, sptr), "rt_render_strips_dev")
+            # the one exchange step of the path: 8-bit shards -> rank 0, permuted to image order
+            sharding.gather_frame(rgba8.view(shard.n_rows, width, 4), shard, dst=0)
+        else:
+            abi.check(lib.rt_render_rows_dev(local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
+                                             C.byref(cam), row0, row1, planes.data_ptr(), abi.RT_DTYPE_F32, n,
+                                             rgba8.data_ptr(), stats.data_ptr() if with_stats else None, sptr),
+                      "rt_render_rows_dev")
 
     def barrier() -> None:
         if world > 1:
@@ -304,25 +312,35 @@ def run_b200_arm(args) -> None:
     traced, hits, deepest, tests = (int(v) for v in stats.cpu().tolist())
     flop = tests * FLOP_PER_SPHERE_TEST + hits * FLOP_PER_HIT
 
-    # ---- end to end through the host-buffer C-ABI entry point, pinned host outputs
-    rgb_host = torch.empty((3, n), dtype=torch.float32).pin_memory()
-    rgb8_host = torch.empty((n, 3), dtype=torch.uint8).pin_memory()
-    e2e_times = []
-    for s in range(total):
-        _, _, env, flat = tables[s]
-        t0 = time.perf_counter()
-        abi.check(lib.rt_render_frame_host(local, flat.spheres.ctypes.data, flat.n_spheres, flat.point_lights.ctypes.data,
-                                           C.byref(env), C.byref(cam), row0, row1, rgb_host.data_ptr(), abi.RT_DTYPE_F32,
-                                           rgb8_host.data_ptr(), None), "rt_render_frame_host")
-        checksum = float(rgb_host[0, n // 2])  # the result is read on the host inside the timed region
-        if s >= args.warmup:
-            e2e_times.append(time.perf_counter() - t0)
-    e2e_ms = torch.tensor([float(np.mean(e2e_times)) * 1e3], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
-    e2e_value = pixels_per_step / (float(e2e_ms.item()) * 1e-3) / 1e6
+    # ---- end to end through the host-buffer C-ABI entry point, pinned host outputs.
+    # The step's result is what raytrace_scene returns: the linear RGB planes.  A second
+    # pass also brings back the 8-bit image save_image would write (reported beside it).
+    n_host = (row1 - row0) * width  # host path: this rank's contiguous band
+    rgb_host = torch.empty((3, n_host), dtype=torch.float32).pin_memory()
+    rgb8_host = torch.empty((n_host, 3), dtype=torch.uint8).pin_memory()
+
+    def e2e_pass(with_rgb8: bool) -> float:
+        times = []
+        for s in range(total):
+            _, _, env, flat = tables[s]
+            t0 = time.perf_counter()
+            abi.check(lib.rt_render_frame_host(local, flat.spheres.ctypes.data, flat.n_spheres, flat.point_lights.ctypes.data,
+                                               C.byref(env), C.byref(cam), row0, row1, rgb_host.data_ptr(), abi.RT_DTYPE_F32,
+                                               rgb8_host.data_ptr() if with_rgb8 else None, None), "rt_render_frame_host")
+            _ = float(rgb_host[0, n_host // 2]) + float(rgb_host[2, n_host - 1])  # the result is read on the host inside the timed region
+            if s >= args.warmup:
+                times.append(time.perf_counter() - t0)
+        ms = torch.tensor([float(np.mean(times)) * 1e3], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    e2e_ms_value = e2e_pass(False)
+    e2e_rgb8_ms = e2e_pass(True)
+    e2e_value = pixels_per_step / (e2e_ms_value * 1e-3) / 1e6
+    flat = tables[-1][3]
     h2d = flat.spheres.nbytes + flat.point_lights.nbytes
-    d2h = rgb_host.numel() * 4 + rgb8_host.numel()
+    d2h = rgb_host.numel() * 4
 
     if rank != 0:
         if world > 1:
@@ -350,10 +368,13 @@ def run_b200_arm(args) -> None:
         "config": {"workload": label, "width": width, "height": height, "spheres": frames[0][1].n_spheres,
                    "max_depth": max_depth or None, "precision": args.precision, "cutoff": args.cutoff,
                    "output": "planar f32 linear RGB + RGBA8 (fused quantisation)",
-                   "parallelism": ("row-band x%d + NCCL gather of RGBA8 to rank 0" % world) if banded else ("frame-sharded x%d, no collective" % world),
+                   "parallelism": ("interleaved 16-row strips x%d + NCCL gather of RGBA8 to rank 0 + row permutation" % world) if banded else ("frame-sharded x%d, no collective" % world),
                    "l2": "512 MiB buffer written between timed steps (L2 flush); each step timed by its own CUDA event pair"},
-        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": float(e2e_ms.item()), "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "api": "rt_render_frame_host (scene upload + kernel + quantise + D2H of f32 planes and RGB8 into pinned host memory)"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_value, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h,
+                "api": "rt_render_frame_host: scene upload + kernel + D2H of the f32 linear planes into pinned host memory, row chunks pipelined (kernel of chunk i+1 under the copy of chunk i)",
+                "with_rgb8": {"ms_per_step": e2e_rgb8_ms, "value": pixels_per_step / (e2e_rgb8_ms * 1e-3) / 1e6,
+                              "d2h_bytes_per_step": d2h + rgb8_host.numel()}},
         "gpu_launches": args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
@@ -377,7 +398,7 @@ def run_b200_arm(args) -> None:
 def main() -> None:
     parser = argparse.ArgumentParser()
     parser.add_argument("--gpus", type=int, default=1)
-    parser.add_argument("--steps", type=int, default=100)
+    parser.add_argument("--steps", type=int, default=200)
     parser.add_argument("--warmup", type=int, default=5)
     parser.add_argument("--impl", choices=["b200", "reference"], default="b200")
     parser.add_argument("--workload", default="c2")

@@ -21,8 +21,12 @@ struct Scratch {
     size_t bytes = 0;
 };
 
+constexpr int kMaxChunks = 8;
+
 struct DeviceCache {
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;       // uploads and kernels
+    cudaStream_t copy_stream = nullptr;  // downloads, overlapped with the next chunk's kernel
+    cudaEvent_t rendered[kMaxChunks] = {};
     Scratch scene, rays, rgb, rgb8, stats;
 };
 
@@ -91,7 +95,11 @@ int enter(int device, Restore& restore, DeviceCache** cache) {
     cudaGetDevice(&restore.previous);
     HOST_CUDA(cudaSetDevice(device));
     DeviceCache& c = g_cache[device];
-    if (c.stream == nullptr) HOST_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    if (c.stream == nullptr) {
+        HOST_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+        HOST_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < kMaxChunks; ++i) HOST_CUDA(cudaEventCreateWithFlags(&c.rendered[i], cudaEventDisableTiming));
+    }
     *cache = &c;
     return RT_OK;
 }
@@ -115,8 +123,13 @@ int rt_release_cache(void) {
         release(c.rgb);
         release(c.rgb8);
         release(c.stats);
-        if (c.stream != nullptr) cudaStreamDestroy(c.stream);
+        if (c.stream != nullptr) {
+            cudaStreamDestroy(c.stream);
+            cudaStreamDestroy(c.copy_stream);
+            for (int i = 0; i < kMaxChunks; ++i) cudaEventDestroy(c.rendered[i]);
+        }
         c.stream = nullptr;
+        c.copy_stream = nullptr;
     }
     return RT_OK;
 }
@@ -144,16 +157,43 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
         HOST_CUDA(reserve(c->stats, sizeof(uint64_t) * RT_STATS_WORDS));
         HOST_CUDA(cudaMemsetAsync(c->stats.ptr, 0, sizeof(uint64_t) * RT_STATS_WORDS, c->stream));
     }
-    rc = rt_render_rows_dev(device, spheres_dev, n_spheres, lights_dev, env, cam, row0, row1, c->rgb.ptr, rgb_dtype, n,
-                            nullptr, stats_host != nullptr ? static_cast<uint64_t*>(c->stats.ptr) : nullptr, c->stream);
-    if (rc != RT_OK) return rc;
-    if (rgb_host != nullptr && n > 0)
-        HOST_CUDA(cudaMemcpyAsync(rgb_host, c->rgb.ptr, (size_t)n * 3 * elem, cudaMemcpyDeviceToHost, c->stream));
-    if (rgb8_host != nullptr && n > 0) {
-        rc = rt_quantize_dev(device, c->rgb.ptr, rgb_dtype, n, n, static_cast<uint8_t*>(c->rgb8.ptr), 3, c->stream);
+    // Frames are rendered in row chunks: while chunk i is copied to the host (copy engine,
+    // copy_stream) the kernel of chunk i+1 runs.  The copies are the longer leg (PCIe), so
+    // the frame costs about one chunk's kernel plus the copy time.  Small frames: one chunk.
+    const int rows = row1 - row0;
+    int chunks = 1;
+    if (n >= (int64_t)1 << 20) chunks = 4;
+    if (n >= (int64_t)1 << 23) chunks = kMaxChunks;
+    if (chunks > rows) chunks = rows > 0 ? rows : 1;
+    char* rgb_base = static_cast<char*>(c->rgb.ptr);
+    uint64_t* stats_dev = stats_host != nullptr ? static_cast<uint64_t*>(c->stats.ptr) : nullptr;
+    for (int i = 0; i < chunks && n > 0; ++i) {
+        // chunk boundaries on multiples of 4 rows (the patch height)
+        const int r0 = row0 + (int)(((int64_t)rows * i / chunks) & ~3LL);
+        const int r1 = i + 1 == chunks ? row1 : row0 + (int)(((int64_t)rows * (i + 1) / chunks) & ~3LL);
+        if (r1 <= r0) continue;
+        const int64_t first = (int64_t)(r0 - row0) * cam->width, count = (int64_t)(r1 - r0) * cam->width;
+        rc = rt_render_rows_dev(device, spheres_dev, n_spheres, lights_dev, env, cam, r0, r1, rgb_base + first * elem,
+                                rgb_dtype, n, nullptr, stats_dev, c->stream);
         if (rc != RT_OK) return rc;
-        HOST_CUDA(cudaMemcpyAsync(rgb8_host, c->rgb8.ptr, (size_t)n * 3, cudaMemcpyDeviceToHost, c->stream));
+        if (rgb8_host != nullptr) {
+            rc = rt_quantize_dev(device, rgb_base + first * elem, rgb_dtype, n, count,
+                                 static_cast<uint8_t*>(c->rgb8.ptr) + first * 3, 3, c->stream);
+            if (rc != RT_OK) return rc;
+        }
+        HOST_CUDA(cudaEventRecord(c->rendered[i], c->stream));
+        HOST_CUDA(cudaStreamWaitEvent(c->copy_stream, c->rendered[i], 0));
+        if (rgb_host != nullptr) {
+            for (int ch = 0; ch < 3; ++ch)
+                HOST_CUDA(cudaMemcpyAsync(static_cast<char*>(rgb_host) + ((size_t)ch * n + first) * elem,
+                                          rgb_base + ((size_t)ch * n + first) * elem, (size_t)count * elem,
+                                          cudaMemcpyDeviceToHost, c->copy_stream));
+        }
+        if (rgb8_host != nullptr)
+            HOST_CUDA(cudaMemcpyAsync(rgb8_host + first * 3, static_cast<uint8_t*>(c->rgb8.ptr) + first * 3,
+                                      (size_t)count * 3, cudaMemcpyDeviceToHost, c->copy_stream));
     }
+    HOST_CUDA(cudaStreamSynchronize(c->copy_stream));
     if (stats_host != nullptr)
         HOST_CUDA(cudaMemcpyAsync(stats_host, c->stats.ptr, sizeof(uint64_t) * RT_STATS_WORDS, cudaMemcpyDeviceToHost, c->stream));
     HOST_CUDA(cudaStreamSynchronize(c->stream));
