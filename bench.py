@@ -258,10 +258,24 @@ def run_b200_arm(args) -> None:
     rgba8 = torch.empty((n, 4), dtype=torch.uint8, device=dev)
     stats = torch.zeros(4, dtype=torch.int64, device=dev)
     flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    peer = None
+    if banded and args.exchange == "peer":
+        # rank 0 owns the whole-frame RGBA8 buffer; the other ranks map it and their kernels
+        # store into it over NVLink while they render (no gather, no permutation)
+        peer = sharding.PeerFrame(height, width, rank, world, local, dst=0)
+        env_flags = abi.RT_FLAG_IMAGE_ORDER
+        for i, (sph, lig, env, flat_) in enumerate(tables):
+            env.flags |= env_flags
 
     def launch(step: int, with_stats: bool = False) -> None:
         spheres, lights, env, flat = tables[step]
-        if banded:
+        if peer is not None:
+            # the exchange step is inside the kernel: stores go to rank 0's framebuffer
+            abi.check(lib.rt_render_strips_dev(local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
+                                               C.byref(cam), shard.strip_rows, rank, world, None, abi.RT_DTYPE_F32, 0,
+                                               peer.ptr, stats.data_ptr() if with_stats else None, sptr),
+                      "rt_render_strips_dev")
+        elif banded:
             abi.check(lib.rt_render_strips_dev(local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
                                                C.byref(cam), shard.strip_rows, rank, world, planes.data_ptr(),
                                                abi.RT_DTYPE_F32, n, rgba8.data_ptr(),
@@ -315,6 +329,12 @@ def run_b200_arm(args) -> None:
     # ---- end to end through the host-buffer C-ABI entry point, pinned host outputs.
     # The step's result is what raytrace_scene returns: the linear RGB planes.  A second
     # pass also brings back the 8-bit image save_image would write (reported beside it).
+    if peer is not None:
+        torch.cuda.synchronize(local)
+        peer.close()
+        peer = None
+        for _, _, env, _ in tables:
+            env.flags &= ~abi.RT_FLAG_IMAGE_ORDER
     n_host = (row1 - row0) * width  # host path: this rank's contiguous band
     rgb_host = torch.empty((3, n_host), dtype=torch.float32).pin_memory()
     rgb8_host = torch.empty((n_host, 3), dtype=torch.uint8).pin_memory()
@@ -368,7 +388,8 @@ def run_b200_arm(args) -> None:
         "config": {"workload": label, "width": width, "height": height, "spheres": frames[0][1].n_spheres,
                    "max_depth": max_depth or None, "precision": args.precision, "cutoff": args.cutoff,
                    "output": "planar f32 linear RGB + RGBA8 (fused quantisation)",
-                   "parallelism": ("interleaved 16-row strips x%d + NCCL gather of RGBA8 to rank 0 + row permutation" % world) if banded else ("frame-sharded x%d, no collective" % world),
+                   "parallelism": (("interleaved 16-row strips x%d, kernels store RGBA8 into rank 0's framebuffer over NVLink peer memory (no gather)" % world)
+                                   if args.exchange == "peer" else ("interleaved 16-row strips x%d + NCCL gather of RGBA8 to rank 0 + row permutation" % world)) if banded else ("frame-sharded x%d, no collective" % world),
                    "l2": "512 MiB buffer written between timed steps (L2 flush); each step timed by its own CUDA event pair"},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_value, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h,
@@ -405,6 +426,9 @@ def main() -> None:
     parser.add_argument("--precision", choices=["fast", "exact"], default="fast")
     parser.add_argument("--cutoff", type=float, default=1e-7)
     parser.add_argument("--no-cpu-baseline", action="store_true")
+    parser.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
+                        help="c4 with N > 1: kernels store into rank 0's framebuffer over NVLink (peer) or "
+                             "render locally and gather with NCCL (nccl)")
     args = parser.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -100,9 +100,17 @@ typedef enum rt_mode {
 
 typedef enum rt_flags {
     RT_FLAG_NONE = 0,
-    RT_FLAG_ALL_POINT_LIGHTS = 1 /* extension (main.py:45 TODO): sum diffuse/specular and
+    RT_FLAG_ALL_POINT_LIGHTS = 1, /* extension (main.py:45 TODO): sum diffuse/specular and
                                     shadow over every point light.  Off = reference
                                     semantics: only lights[0] shades (shader.py:75).     */
+    RT_FLAG_IMAGE_ORDER = 2       /* rt_render_rows_dev / rt_render_strips_dev: rgb_dev and
+                                    rgba8_dev are WHOLE frames (height x width) and every
+                                    pixel is stored at row*width + col, whatever rows the
+                                    call renders.  The buffers may be peer memory of
+                                    another GPU (rt_peer_buffer_open): the shards of a
+                                    frame are then written straight into rank 0's
+                                    framebuffer over NVLink while the kernel runs, and no
+                                    gather follows.                                       */
 } rt_flags;
 
 /* Camera(position, width, height) (domain.py:14-23). */
@@ -172,6 +180,23 @@ int rt_render_strips_dev(int device, const double* spheres_dev, int32_t n_sphere
                          int32_t strip_step, void* rgb_dev, int32_t rgb_dtype,
                          int64_t plane_stride, uint8_t* rgba8_dev, uint64_t* stats_dev,
                          void* stream);
+
+/*
+ * Peer framebuffers (one process per GPU): the owner creates a device buffer and gets a
+ * 64-byte handle to send to the other processes of the node (any byte transport, e.g.
+ * torch.distributed.broadcast_object_list); they open it and pass the pointer as
+ * rgb_dev / rgba8_dev of a render call with RT_FLAG_IMAGE_ORDER.  Nothing in the
+ * reference corresponds to this (it is single-process); it is the
+ * exchange step of the row-band sharding of BASELINE config 4.
+ *   create   cudaMalloc + zero + export; the owner frees with rt_peer_buffer_destroy
+ *   open     map the owner's buffer into this process (peer access over NVLink/PCIe);
+ *            a process cannot open its own handle
+ */
+#define RT_IPC_HANDLE_BYTES 64
+int rt_peer_buffer_create(int device, uint64_t bytes, void** ptr_out, uint8_t* handle_out);
+int rt_peer_buffer_open(int device, const uint8_t* handle_in, void** ptr_out);
+int rt_peer_buffer_close(int device, void* ptr);
+int rt_peer_buffer_destroy(int device, void* ptr);
 
 /*
  * rt_trace_rays_dev -- an arbitrary batch of n rays.

@@ -230,12 +230,13 @@ int render_camera(int device, const double* spheres_dev, int32_t n_spheres, cons
                   int64_t plane_stride, uint8_t* rgba8_dev, uint64_t* stats_dev, void* stream) {
     if (spheres_dev == nullptr || point_lights_dev == nullptr) return fail(RT_ERR_BAD_ARG, "scene pointers are NULL");
     if (rgb_dtype != RT_DTYPE_F32 && rgb_dtype != RT_DTYPE_F64) return fail(RT_ERR_BAD_ARG, "unknown rgb_dtype %d", rgb_dtype);
-    const int64_t n = (int64_t)cp.n_rows * cp.width;
+    const bool image_order = (env->flags & RT_FLAG_IMAGE_ORDER) != 0;
+    const int64_t n = image_order ? (int64_t)cp.height * cp.width : (int64_t)cp.n_rows * cp.width;
     if (rgb_dev != nullptr && plane_stride < n) return fail(RT_ERR_BAD_ARG, "plane_stride %lld < %lld pixels", (long long)plane_stride, (long long)n);
     DeviceScope scope(device);
     if (scope.status != RT_OK) return scope.status;
     rt::OutputParams out = {rgb_dev, rgba8_dev, reinterpret_cast<unsigned long long*>(stats_dev), plane_stride,
-                            rgb_dtype == RT_DTYPE_F64};
+                            rgb_dtype == RT_DTYPE_F64, image_order ? 1 : 0};
     cudaError_t err = launchers(env->mode).render_rows(stats_dev != nullptr, scene_params(spheres_dev, n_spheres, point_lights_dev, env),
                                                       cp, out, static_cast<cudaStream_t>(stream));
     if (err != cudaSuccess) return cuda_fail(err, "render_rows launch");
@@ -282,6 +283,51 @@ int rt_render_strips_dev(int device, const double* spheres_dev, int32_t n_sphere
                          rgba8_dev, stats_dev, stream);
 }
 
+int rt_peer_buffer_create(int device, uint64_t bytes, void** ptr_out, uint8_t* handle_out) {
+    if (ptr_out == nullptr || handle_out == nullptr || bytes == 0) return fail(RT_ERR_BAD_ARG, "peer buffer: NULL pointer or zero size");
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "RT_IPC_HANDLE_BYTES must equal the CUDA IPC handle size");
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    void* p = nullptr;
+    RT_CUDA(cudaMalloc(&p, bytes));
+    cudaIpcMemHandle_t handle;
+    cudaError_t err = cudaMemset(p, 0, bytes);
+    if (err == cudaSuccess) err = cudaIpcGetMemHandle(&handle, p);
+    if (err != cudaSuccess) {
+        cudaFree(p);
+        return cuda_fail(err, "peer buffer create");
+    }
+    memcpy(handle_out, &handle, sizeof(handle));
+    *ptr_out = p;
+    return RT_OK;
+}
+
+int rt_peer_buffer_open(int device, const uint8_t* handle_in, void** ptr_out) {
+    if (ptr_out == nullptr || handle_in == nullptr) return fail(RT_ERR_BAD_ARG, "peer buffer: NULL pointer");
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    cudaIpcMemHandle_t handle;
+    memcpy(&handle, handle_in, sizeof(handle));
+    RT_CUDA(cudaIpcOpenMemHandle(ptr_out, handle, cudaIpcMemLazyEnablePeerAccess));
+    return RT_OK;
+}
+
+int rt_peer_buffer_close(int device, void* ptr) {
+    if (ptr == nullptr) return RT_OK;
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    RT_CUDA(cudaIpcCloseMemHandle(ptr));
+    return RT_OK;
+}
+
+int rt_peer_buffer_destroy(int device, void* ptr) {
+    if (ptr == nullptr) return RT_OK;
+    DeviceScope scope(device);
+    if (scope.status != RT_OK) return scope.status;
+    RT_CUDA(cudaFree(ptr));
+    return RT_OK;
+}
+
 int rt_trace_rays_dev(int device, const double* spheres_dev, int32_t n_spheres, const double* point_lights_dev,
                       const rt_env* env, const double* origins_dev, const double* origin0,
                       const double* directions_dev, int64_t n_rays, void* rgb_dev, int32_t rgb_dtype,
@@ -303,7 +349,7 @@ int rt_trace_rays_dev(int device, const double* spheres_dev, int32_t n_spheres, 
     for (int i = 0; i < 3; ++i) rb.origin0[i] = origin0 != nullptr ? origin0[i] : 0.0;
     rb.n = n_rays;
     rt::OutputParams out = {rgb_dev, nullptr, reinterpret_cast<unsigned long long*>(stats_dev), plane_stride,
-                            rgb_dtype == RT_DTYPE_F64};
+                            rgb_dtype == RT_DTYPE_F64, 0};
     cudaError_t err = launchers(env->mode).trace_rays(stats_dev != nullptr, scene_params(spheres_dev, n_spheres, point_lights_dev, env), rb,
                                                      out, static_cast<cudaStream_t>(stream));
     if (err != cudaSuccess) return cuda_fail(err, "trace_rays launch");

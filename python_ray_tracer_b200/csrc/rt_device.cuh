@@ -89,6 +89,9 @@ struct OutputParams {
     unsigned long long* stats;
     long long plane_stride;
     int rgb_is_f64;
+    int image_order;      // camera kernel: index outputs by image pixel (row*W + col) instead of
+                          // the shard's packed order -- the buffers are whole frames, possibly
+                          // peer memory of another GPU (RT_FLAG_IMAGE_ORDER)
 };
 
 // Per-sphere records staged in shared memory.  Reads are warp-uniform (every lane tests

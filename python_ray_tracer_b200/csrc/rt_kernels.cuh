@@ -132,9 +132,10 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
         const int local_row = (int)ty * kWarpTileH + py;
         const int col = (int)tx * kWarpTileW + px;
         if (col < cp.width && local_row < cp.n_rows) {
-            Vec3 d = primary_direction<MODE>(cp, col, image_row(cp, local_row));
+            const int row = image_row(cp, local_row);
+            Vec3 d = primary_direction<MODE>(cp, col, row);
             Vec3 c = trace_chain<MODE, STATS, true>(sp, st, eye, d, k);
-            store_pixel(out, (long long)local_row * cp.width + col, c);
+            store_pixel(out, (long long)(out.image_order ? row : local_row) * cp.width + col, c);
         }
     };
 

@@ -22,6 +22,8 @@ RT_MODE_EXACT = 0
 RT_MODE_FAST = 1
 RT_FLAG_NONE = 0
 RT_FLAG_ALL_POINT_LIGHTS = 1
+RT_FLAG_IMAGE_ORDER = 2
+RT_IPC_HANDLE_BYTES = 64
 RT_DTYPE_F32 = 0
 RT_DTYPE_F64 = 1
 
@@ -111,6 +113,10 @@ PROTOTYPES = {
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), C.POINTER(RtCamera), C.c_int32, C.c_int32, C.c_int32,
          _P, C.c_int32, C.c_int64, _P, _P, _P],
     ),
+    "rt_peer_buffer_create": (C.c_int, [C.c_int, C.c_uint64, C.POINTER(C.c_void_p), C.c_char_p]),
+    "rt_peer_buffer_open": (C.c_int, [C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]),
+    "rt_peer_buffer_close": (C.c_int, [C.c_int, _P]),
+    "rt_peer_buffer_destroy": (C.c_int, [C.c_int, _P]),
     "rt_trace_rays_dev": (
         C.c_int,
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), _P, C.POINTER(C.c_double), _P, C.c_int64,

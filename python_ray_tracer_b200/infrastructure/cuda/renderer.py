@@ -175,7 +175,7 @@ class CudaRenderer(Renderer):
         self._scene_dev: Optional[Tuple[Any, Any]] = None
 
     # ------------------------------------------------------------------ helpers
-    def _env(self, flat: FlatScene) -> abi.RtEnv:
+    def _env(self, flat: FlatScene, extra_flags: int = 0) -> abi.RtEnv:
         return abi.make_env(
             flat.eye,
             len(flat.point_lights),
@@ -183,7 +183,7 @@ class CudaRenderer(Renderer):
             flat.dome_color,
             max_depth=self.max_depth or 0,
             mode=_PRECISIONS[self.precision],
-            flags=abi.RT_FLAG_ALL_POINT_LIGHTS if self.all_point_lights else abi.RT_FLAG_NONE,
+            flags=(abi.RT_FLAG_ALL_POINT_LIGHTS if self.all_point_lights else abi.RT_FLAG_NONE) | extra_flags,
             cutoff=self.cutoff if self.precision == "fast" else 0.0,
         )
 
@@ -301,6 +301,25 @@ class CudaRenderer(Renderer):
             "rt_render_strips_dev",
         )
         return DeviceColor(planes, rgba8, stats, self.device)
+
+    def render_strips_into(self, flat: FlatScene, camera: Camera, shard: Any, frame_rgba8_ptr: int) -> None:
+        """Render this rank's strips straight into a whole-frame RGBA8 buffer at
+        ``frame_rgba8_ptr`` (``RT_FLAG_IMAGE_ORDER``): local memory or a peer GPU's
+        framebuffer (``sharding.PeerFrame``).  No linear planes are written.
+        Asynchronous on torch's current stream."""
+        _require_cuda(self.device)
+        lib = abi.load()
+        spheres, lights = self.upload_scene(flat)
+        env = self._env(flat, abi.RT_FLAG_IMAGE_ORDER)
+        cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
+        abi.check(
+            lib.rt_render_strips_dev(
+                self.device, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env), C.byref(cam),
+                shard.strip_rows, shard.rank, shard.world, None, abi.RT_DTYPE_F32, 0, frame_rgba8_ptr, None,
+                self._stream(),
+            ),
+            "rt_render_strips_dev",
+        )
 
     def render_frame_sharded(self, scene: Scene3D, rank: int, world: int, *, strip_rows: Optional[int] = None,
                              dst: int = 0, group: Any = None):

@@ -90,6 +90,9 @@ def image_order(height: int, world: int, strip_rows: int = DEFAULT_STRIP_ROWS) -
     return idx
 
 
+_ORDER_CACHE: dict = {}
+
+
 def gather_frame(local: Any, shard: StripShard, dst: int = 0, group: Any = None) -> Optional[Any]:
     """Gather the packed shards (``local``: tensor ``[shard.n_rows, ...]``) to rank ``dst``
     and return the frame in image row order there (``None`` on the other ranks).
@@ -116,7 +119,10 @@ def gather_frame(local: Any, shard: StripShard, dst: int = 0, group: Any = None)
         return None
     gathered = local.new_empty((world, max_rows) + tuple(local.shape[1:]))
     dist.gather(block, list(gathered.unbind(0)), dst=dst, group=group)
-    order = torch.from_numpy(image_order(shard.height, world, shard.strip_rows)).to(local.device)
+    key = (shard.height, world, shard.strip_rows, str(local.device))
+    order = _ORDER_CACHE.get(key)
+    if order is None:  # uploaded once per partition and device, not per frame
+        order = _ORDER_CACHE[key] = torch.from_numpy(image_order(shard.height, world, shard.strip_rows)).to(local.device)
     return gathered.reshape((world * max_rows,) + tuple(local.shape[1:])).index_select(0, order)
 
 
@@ -142,7 +148,79 @@ def covered_exactly_once(height: int, world: int, strip_rows: int = DEFAULT_STRI
     return bool((seen == 1).all())
 
 
+class _DeviceBytes:
+    """``__cuda_array_interface__`` view of raw device memory so torch can wrap it."""
+
+    def __init__(self, ptr: int, shape: tuple, typestr: str) -> None:
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 3}
+
+
+class PeerFrame:
+    """A whole-frame RGBA8 buffer on rank ``dst`` that every rank of the node can write.
+
+    Rank ``dst`` owns the memory (``rt_peer_buffer_create``) and sends the 64-byte IPC handle
+    to the other ranks (``broadcast_object_list``); they map it (``rt_peer_buffer_open``)
+    and hand the pointer to ``rt_render_strips_dev`` with ``RT_FLAG_IMAGE_ORDER``: each
+    rank's kernel stores its pixels straight into the owner's framebuffer over NVLink while
+    it renders, so the exchange step overlaps the compute and no gather or permutation
+    follows.  ``complete()`` is the only synchronisation: every rank drains its stream,
+    then a barrier tells the owner that all shards have landed.
+    """
+
+    def __init__(self, height: int, width: int, rank: int, world: int, device: int, dst: int = 0,
+                 group: Any = None) -> None:
+        import ctypes as C
+
+        import torch
+        import torch.distributed as dist
+
+        from . import abi
+
+        self.height, self.width, self.rank, self.world, self.device, self.dst = height, width, rank, world, device, dst
+        self.group = group
+        self._lib = abi.load()
+        self._owner = rank == dst
+        ptr = C.c_void_p()
+        handle = C.create_string_buffer(abi.RT_IPC_HANDLE_BYTES)
+        if self._owner:
+            abi.check(self._lib.rt_peer_buffer_create(device, height * width * 4, C.byref(ptr), handle), "rt_peer_buffer_create")
+        box = [handle.raw if self._owner else None]
+        if world > 1:
+            dist.broadcast_object_list(box, src=dst, group=group)
+        if not self._owner:
+            abi.check(self._lib.rt_peer_buffer_open(device, box[0], C.byref(ptr)), "rt_peer_buffer_open")
+        self.ptr = int(ptr.value)
+        # the owner reads the frame through torch; the writers only need the pointer
+        self.frame = None
+        if self._owner:
+            self.frame = torch.as_tensor(_DeviceBytes(self.ptr, (height, width, 4), "|u1"), device=torch.device("cuda", device))
+
+    def complete(self) -> Optional[Any]:
+        """Wait until every rank's kernel has finished writing; returns the frame on the owner."""
+        import torch
+        import torch.distributed as dist
+
+        torch.cuda.current_stream(self.device).synchronize()
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        return self.frame
+
+    def close(self) -> None:
+        if self.ptr:
+            if self.world > 1:
+                import torch.distributed as dist
+
+                dist.barrier(group=self.group)  # nobody unmaps or frees while a peer may still write
+            self.frame = None
+            if self._owner:
+                self._lib.rt_peer_buffer_destroy(self.device, self.ptr)
+            else:
+                self._lib.rt_peer_buffer_close(self.device, self.ptr)
+            self.ptr = 0
+
+
 __all__: Sequence[str] = (
+    "PeerFrame",
     "DEFAULT_STRIP_ROWS", "StripShard", "strip_shards", "band_rows", "frames_of_rank", "image_order",
     "gather_frame", "render_frame_sharded", "render_frames_sharded", "covered_exactly_once",
 )

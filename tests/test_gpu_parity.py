@@ -7,6 +7,8 @@ pixels; integer/byte work (quantisation, counters in exact mode) is bit-exact.
 """
 
 import ctypes as C
+import os
+import socket
 
 import numpy as np
 import pytest
@@ -316,3 +318,71 @@ def test_strip_shards_reassemble_to_the_full_frame(rt):
             assert np.array_equal(stacked[order].reshape(-1, 3).T, want), (name, precision)
             assert np.array_equal(stacked8[order].reshape(-1, 4), want8)
             assert traced == full.counters()["rays_traced"]
+
+
+def test_image_order_shards_fill_one_framebuffer(rt):
+    """RT_FLAG_IMAGE_ORDER: every rank's strips are stored at their image positions of ONE
+    whole-frame RGBA8 buffer (what the peer-memory exchange does across GPUs); after all
+    shards ran the buffer equals the single-launch frame, byte for byte."""
+    import torch
+
+    from python_ray_tracer_b200.infrastructure.cuda import sharding
+
+    for name, world, strip_rows in (("readme_160x90", 3, 4), ("readme_37x23", 2, 16), ("c2_readme_1080p_subset", 8, 16)):
+        case = load_case(name)
+        renderer = rt("fast")
+        cam = _camera(case)
+        want8 = _render(renderer, case).rgba8.cpu().numpy().reshape(case.height, case.width, 4)
+        frame = torch.zeros((case.height, case.width, 4), dtype=torch.uint8, device="cuda")
+        for s in sharding.strip_shards(case.height, world, strip_rows):
+            renderer.render_strips_into(case.flat, cam, s, frame.data_ptr())
+        assert np.array_equal(frame.cpu().numpy(), want8), name
+
+
+def _peer_writer(rank, world, port, name, strip_rows, out):
+    import torch
+    import torch.distributed as dist
+
+    from python_ray_tracer_b200.infrastructure import CudaRenderer
+    from python_ray_tracer_b200.infrastructure.cuda import sharding
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        case = load_case(name)
+        renderer = CudaRenderer(precision="fast")
+        cam = _camera(case)
+        peer = sharding.PeerFrame(case.height, case.width, rank, world, 0, dst=0)
+        shard = sharding.StripShard(case.height, world, rank, strip_rows)
+        renderer.render_strips_into(case.flat, cam, shard, peer.ptr)
+        frame = peer.complete()
+        if rank == 0:
+            out.put(frame.cpu().numpy())
+        peer.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_peer_framebuffer_two_processes(rt):
+    """The exchange step of config 4 with one process per rank: rank 0 owns the framebuffer,
+    rank 1 maps it through the CUDA IPC handle and its kernel stores into it.  (Both
+    processes use cuda:0 here; across GPUs the same mapping goes over NVLink.)"""
+    import torch.multiprocessing as mp
+
+    name, world, strip_rows = "readme_160x90", 2, 8
+    case = load_case(name)
+    want8 = _render(rt("fast"), case).rgba8.cpu().numpy().reshape(case.height, case.width, 4)
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    procs = [ctx.Process(target=_peer_writer, args=(r, world, port, name, strip_rows, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    frame = out.get(timeout=240)
+    for p in procs:
+        p.join(timeout=240)
+        assert p.exitcode == 0
+    assert np.array_equal(frame, want8)
