@@ -28,13 +28,18 @@ __device__ __forceinline__ double material_bound(const SceneParams& sp, int s) {
 
 // Fill the shared-memory sphere records from the SoA in global memory.  The kernels are
 // persistent (one resident block per slot, looping over tiles), so every block does this
-// once per launch; the table is 80 bytes per sphere.  Must be called by all threads.
+// once per launch; the table is 144 bytes per sphere plus the point lights in use.  Must be called by all threads.
 template <int MODE>
 __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned char* smem, const double* origin0) {
     const int n = sp.n_spheres;
     SphereGeom* geom = reinterpret_cast<SphereGeom*>(smem);
     SpherePrimary* prim = reinterpret_cast<SpherePrimary*>(smem + sizeof(SphereGeom) * (size_t)n);
     SphereAux* aux = reinterpret_cast<SphereAux*>(smem + (sizeof(SphereGeom) + sizeof(SpherePrimary)) * (size_t)n);
+    SphereMaterial* mat = reinterpret_cast<SphereMaterial*>(
+        smem + (sizeof(SphereGeom) + sizeof(SpherePrimary) + sizeof(SphereAux)) * (size_t)n);
+    double* lights = reinterpret_cast<double*>(
+        smem + (sizeof(SphereGeom) + sizeof(SpherePrimary) + sizeof(SphereAux) + sizeof(SphereMaterial)) * (size_t)n);
+    for (int i = threadIdx.x; i < 3 * sp.n_lights_used; i += blockDim.x) lights[i] = __ldg(sp.lights + i);
     __shared__ unsigned long long s_bound_bits, s_gain_bits;
     if (threadIdx.x == 0) {
         s_bound_bits = 0ull;
@@ -54,6 +59,10 @@ __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned ch
             double lx = origin0[0] - cx, ly = origin0[1] - cy, lz = origin0[2] - cz;
             prim[s] = {lx, ly, lz, fma(lz, lz, fma(ly, ly, fma(lx, lx, -(r * r))))};
         }
+        {
+            Material m = load_material(sp, s);
+            mat[s] = {m.diffuse_gain, m.specular_gain, m.roughness, m.irid_gain, m.r, m.g, m.b, m.checker ? 1.0 : 0.0};
+        }
         if (MODE == kModeFast) {
             bound = fmax(bound, material_bound(sp, s));
             gain = fmax(gain, fabs(__ldg(sp.spheres + (size_t)RT_F_SPECULAR_GAIN * n + s)));
@@ -69,6 +78,8 @@ __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned ch
     st.geom = (unsigned int)__cvta_generic_to_shared(geom);
     st.prim = (unsigned int)__cvta_generic_to_shared(prim);
     st.aux = (unsigned int)__cvta_generic_to_shared(aux);
+    st.mat = (unsigned int)__cvta_generic_to_shared(mat);
+    st.lights = (unsigned int)__cvta_generic_to_shared(lights);
     st.chain_bound = -1.0;
     if (MODE == kModeFast && sp.cutoff > 0.0) {
         double lmax = __longlong_as_double((long long)s_bound_bits);
@@ -151,7 +162,7 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
         // ---- NumpyShader.create (shader.py:63-112)
         const SphereGeom g = load_geom(st, sid);
         const double inv_r = load_aux(st, sid).inv_r;
-        const Material m = load_material(sp, sid);
+        const Material m = load_material(st, sid);
         const Vec3 centre = {g.cx, g.cy, g.cz};
         Vec3 hit, normal, nudged, to_eye;
         if (MODE == kModeExact) {
@@ -176,7 +187,7 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
         bool lit0 = false;
         double spec_sum = 0.0;
         for (int li = 0; li < sp.n_lights_used; ++li) {
-            Vec3 lp = {__ldg(sp.lights + 3 * li), __ldg(sp.lights + 3 * li + 1), __ldg(sp.lights + 3 * li + 2)};
+            Vec3 lp = load_light(st, li);
             Vec3 to_light = MODE == kModeExact ? norm_exact(lp - hit) : norm_fast(lp - hit);
             bool lit = in_light<MODE>(st, n, sid, nudged, to_light, tests);
             if (li == 0) lit0 = lit;

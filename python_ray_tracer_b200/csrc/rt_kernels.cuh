@@ -24,8 +24,9 @@ constexpr int kBlockThreads = 128;
 constexpr int kBigBlockThreads = 640;
 constexpr size_t kSmemPerSm = 227 * 1024;
 
-__host__ __device__ inline size_t staged_bytes(int n_spheres) {
-    return (sizeof(SphereGeom) + sizeof(SpherePrimary) + sizeof(SphereAux)) * (size_t)n_spheres;
+__host__ __device__ inline size_t staged_bytes(int n_spheres, int n_lights = 1) {
+    return (sizeof(SphereGeom) + sizeof(SpherePrimary) + sizeof(SphereAux) + sizeof(SphereMaterial)) * (size_t)n_spheres +
+           sizeof(double) * 3 * (size_t)n_lights;
 }
 
 // Work distribution of the persistent kernels.  A work item is one 8x4 patch (or 32 rays).

@@ -48,7 +48,7 @@ cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParam
                               const OutputParams& out, unsigned long long n_items64, cudaStream_t stream) {
     if (n_items64 > 0xfffffff0ull) return cudaErrorInvalidValue;
     const unsigned int n_items = (unsigned int)n_items64;
-    const size_t smem = staged_bytes(sp.n_spheres);
+    const size_t smem = staged_bytes(sp.n_spheres, sp.n_lights_used);
     unsigned int grid = 0;
     cudaError_t err = persistent_grid(kernel, block_threads, smem, n_items, &grid);
     if (err != cudaSuccess) return err;

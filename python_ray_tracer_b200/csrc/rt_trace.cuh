@@ -19,6 +19,8 @@ struct Staged {
     unsigned int geom;   // SphereGeom[n]
     unsigned int prim;   // SpherePrimary[n]: constants of rays that start at the camera
     unsigned int aux;    // SphereAux[n]
+    unsigned int mat;    // SphereMaterial[n]
+    unsigned int lights; // double[3 * n_lights_used]
     double chain_bound;  // Fast: sup of |local colour| over materials / (1 - sup w), or < 0
 };
 __device__ __forceinline__ void lds_f64x2(unsigned int addr, double& a, double& b) {
@@ -36,6 +38,12 @@ __device__ __forceinline__ SpherePrimary load_prim(const Staged& st, int s) {
     lds_f64x2(st.prim + (unsigned int)s * 32u + 16u, p.lz, p.c);
     return p;
 }
+// Material of one sphere as staged (64 bytes): NumpyShader's gains (shader.py:36-54), the
+// constant texture colour and the texture kind (1.0 = checker).
+struct __align__(16) SphereMaterial {
+    double diffuse_gain, specular_gain, roughness, irid_gain;
+    double r, g, b, checker;
+};
 __device__ __forceinline__ SphereAux load_aux(const Staged& st, int s) {
     SphereAux a;
     lds_f64x2(st.aux + (unsigned int)s * 16u, a.inv_r, a.cc);
@@ -102,6 +110,10 @@ __device__ __forceinline__ double near_root(const HalfB& q) {
 // NumpyShader._calculate_shadow (shader.py:114-128): lit iff no other sphere is closer
 // along the shadow ray than the point's own sphere (FARAWAY when the ray leaves it).
 // ---------------------------------------------------------------------------------------
+// min of two positive doubles (no NaN plumbing): positive doubles order like their bits
+__device__ __forceinline__ double fmin_pos(double a, double b) {
+    return __double_as_longlong(b) < __double_as_longlong(a) ? b : a;
+}
 template <int MODE>
 __device__ __forceinline__ bool in_light(const Staged& st, int n, int s, Vec3 p, Vec3 l,
                                          unsigned long long& tests) {
@@ -115,21 +127,24 @@ __device__ __forceinline__ bool in_light(const Staged& st, int n, int s, Vec3 p,
         }
         return lit;
     } else {
-        HalfB qo = half_b(p, l, load_geom(st, s));
-        const double own = can_hit(qo) ? near_root(qo) : kMiss;
-        // any sphere hit closer than `own` occludes (a root that rounds to <= 0 comes back
-        // as kMiss and never does).  Two spheres per trip: independent FP64 chains.
+        // nearest hit among the OTHER spheres first: in most shadow tests there is none and
+        // the point's own sphere never has to be intersected.  Two spheres per trip.
+        double other = kMiss;
         int j = 0;
         for (; j + 1 < n; j += 2) {
             HalfB q0 = half_b(p, l, load_geom(st, j));
             HalfB q1 = half_b(p, l, load_geom(st, j + 1));
-            if (j != s && can_hit(q0) && near_root(q0) < own) return false;
-            if (j + 1 != s && can_hit(q1) && near_root(q1) < own) return false;
+            if (j != s && can_hit(q0)) other = fmin_pos(other, near_root(q0));
+            if (j + 1 != s && can_hit(q1)) other = fmin_pos(other, near_root(q1));
         }
         if (j < n && j != s) {
             HalfB q = half_b(p, l, load_geom(st, j));
-            if (can_hit(q) && near_root(q) < own) return false;
+            if (can_hit(q)) other = fmin_pos(other, near_root(q));
         }
+        if (other == kMiss) return true;
+        HalfB qo = half_b(p, l, load_geom(st, s));
+        const double own = can_hit(qo) ? near_root(qo) : kMiss;
+        return !(other < own);
         return true;
     }
 }
@@ -142,6 +157,7 @@ struct Material {
     double r, g, b;
     bool checker;
 };
+// from the global SoA (staging only)
 __device__ __forceinline__ Material load_material(const SceneParams& sp, int s) {
     const double* f = sp.spheres;
     const size_t n = (size_t)sp.n_spheres;
@@ -155,6 +171,25 @@ __device__ __forceinline__ Material load_material(const SceneParams& sp, int s) 
     m.b = __ldg(f + RT_F_COLOR_B * n + s);
     m.checker = __ldg(f + RT_F_TEXTURE * n + s) != 0.0;
     return m;
+}
+// from shared memory (one shaded hit): four broadcast 16-byte loads
+__device__ __forceinline__ Material load_material(const Staged& st, int s) {
+    Material m;
+    double checker;
+    const unsigned int a = st.mat + (unsigned int)s * 64u;
+    lds_f64x2(a, m.diffuse_gain, m.specular_gain);
+    lds_f64x2(a + 16u, m.roughness, m.irid_gain);
+    lds_f64x2(a + 32u, m.r, m.g);
+    lds_f64x2(a + 48u, m.b, checker);
+    m.checker = checker != 0.0;
+    return m;
+}
+__device__ __forceinline__ Vec3 load_light(const Staged& st, int li) {
+    Vec3 p;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p.x) : "r"(st.lights + (unsigned int)li * 24u));
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p.y) : "r"(st.lights + (unsigned int)li * 24u + 8u));
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p.z) : "r"(st.lights + (unsigned int)li * 24u + 16u));
+    return p;
 }
 
 // TextureChecker.get_color (shader.py:29-32): astype(int) truncates, % 2 is non-negative.
