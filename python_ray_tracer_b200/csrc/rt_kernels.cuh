@@ -10,8 +10,14 @@ namespace rt {
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 5  // resident 128-thread blocks per SM the register allocator must allow
 #endif
-#ifndef RT_STATIC_PCT
-#define RT_STATIC_PCT 70  // share of the work items handed out statically (no atomics)
+#ifndef RT_DYNAMIC_PCT
+#define RT_DYNAMIC_PCT 30     // long launches of cheap items: share of the items left to the ticket counter
+#endif
+#ifndef RT_SHORT_LAUNCH_ROUNDS
+#define RT_SHORT_LAUNCH_ROUNDS 64  // launches with fewer items per warp are ticketed entirely
+#endif
+#ifndef RT_COSTLY_ITEM_SPHERES
+#define RT_COSTLY_ITEM_SPHERES 8   // scenes with at least this many spheres are ticketed entirely
 #endif
 
 constexpr int kWarpTileW = 8;     // each warp renders 8x4 pixel patches: bounce coherence, and
@@ -31,17 +37,31 @@ __host__ __device__ inline size_t staged_bytes(int n_spheres, int n_lights = 1) 
 
 // Work distribution of the persistent kernels.  A work item is one 8x4 patch (or 32 rays).
 // The first static_rounds * n_warps items are dealt round-robin (warp w takes items w,
-// w + n_warps, ...: a stratified sample of the frame, no atomics); the rest are drawn one
-// at a time from a device counter (lane 0, one atomicAdd per ticket), so the tail of the
-// launch is balanced at the granularity of a single patch.  Every warp keeps its next
-// ticket in flight while it works, and draws exactly one ticket >= n_tickets before it
-// leaves, so the draw that returns n_tickets + n_warps - 1 is the last of the launch and
-// puts the counter back to zero for the next launch that uses it.
+// w + n_warps, ...: no atomics); the rest are drawn one at a time from a device counter
+// (lane 0, one atomicAdd per ticket), so the launch ends balanced at the granularity of a
+// single patch.  Every warp keeps its next ticket in flight while it works and draws
+// exactly one ticket >= n_tickets before it leaves, so the draw that returns
+// n_tickets + n_warps - 1 is the last of the launch and puts the counter back to zero for
+// the next launch that uses it.
+//
+// How much is ticketed, and in which order, is chosen per launch from measurements on B200
+// (profiles/r01/schedule_sweep.txt).  Patch times of the README frame run from 1 us (sky)
+// to 28 us (15-bounce chains where the spheres meet the ground): a static deal of
+// everything leaves a 15 % tail at 1080p, while ticketing everything costs ~1 G
+// same-address atomics/s on an 8K frame (+9 %).  So: short launches and launches of costly
+// items (many spheres) are ticketed entirely, after one static round that hides the burst
+// of first draws, and taken from the bottom of the frame upwards -- the long chains sit low
+// in the frame and the rows that come last are its top, where the reference's fixed camera
+// (image plane z = 0, +y up, base.py:130-141) sees the least, so the tail is made of short
+// patches; long launches of cheap items deal the first 70 % statically, top-down.  These
+// are heuristics about time only, never about results.
 struct Tickets {
     unsigned int* counter;
     unsigned int n_tickets;      // items handed out dynamically
     unsigned int n_warps;        // gridDim.x * (block threads / 32)
     unsigned int static_rounds;  // items [0, static_rounds * n_warps) are dealt statically
+    unsigned int n_items;
+    unsigned int reversed;       // take items from the last one backwards
 };
 __device__ __forceinline__ unsigned int draw_ticket(const Tickets& tk, int lane) {
     unsigned int t = 0;
@@ -129,6 +149,10 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
     Counters k = {0, 0, 0, 0};
 
     auto render_patch = [&](unsigned int item) {
+#ifdef RT_TIMING_DEBUG
+        unsigned long long t_item0 = 0;
+        if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_item0));
+#endif
         const unsigned int ty = item / tiles_x, tx = item - ty * tiles_x;
         const int local_row = (int)ty * kWarpTileH + py;
         const int col = (int)tx * kWarpTileW + px;
@@ -138,18 +162,43 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
             Vec3 c = trace_chain<MODE, STATS, true>(sp, st, eye, d, k);
             store_pixel(out, (long long)(out.image_order ? row : local_row) * cp.width + col, c);
         }
+#ifdef RT_TIMING_DEBUG
+        if (STATS && out.stats != nullptr) {
+            __syncwarp();
+            unsigned long long t_item1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_item1));
+            if (lane == 0) {
+                out.stats[8 + 2 * 148 * 32 + 2 * item] = t_item0;
+                out.stats[8 + 2 * 148 * 32 + 2 * item + 1] = t_item1;
+            }
+        }
+#endif
     };
 
+#ifdef RT_TIMING_DEBUG
+    // experiment only (tools/warp_timeline.py): per-warp start/end stamps behind the counters
+    unsigned long long t_start = 0;
+    if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+#endif
+    auto render_item = [&](unsigned int idx) { render_patch(tk.reversed ? tk.n_items - 1u - idx : idx); };
     unsigned int next = draw_ticket(tk, lane);  // in flight during the static rounds
 #pragma unroll 1
-    for (unsigned int r = 0; r < tk.static_rounds; ++r) render_patch(r * tk.n_warps + warp_id);
+    for (unsigned int r = 0; r < tk.static_rounds; ++r) render_item(r * tk.n_warps + warp_id);
     const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
 #pragma unroll 1
     while (next < tk.n_tickets) {
-        const unsigned int item = first_dynamic + next;
+        const unsigned int idx = first_dynamic + next;
         next = draw_ticket(tk, lane);
-        render_patch(item);
+        render_item(idx);
     }
+#ifdef RT_TIMING_DEBUG
+    if (STATS && out.stats != nullptr && lane == 0) {
+        unsigned long long t_end;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+        out.stats[8 + 2 * warp_id] = t_start;
+        out.stats[8 + 2 * warp_id + 1] = t_end;
+    }
+#endif
     flush_counters<STATS>(k, out.stats);
 }
 

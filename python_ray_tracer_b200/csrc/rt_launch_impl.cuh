@@ -45,7 +45,8 @@ cudaError_t persistent_grid(Kernel kernel, int block_threads, size_t smem, unsig
 
 template <typename Kernel, typename Work>
 cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParams& sp, const Work& work,
-                              const OutputParams& out, unsigned long long n_items64, cudaStream_t stream) {
+                              const OutputParams& out, unsigned long long n_items64, cudaStream_t stream,
+                              bool camera = false) {
     if (n_items64 > 0xfffffff0ull) return cudaErrorInvalidValue;
     const unsigned int n_items = (unsigned int)n_items64;
     const size_t smem = staged_bytes(sp.n_spheres, sp.n_lights_used);
@@ -55,7 +56,16 @@ cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParam
     Tickets tk;
     if ((err = ticket_counter(&tk.counter)) != cudaSuccess) return err;
     tk.n_warps = grid * ((unsigned int)block_threads / 32u);
-    tk.static_rounds = (unsigned int)((unsigned long long)n_items * RT_STATIC_PCT / 100ull / tk.n_warps);
+    tk.n_items = n_items;
+    const unsigned int rounds = n_items / tk.n_warps;
+    const bool all_tickets = rounds <= RT_SHORT_LAUNCH_ROUNDS || sp.n_spheres >= RT_COSTLY_ITEM_SPHERES;
+    if (all_tickets) {
+        tk.reversed = camera ? 1u : 0u;
+        tk.static_rounds = rounds >= 1u ? 1u : 0u;
+    } else {
+        tk.reversed = 0u;
+        tk.static_rounds = rounds - (unsigned int)((unsigned long long)rounds * RT_DYNAMIC_PCT / 100ull);
+    }
     tk.n_tickets = n_items - tk.static_rounds * tk.n_warps;
     kernel<<<grid, block_threads, smem, stream>>>(sp, work, out, tk);
     return cudaGetLastError();
@@ -69,11 +79,11 @@ cudaError_t render_rows(bool stats, const SceneParams& sp, const CameraParams& c
     const unsigned long long tiles_y = (unsigned long long)(rows + kWarpTileH - 1) / kWarpTileH;
     const unsigned long long n = tiles_x * tiles_y;
     if (big_blocks(sp.n_spheres)) {
-        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads>, kBigBlockThreads, sp, cp, out, n, stream);
-        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads>, kBigBlockThreads, sp, cp, out, n, stream);
+        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads>, kBigBlockThreads, sp, cp, out, n, stream, true);
+        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads>, kBigBlockThreads, sp, cp, out, n, stream, true);
     }
-    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads>, kBlockThreads, sp, cp, out, n, stream);
-    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads>, kBlockThreads, sp, cp, out, n, stream);
+    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads>, kBlockThreads, sp, cp, out, n, stream, true);
+    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads>, kBlockThreads, sp, cp, out, n, stream, true);
 }
 
 cudaError_t trace_rays(bool stats, const SceneParams& sp, const RayBatch& rb, const OutputParams& out,
