@@ -144,6 +144,7 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
     const int lane = threadIdx.x & 31;
     const int px = lane & (kWarpTileW - 1), py = lane >> 3;
     const unsigned int tiles_x = (unsigned int)(cp.width + kWarpTileW - 1) / kWarpTileW;
+    const unsigned int tiles_x_recip = tiles_x > 1u ? (unsigned int)(0x100000000ull / tiles_x) : 0xffffffffu;
     const unsigned int warp_id = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
     const Vec3 eye = {cp.cam[0], cp.cam[1], cp.cam[2]};
     Counters k = {0, 0, 0, 0};
@@ -153,7 +154,14 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
         unsigned long long t_item0 = 0;
         if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_item0));
 #endif
-        const unsigned int ty = item / tiles_x, tx = item - ty * tiles_x;
+        // item / tiles_x by a reciprocal formed once per thread: floor(2^32 / d) underestimates
+        // the quotient of a 31-bit item by at most one
+        unsigned int ty = __umulhi(item, tiles_x_recip);
+        unsigned int tx = item - ty * tiles_x;
+        if (tx >= tiles_x) {
+            tx -= tiles_x;
+            ty += 1u;
+        }
         const int local_row = (int)ty * kWarpTileH + py;
         const int col = (int)tx * kWarpTileW + px;
         if (col < cp.width && local_row < cp.n_rows) {

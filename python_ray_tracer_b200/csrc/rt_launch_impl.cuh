@@ -47,7 +47,7 @@ template <typename Kernel, typename Work>
 cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParams& sp, const Work& work,
                               const OutputParams& out, unsigned long long n_items64, cudaStream_t stream,
                               bool camera = false) {
-    if (n_items64 > 0xfffffff0ull) return cudaErrorInvalidValue;
+    if (n_items64 > 0x7ffffff0ull) return cudaErrorInvalidValue;  // 31-bit items (reciprocal division in the kernels)
     const unsigned int n_items = (unsigned int)n_items64;
     const size_t smem = staged_bytes(sp.n_spheres, sp.n_lights_used);
     unsigned int grid = 0;
