@@ -46,6 +46,9 @@ README_DEFAULT = DefaultMaterial(**scenes.README_GAINS)
 FLOP_PER_SPHERE_TEST = 24.0   # one ray/sphere quadratic
 FLOP_PER_HIT = 280.0          # NumpyShader.create without its S shadow tests
 BYTES_PER_PIXEL = 12.0 + 4.0  # planar f32 RGB + RGBA8, each written once
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, one `ncu --set full` capture per workload
+# (profiles/r01/*_details.txt); None where no capture was taken
+NCU_DRAM_BYTES_PER_LAUNCH = {"c2": 560896}
 
 
 def workload(name: str, rank: int, step: int, world: int):
@@ -398,15 +401,25 @@ def run_b200_arm(args) -> None:
                 "with_rgb8": {"ms_per_step": e2e_rgb8_ms, "value": pixels_per_step / (e2e_rgb8_ms * 1e-3) / 1e6,
                               "d2h_bytes_per_step": d2h + rgb8_host.numel()}},
         "gpu_launches": args.steps,
-        "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
-                     "kernel": "render_rows_kernel", "kernel_ms": kernel_ms,
-                     "note": "the kernel is FP64-ALU-bound, not HBM-bound: see roofline_alu (DESIGN.md section 4)"},
-        "roofline_alu": {"bound": "fp64", "achieved": achieved_tflops, "peak": fp64.value / 1e12, "unit": "TFLOP/s",
-                         "frac": achieved_tflops / (fp64.value / 1e12) if fp64.value else None,
-                         "fp32_peak": fp32.value / 1e12, "peak_source": "rt_measure_fma_peak, same GPU, same run",
-                         "algorithmic_flop_per_step": flop,
-                         "counters": {"rays_traced": traced, "hits_shaded": hits, "generations": deepest, "sphere_tests": tests}},
+        # The binding roofline of this path is the FP64 pipe (no contraction, 16 B written per
+        # pixel): algorithmic flops / kernel time against the FP64 FMA rate measured on this GPU
+        # in this run.  The HBM reading (MEASURED_PEAKS.json denominator) is kept beside it.
+        "roofline": {"bound": "fp64-alu", "achieved": achieved_tflops, "peak": fp64.value / 1e12, "unit": "TFLOP/s",
+                     "frac": achieved_tflops / (fp64.value / 1e12) if fp64.value else None,
+                     "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload),
+                     "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one launch under ncu --set full "
+                                     "(profiles/): the frame stays in the 126 MB L2 while the kernel runs, so DRAM sees "
+                                     "almost nothing of the 33 MB the launch writes",
+                     "peak_source": "rt_measure_fma_peak (register-resident FP64 FMA chains), same GPU, same run; "
+                                    "MEASURED_PEAKS.json holds no ALU peak",
+                     "fp32_peak": fp32.value / 1e12, "kernel": "render_rows_kernel", "kernel_ms": kernel_ms,
+                     "algorithmic_flop_per_step": flop,
+                     "counters": {"rays_traced": traced, "hits_shaded": hits, "generations": deepest, "sphere_tests": tests}},
+        "roofline_hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": achieved_gbs / peaks["hbm_gbs"], "peak_source": peaks["source"],
+                         "algorithmic_bytes_per_step": bytes_per_pixel * n},
+        "roofline_alu": {"frac": achieved_tflops / (fp64.value / 1e12) if fp64.value else None,
+                         "note": "same as roofline (kept for the sweep scripts)"},
         "clocks": clocks,
         "wall_s_timed_region": wall,
     }
