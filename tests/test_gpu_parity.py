@@ -386,3 +386,23 @@ def test_peer_framebuffer_two_processes(rt):
         p.join(timeout=240)
         assert p.exitcode == 0
     assert np.array_equal(frame, want8)
+
+
+def test_turntable_batch_writes_reference_frames(rt, c_oracle, tmp_path):
+    """Config 5 at small size: the batch driver (render || copy || parallel PNG encode) writes
+    the frames this rank owns; frame 37 decodes to the reference's fixture within 1 LSB,
+    a second call resumes (writes nothing)."""
+    from python_ray_tracer_b200 import scenes, turntable
+    from python_ray_tracer_b200.infrastructure import CudaRenderer
+    from python_ray_tracer_b200.infrastructure.png import read_png
+
+    case = load_case("turntable37_160x90")
+    renderer = CudaRenderer(**scenes.README_GAINS, precision="fast")
+    stats = turntable.render_turntable(renderer, 256, tmp_path, 160, 90, rank=37, world=64, encoder_threads=4)
+    assert stats["frames"] == 4 and stats["skipped"] == 0
+    assert sorted(p.name for p in tmp_path.glob("*.png")) == [f"frame_{k:04d}.png" for k in (37, 101, 165, 229)]
+    got = read_png(turntable.frame_path(tmp_path, 37))
+    assert got.shape == (90, 160, 3)
+    assert_png_parity(got, c_oracle.quantize(case.rgb), "turntable frame 37")
+    again = turntable.render_turntable(renderer, 256, tmp_path, 160, 90, rank=37, world=64, encoder_threads=4)
+    assert again["frames"] == 0 and again["skipped"] == 4

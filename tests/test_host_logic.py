@@ -211,3 +211,26 @@ def test_abi_rejects_bad_arguments_without_a_gpu():
         abi.check(rc, "rt_render_rows_dev")
     rc = lib.rt_quantize_dev(0, 8, 0, 4, 4, 8, 5, None)
     assert rc == -1
+
+
+def test_parallel_png_is_a_valid_png_with_the_same_pixels(tmp_path):
+    """The banded (pigz-style) encoder of the animation path decodes to the same pixels as the
+    single-stream one, with our reader and with Pillow when it is installed."""
+    from python_ray_tracer_b200.infrastructure.png import encode_png, encode_png_parallel, read_png
+
+    rng = np.random.default_rng(5)
+    for h, w in ((1, 1), (7, 5), (90, 160), (33, 257)):
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        for threads, level in ((1, 1), (3, 1), (8, 6), (64, 0)):
+            data = encode_png_parallel(img, level, threads)
+            path = tmp_path / "p.png"
+            path.write_bytes(data)
+            assert np.array_equal(read_png(path), img)
+            try:
+                from PIL import Image
+            except ImportError:
+                continue
+            assert np.array_equal(np.asarray(Image.open(path).convert("RGB")), img)
+        ref = tmp_path / "r.png"
+        ref.write_bytes(encode_png(img))
+        assert np.array_equal(read_png(ref), img)
