@@ -20,8 +20,11 @@ namespace rt {
 #define RT_COSTLY_ITEM_SPHERES 8   // scenes with at least this many spheres are ticketed entirely
 #endif
 
-constexpr int kWarpTileW = 8;     // each warp renders 8x4 pixel patches: bounce coherence, and
-constexpr int kWarpTileH = 4;     // every row segment it stores is one full 32-byte sector
+#ifndef RT_PATCH_W
+#define RT_PATCH_W 8
+#endif
+constexpr int kWarpTileW = RT_PATCH_W;       // each warp renders 8x4 pixel patches: bounce coherence, and
+constexpr int kWarpTileH = 32 / RT_PATCH_W;  // every row segment it stores is one full 32-byte sector
 // Two block shapes.  Small scenes: 128-thread blocks, RT_MIN_BLOCKS resident per SM, each
 // with its own copy of the (small) sphere table.  Scenes whose table would not fit that
 // many times in an SM's shared memory: one 640-thread block per SM sharing one copy, the
@@ -142,7 +145,7 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
     const Staged st = stage_scene<MODE>(sp, smem, cp.cam);
 
     const int lane = threadIdx.x & 31;
-    const int px = lane & (kWarpTileW - 1), py = lane >> 3;
+    const int px = lane & (kWarpTileW - 1), py = lane / kWarpTileW;
     const unsigned int tiles_x = (unsigned int)(cp.width + kWarpTileW - 1) / kWarpTileW;
     const unsigned int tiles_x_recip = tiles_x > 1u ? (unsigned int)(0x100000000ull / tiles_x) : 0xffffffffu;
     const unsigned int warp_id = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);

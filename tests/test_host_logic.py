@@ -234,3 +234,25 @@ def test_parallel_png_is_a_valid_png_with_the_same_pixels(tmp_path):
         ref = tmp_path / "r.png"
         ref.write_bytes(encode_png(img))
         assert np.array_equal(read_png(ref), img)
+
+
+def test_new_entry_points_reject_bad_arguments_without_a_gpu():
+    lib = abi.load()
+    cam = abi.make_camera((0, 0.2, -2), 16, 9)
+    env = abi.make_env((0, 0.2, -2), 1, [0.1], (1, 1, 1))
+    # strips: first must be below step, rows and step positive
+    for rows, first, step in ((0, 0, 1), (4, 2, 2), (4, -1, 2), (4, 0, 0)):
+        rc = lib.rt_render_strips_dev(0, 8, 3, 8, ctypes.byref(env), ctypes.byref(cam), rows, first, step, None, 0, 144,
+                                      None, None, None)
+        assert rc == -1 and b"strips" in lib.rt_last_error(), (rows, first, step)
+    # image-order outputs are whole frames: the plane stride must cover height x width
+    env.flags = abi.RT_FLAG_IMAGE_ORDER
+    rc = lib.rt_render_strips_dev(0, 8, 3, 8, ctypes.byref(env), ctypes.byref(cam), 4, 0, 2, 8, 0, 16 * 5, None, None, None)
+    assert rc == -1 and b"plane_stride" in lib.rt_last_error()
+    # peer buffers
+    ptr = ctypes.c_void_p()
+    handle = ctypes.create_string_buffer(abi.RT_IPC_HANDLE_BYTES)
+    assert lib.rt_peer_buffer_create(0, 0, ctypes.byref(ptr), handle) == -1
+    assert lib.rt_peer_buffer_create(0, 64, None, handle) == -1
+    assert lib.rt_peer_buffer_open(0, None, ctypes.byref(ptr)) == -1
+    assert lib.rt_peer_buffer_close(0, None) == 0 and lib.rt_peer_buffer_destroy(0, None) == 0
