@@ -22,6 +22,11 @@ FULL_FRAME_CASES = [
     "main_160x90", "readme_160x90", "turntable37_160x90", "readme_1x7", "readme_9x1", "readme_37x23",
     "readme_2x2", "c3_small_48_192x108", "c3_small_48_192x108_depth8", "c3_small_48_192x108_depth1",
 ]
+STRESS_CASES = [
+    "stress_inside", "stress_overlap", "stress_light_inside", "stress_mirror", "stress_diffuse_only", "stress_domes",
+    "stress_scales", "stress_signed_gains", "stress_checkers", "stress_random20", "stress_dark", "stress_far_light",
+]
+FULL_FRAME_CASES += [f"{name}_48x27" for name in STRESS_CASES]
 SUBSET_CASES = [
     "g0_main_960x540_subset", "c1_readme_960x540_subset", "c2_readme_1080p_subset", "c4_readme_8k_subset",
     "c3_1024_4k_subset_depth8",
