@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 /* The reference's miss sentinel (base.py:12, shader.py:10). */
 #define RT_FARAWAY 1.0e39
@@ -91,6 +91,12 @@ typedef struct rt_env {
     double cutoff;               /* RT_MODE_FAST only: stop a bounce chain once its
                                     remaining contribution is provably below this
                                     (linear units).  0 = never cut.                       */
+    const void* accel_dev;       /* optional: device copy of the blob rt_accel_build_host()
+                                    made for THIS sphere table (a bounding-volume tree);
+                                    rays then skip the sphere tests that provably miss.
+                                    NULL = test every sphere, like base.py:97 /
+                                    shader.py:126.  Results are identical either way.     */
+    int64_t accel_bytes;         /* size of that blob                                     */
 } rt_env;
 
 typedef enum rt_mode {
@@ -140,6 +146,20 @@ int rt_release_cache(void);
  * main.py:55-57); it exists for the measurement contract only.  Synchronous.
  */
 int rt_measure_fma_peak(int device, int32_t dtype, double* flops_out);
+
+/*
+ * rt_accel_build_host -- bounding-volume tree over the spheres, built on the host into one
+ * position-independent blob the caller uploads and names in rt_env.accel_dev.  Nothing in
+ * the reference corresponds to it (it intersects every ray with every shape); it exists so
+ * that scenes of hundreds of spheres (BASELINE config 3) do not pay for tests that cannot
+ * hit, and so that scenes too large for shared memory can be rendered at all.
+ *   rt_accel_bytes(n)  capacity to allocate for n spheres (an upper bound)
+ *   env                dome lights and mode of the render calls the blob will serve (it
+ *                      carries the material bound of the fast policy's chain cut-off)
+ */
+int64_t rt_accel_bytes(int32_t n_spheres);
+int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_env* env,
+                        void* blob_out, int64_t capacity, int64_t* bytes_out);
 
 /*
  * rt_render_rows_dev -- camera rays for image rows [row0, row1) of cam.

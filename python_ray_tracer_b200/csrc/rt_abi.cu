@@ -11,6 +11,7 @@
 #include <mutex>
 
 #include "../../include/rt_abi.h"
+#include "rt_accel.h"
 #include "rt_launch.h"
 
 namespace {
@@ -71,8 +72,11 @@ int check_env(const rt_env* env, int32_t n_spheres) {
         return fail(RT_ERR_BAD_ARG, "n_dome_lights = %d outside 0..%d", env->n_dome_lights, RT_MAX_DOME_LIGHTS);
     if (env->mode != RT_MODE_EXACT && env->mode != RT_MODE_FAST) return fail(RT_ERR_BAD_ARG, "unknown mode %d", env->mode);
     if (!(env->cutoff >= 0.0)) return fail(RT_ERR_BAD_ARG, "cutoff must be >= 0");
-    if (n_spheres > rt::max_staged_spheres())
-        return fail(RT_ERR_UNSUPPORTED, "%d spheres exceed the %d that fit one block's shared memory", n_spheres,
+    if (env->accel_dev != nullptr && env->accel_bytes < (int64_t)sizeof(rt::AccelHeader))
+        return fail(RT_ERR_BAD_ARG, "accel_bytes = %lld is smaller than a blob header", (long long)env->accel_bytes);
+    if (env->accel_dev == nullptr && n_spheres > rt::max_staged_spheres())
+        return fail(RT_ERR_UNSUPPORTED, "%d spheres exceed the %d that fit one block's shared memory; "
+                    "build a tree with rt_accel_build_host and pass it in rt_env.accel_dev", n_spheres,
                     rt::max_staged_spheres());
     return RT_OK;
 }
@@ -89,6 +93,7 @@ rt::SceneParams scene_params(const double* spheres_dev, int32_t n_spheres, const
     memset(&sp, 0, sizeof(sp));
     sp.spheres = spheres_dev;
     sp.lights = lights_dev;
+    sp.accel = static_cast<const unsigned char*>(env->accel_dev);
     sp.n_spheres = n_spheres;
     sp.n_lights_used = (env->flags & RT_FLAG_ALL_POINT_LIGHTS) ? env->n_point_lights : 1;
     sp.n_dome = env->n_dome_lights;

@@ -1,0 +1,51 @@
+// rt_accel.h -- layout of the sphere BVH blob (host builder <-> device traversal).
+//
+// Nothing in the reference corresponds to this: NumpyRenderer.raytrace_scene intersects every
+// ray with every shape (base.py:97) and every shadow ray with every shape again
+// (shader.py:126).  The BVH only skips tests that provably miss; the tests it does run are the
+// same arithmetic on the same records, so the nearest hit, the shadow decision and the ray
+// totals are the ones brute force finds (ties still go to the lowest shape index).
+//
+// One position-independent blob in device memory (offsets from its start):
+//   AccelHeader
+//   AccelNode  nodes[n_nodes]        binary tree, root = 0, children of an inner node adjacent
+//   int32      order[n_in_tree]      shape index of every leaf slot
+//   SphereGeom leaf_geom[n_in_tree]  {cx,cy,cz,r*r} in leaf-slot order (what traversal reads)
+//   SphereGeom geom[n_spheres]       the same records by shape index (what shading reads)
+//   SphereAux  aux[n_spheres]        {1/r, |C|^2} by shape index
+//   int32      large[n_large]        shapes kept out of the tree and tested for every ray
+//                                    (a ground sphere of radius 1e5 would swallow every box)
+#pragma once
+
+#include <stdint.h>
+
+namespace rt {
+
+constexpr uint32_t kAccelMagic = 0x52544256u;  // "RTBV"
+constexpr int kAccelLeafSize = 4;
+constexpr int kAccelMaxLarge = 16;
+constexpr int kAccelStack = 48;
+
+struct AccelHeader {
+    uint32_t magic;
+    int32_t n_spheres;
+    int32_t n_nodes;
+    int32_t n_in_tree;
+    int32_t n_large;
+    int32_t reserved;
+    int64_t off_nodes, off_order, off_leaf_geom, off_geom, off_aux, off_large;
+    int64_t bytes;
+    double local_bound;  // sup over materials of |local colour| (material_bound(), rt_chain.cuh)
+    double gain_bound;   // sup over materials of |specular_gain|
+};
+
+// 64 bytes.  Boxes are the union of the spheres' boxes, grown by a relative 1e-9 so that a ray
+// the exact FP64 sphere test accepts is never rejected by the slab test's own rounding.
+struct alignas(16) AccelNode {
+    double lo[3];
+    double hi[3];
+    int32_t first;   // inner: index of the left child (right = first + 1); leaf: first leaf slot
+    int32_t count;   // inner: -(split axis + 1); leaf: number of slots (1..kAccelLeafSize)
+};
+
+}  // namespace rt

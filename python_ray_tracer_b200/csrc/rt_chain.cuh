@@ -1,7 +1,7 @@
 // rt_chain.cuh -- scene staging and the register-resident bounce chain (device).
 #pragma once
 
-#include "rt_trace.cuh"
+#include "rt_accel.cuh"
 
 namespace rt {
 
@@ -29,6 +29,24 @@ __device__ __forceinline__ double material_bound(const SceneParams& sp, int s) {
 // Fill the shared-memory sphere records from the SoA in global memory.  The kernels are
 // persistent (one resident block per slot, looping over tiles), so every block does this
 // once per launch; the table is 144 bytes per sphere plus the point lights in use.  Must be called by all threads.
+// ACCEL launches keep the spheres in global memory (BVH blob): only the lights are staged, and
+// the cut-off bound comes from the blob header (computed once per scene on the host).
+template <int MODE>
+__device__ __forceinline__ Staged stage_lights_only(const SceneParams& sp, unsigned char* smem, const AccelView& av) {
+    double* lights = reinterpret_cast<double*>(smem);
+    for (int i = threadIdx.x; i < 3 * sp.n_lights_used; i += blockDim.x) lights[i] = __ldg(sp.lights + i);
+    __syncthreads();
+    Staged st;
+    st.geom = st.prim = st.aux = st.mat = 0u;
+    st.lights = (unsigned int)__cvta_generic_to_shared(lights);
+    st.chain_bound = -1.0;
+    if (MODE == kModeFast && sp.cutoff > 0.0) {
+        const double wmax = 0.5 * av.gain_bound;
+        if (wmax < 1.0 && isfinite(av.local_bound)) st.chain_bound = av.local_bound / (1.0 - wmax);
+    }
+    return st;
+}
+
 template <int MODE>
 __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned char* smem, const double* origin0) {
     const int n = sp.n_spheres;
@@ -95,9 +113,10 @@ __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned ch
 // (both contribute in the reference) resolve to the lowest shape index here.
 // CAMERA: generation 0 starts at sp.eye (the camera kernel), so the fast policy uses the
 // staged per-sphere constants of that origin.
-template <int MODE, bool STATS, bool CAMERA>
-__device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged& st, Vec3 o, Vec3 d,
-                                            Counters& k) {
+// ACCEL: nearest hit and shadow test walk the BVH blob (av) instead of the staged table.
+template <int MODE, bool STATS, bool CAMERA, bool ACCEL>
+__device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged& st, const AccelView& av, Vec3 o,
+                                            Vec3 d, Counters& k) {
     const int n = sp.n_spheres;
     const Vec3 eye = {sp.eye[0], sp.eye[1], sp.eye[2]};
     Vec3 color = {0.0, 0.0, 0.0};
@@ -109,13 +128,15 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
         if (STATS) {
             k.traced += 1;
             k.deepest = generation + 1 > (int)k.deepest ? generation + 1 : k.deepest;
-            tests += (unsigned long long)n;
+            if (!ACCEL) tests += (unsigned long long)n;
         }
 
         // ---- nearest hit (base.py:97-105)
         double tmin = kMiss;
         int sid = -1;
-        if (MODE == kModeExact) {
+        if (ACCEL) {
+            accel_nearest<MODE>(av, o, d, tmin, sid, tests);
+        } else if (MODE == kModeExact) {
             for (int s = 0; s < n; ++s) {
                 double t = sphere_distance_exact(o, d, load_geom(st, s), load_aux(st, s).cc);
                 if (t < tmin) {
@@ -160,9 +181,9 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
         if (STATS) k.hits += 1;
 
         // ---- NumpyShader.create (shader.py:63-112)
-        const SphereGeom g = load_geom(st, sid);
-        const double inv_r = load_aux(st, sid).inv_r;
-        const Material m = load_material(st, sid);
+        const SphereGeom g = ACCEL ? ldg_geom(av.geom + sid) : load_geom(st, sid);
+        const double inv_r = ACCEL ? __ldg(&av.aux[sid].inv_r) : load_aux(st, sid).inv_r;
+        const Material m = ACCEL ? load_material(sp, sid) : load_material(st, sid);
         const Vec3 centre = {g.cx, g.cy, g.cz};
         Vec3 hit, normal, nudged, to_eye;
         if (MODE == kModeExact) {
@@ -189,7 +210,14 @@ __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged&
         for (int li = 0; li < sp.n_lights_used; ++li) {
             Vec3 lp = load_light(st, li);
             Vec3 to_light = MODE == kModeExact ? norm_exact(lp - hit) : norm_fast(lp - hit);
-            bool lit = in_light<MODE>(st, n, sid, nudged, to_light, tests);
+            bool lit;
+            if (ACCEL) {
+                const double own = accel_sphere_t<MODE>(nudged, to_light, g, MODE == kModeExact ? __ldg(&av.aux[sid].cc) : 0.0);
+                tests += 1;
+                lit = !accel_occluded<MODE>(av, sid, nudged, to_light, own, tests);
+            } else {
+                lit = in_light<MODE>(st, n, sid, nudged, to_light, tests);
+            }
             if (li == 0) lit0 = lit;
             if (MODE == kModeExact) {
                 double litf = lit ? 1.0 : 0.0;

@@ -45,6 +45,7 @@ constexpr double kFilmThickness = 0.3;   // shader.py:53
 struct SceneParams {
     const double* spheres;  // field-major sphere SoA (rt_abi.h), device
     const double* lights;   // n_point_lights x 3, device
+    const unsigned char* accel;  // BVH blob (rt_accel.h) or nullptr: test every sphere
     int n_spheres;
     int n_lights_used;      // 1 unless RT_FLAG_ALL_POINT_LIGHTS
     int n_dome;

@@ -138,11 +138,13 @@ __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p
 
 // Camera rows of one band or interleaved shard (CameraParams): ray generation + trace + stores, one thread per pixel of a
 // patch.  Persistent: the grid is sized to the resident block slots of the GPU.
-template <int MODE, bool STATS, int BLOCK>
+template <int MODE, bool STATS, int BLOCK, bool ACCEL>
 __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS : 1)
     render_rows_kernel(SceneParams sp, CameraParams cp, OutputParams out, Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const Staged st = stage_scene<MODE>(sp, smem, cp.cam);
+    AccelView av = {};
+    if (ACCEL) av = accel_view(sp.accel);
+    const Staged st = ACCEL ? stage_lights_only<MODE>(sp, smem, av) : stage_scene<MODE>(sp, smem, cp.cam);
 
     const int lane = threadIdx.x & 31;
     const int px = lane & (kWarpTileW - 1), py = lane / kWarpTileW;
@@ -170,7 +172,7 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
         if (col < cp.width && local_row < cp.n_rows) {
             const int row = image_row(cp, local_row);
             Vec3 d = primary_direction<MODE>(cp, col, row);
-            Vec3 c = trace_chain<MODE, STATS, true>(sp, st, eye, d, k);
+            Vec3 c = trace_chain<MODE, STATS, !ACCEL, ACCEL>(sp, st, av, eye, d, k);
             store_pixel(out, (long long)(out.image_order ? row : local_row) * cp.width + col, c);
         }
 #ifdef RT_TIMING_DEBUG
@@ -214,11 +216,13 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
 }
 
 // Explicit ray batch, one thread per ray, same work distribution (an item = 32 rays).
-template <int MODE, bool STATS, int BLOCK>
+template <int MODE, bool STATS, int BLOCK, bool ACCEL>
 __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS : 1)
     trace_rays_kernel(SceneParams sp, RayBatch rb, OutputParams out, Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const Staged st = stage_scene<MODE>(sp, smem, sp.eye);
+    AccelView av = {};
+    if (ACCEL) av = accel_view(sp.accel);
+    const Staged st = ACCEL ? stage_lights_only<MODE>(sp, smem, av) : stage_scene<MODE>(sp, smem, sp.eye);
     const int lane = threadIdx.x & 31;
     const unsigned int warp_id = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
     Counters k = {0, 0, 0, 0};
@@ -229,7 +233,7 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
             Vec3 o = {rb.origin0[0], rb.origin0[1], rb.origin0[2]};
             if (rb.origins != nullptr) o = {rb.origins[i], rb.origins[rb.n + i], rb.origins[2 * rb.n + i]};
             Vec3 d = {rb.directions[i], rb.directions[rb.n + i], rb.directions[2 * rb.n + i]};
-            Vec3 c = trace_chain<MODE, STATS, false>(sp, st, o, d, k);
+            Vec3 c = trace_chain<MODE, STATS, false, ACCEL>(sp, st, av, o, d, k);
             store_pixel(out, i, c);
         }
     };

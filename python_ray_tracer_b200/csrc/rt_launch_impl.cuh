@@ -49,7 +49,8 @@ cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParam
                               bool camera = false) {
     if (n_items64 > 0x7ffffff0ull) return cudaErrorInvalidValue;  // 31-bit items (reciprocal division in the kernels)
     const unsigned int n_items = (unsigned int)n_items64;
-    const size_t smem = staged_bytes(sp.n_spheres, sp.n_lights_used);
+    const size_t smem = sp.accel != nullptr ? sizeof(double) * 3 * (size_t)sp.n_lights_used + 16
+                                            : staged_bytes(sp.n_spheres, sp.n_lights_used);
     unsigned int grid = 0;
     cudaError_t err = persistent_grid(kernel, block_threads, smem, n_items, &grid);
     if (err != cudaSuccess) return err;
@@ -78,24 +79,32 @@ cudaError_t render_rows(bool stats, const SceneParams& sp, const CameraParams& c
     const unsigned long long tiles_x = (unsigned long long)(cp.width + kWarpTileW - 1) / kWarpTileW;
     const unsigned long long tiles_y = (unsigned long long)(rows + kWarpTileH - 1) / kWarpTileH;
     const unsigned long long n = tiles_x * tiles_y;
-    if (big_blocks(sp.n_spheres)) {
-        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads>, kBigBlockThreads, sp, cp, out, n, stream, true);
-        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads>, kBigBlockThreads, sp, cp, out, n, stream, true);
+    if (sp.accel != nullptr) {
+        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, true>, kBlockThreads, sp, cp, out, n, stream, true);
+        return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, true>, kBlockThreads, sp, cp, out, n, stream, true);
     }
-    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads>, kBlockThreads, sp, cp, out, n, stream, true);
-    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads>, kBlockThreads, sp, cp, out, n, stream, true);
+    if (big_blocks(sp.n_spheres)) {
+        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads, false>, kBigBlockThreads, sp, cp, out, n, stream, true);
+        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads, false>, kBigBlockThreads, sp, cp, out, n, stream, true);
+    }
+    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, false>, kBlockThreads, sp, cp, out, n, stream, true);
+    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, false>, kBlockThreads, sp, cp, out, n, stream, true);
 }
 
 cudaError_t trace_rays(bool stats, const SceneParams& sp, const RayBatch& rb, const OutputParams& out,
                        cudaStream_t stream) {
     if (rb.n <= 0) return cudaSuccess;
     const unsigned long long n_items = ((unsigned long long)rb.n + 31ull) / 32ull;
-    if (big_blocks(sp.n_spheres)) {
-        if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBigBlockThreads>, kBigBlockThreads, sp, rb, out, n_items, stream);
-        return launch_persistent(trace_rays_kernel<kMode, false, kBigBlockThreads>, kBigBlockThreads, sp, rb, out, n_items, stream);
+    if (sp.accel != nullptr) {
+        if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBlockThreads, true>, kBlockThreads, sp, rb, out, n_items, stream);
+        return launch_persistent(trace_rays_kernel<kMode, false, kBlockThreads, true>, kBlockThreads, sp, rb, out, n_items, stream);
     }
-    if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBlockThreads>, kBlockThreads, sp, rb, out, n_items, stream);
-    return launch_persistent(trace_rays_kernel<kMode, false, kBlockThreads>, kBlockThreads, sp, rb, out, n_items, stream);
+    if (big_blocks(sp.n_spheres)) {
+        if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBigBlockThreads, false>, kBigBlockThreads, sp, rb, out, n_items, stream);
+        return launch_persistent(trace_rays_kernel<kMode, false, kBigBlockThreads, false>, kBigBlockThreads, sp, rb, out, n_items, stream);
+    }
+    if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBlockThreads, false>, kBlockThreads, sp, rb, out, n_items, stream);
+    return launch_persistent(trace_rays_kernel<kMode, false, kBlockThreads, false>, kBlockThreads, sp, rb, out, n_items, stream);
 }
 
 cudaError_t sphere_distance(const RayBatch& rb, const double* c, double radius, double* out,

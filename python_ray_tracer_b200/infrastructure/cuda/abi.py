@@ -12,7 +12,7 @@ import os
 from pathlib import Path
 from typing import Optional, Sequence
 
-RT_ABI_VERSION = 1
+RT_ABI_VERSION = 2
 RT_FARAWAY = 1.0e39
 RT_MAX_DOME_LIGHTS = 8
 RT_STATS_WORDS = 4
@@ -49,6 +49,8 @@ class RtEnv(C.Structure):
         ("flags", C.c_int32),
         ("reserved", C.c_int32),
         ("cutoff", C.c_double),
+        ("accel_dev", C.c_void_p),
+        ("accel_bytes", C.c_int64),
     ]
 
 
@@ -102,6 +104,8 @@ PROTOTYPES = {
     "rt_device_count": (C.c_int, [C.POINTER(C.c_int)]),
     "rt_release_cache": (C.c_int, []),
     "rt_measure_fma_peak": (C.c_int, [C.c_int, C.c_int32, C.POINTER(C.c_double)]),
+    "rt_accel_bytes": (C.c_int64, [C.c_int32]),
+    "rt_accel_build_host": (C.c_int, [_P, C.c_int32, C.POINTER(RtEnv), _P, C.c_int64, C.POINTER(C.c_int64)]),
     "rt_render_rows_dev": (
         C.c_int,
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), C.POINTER(RtCamera), C.c_int32, C.c_int32,

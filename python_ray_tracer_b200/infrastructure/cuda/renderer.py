@@ -129,7 +129,13 @@ class CudaRenderer(Renderer):
     ``all_point_lights``  extension (``main.py:45`` TODO): shade with every point light.
     ``output_dtype``  ``"float64"`` (default, the reference's dtype) or ``"float32"``.
     ``collect_stats``  count rays / hits / generations / sphere tests per launch.
+    ``accel``      ``"auto"`` (default): scenes of at least ``ACCEL_MIN_SPHERES`` shapes get a
+                   bounding-volume tree (``rt_accel_build_host``) so rays skip sphere tests
+                   that provably miss; ``True`` / ``False`` force it on or off.  Results do
+                   not depend on it.
     """
+
+    ACCEL_MIN_SPHERES = 32
 
     def __init__(
         self,
@@ -147,6 +153,7 @@ class CudaRenderer(Renderer):
         collect_stats: bool = False,
         device: int = 0,
         png_compress_level: int = 6,
+        accel: Any = "auto",
     ) -> None:
         if precision not in _PRECISIONS:
             raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}, got {precision!r}")
@@ -171,11 +178,25 @@ class CudaRenderer(Renderer):
         self.collect_stats = bool(collect_stats)
         self.device = int(device)
         self.png_compress_level = int(png_compress_level)
+        if accel not in ("auto", True, False):
+            raise ValueError("accel must be 'auto', True or False")
+        self.accel = accel
+        self._accel_dev = None
         self._scene_key: Optional[bytes] = None
         self._scene_dev: Optional[Tuple[Any, Any]] = None
 
     # ------------------------------------------------------------------ helpers
+    def _wants_accel(self, flat: FlatScene) -> bool:
+        return self.accel is True or (self.accel == "auto" and flat.n_spheres >= self.ACCEL_MIN_SPHERES)
+
     def _env(self, flat: FlatScene, extra_flags: int = 0) -> abi.RtEnv:
+        env = self._plain_env(flat, extra_flags)
+        if self._accel_dev is not None and self._scene_key == flat.key():
+            env.accel_dev = self._accel_dev.data_ptr()
+            env.accel_bytes = self._accel_dev.numel()
+        return env
+
+    def _plain_env(self, flat: FlatScene, extra_flags: int = 0) -> abi.RtEnv:
         return abi.make_env(
             flat.eye,
             len(flat.point_lights),
@@ -198,6 +219,16 @@ class CudaRenderer(Renderer):
             dev = torch.device("cuda", self.device)
             spheres = torch.from_numpy(flat.spheres).to(dev, non_blocking=False)
             lights = torch.from_numpy(flat.point_lights).to(dev, non_blocking=False)
+            self._accel_dev = None
+            if self._wants_accel(flat):
+                lib = abi.load()
+                capacity = int(lib.rt_accel_bytes(flat.n_spheres))
+                blob = np.empty(capacity, dtype=np.uint8)
+                used = C.c_int64(0)
+                env = self._plain_env(flat)
+                abi.check(lib.rt_accel_build_host(flat.spheres.ctypes.data, flat.n_spheres, C.byref(env),
+                                                  blob.ctypes.data, capacity, C.byref(used)), "rt_accel_build_host")
+                self._accel_dev = torch.from_numpy(blob[: used.value]).to(dev, non_blocking=False)
             self._scene_key, self._scene_dev = key, (spheres, lights)
         return self._scene_dev
 

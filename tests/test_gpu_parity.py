@@ -269,12 +269,12 @@ def test_edge_cases(rt, c_oracle):
     want, _ = c_oracle.render(case.flat, case.width, case.height, max_depth=8, all_point_lights=True)
     assert_linear_parity(got, want, EXACT_TOL, "all point lights")
     assert np.abs(got - case.rgb).max() > 1e-3  # and it does change the picture
-    # too many spheres for one block's shared memory -> loud error, no fallback
+    # too many spheres for one block's shared memory and no tree -> loud error, no fallback
     from python_ray_tracer_b200.infrastructure.flatten import FlatScene
 
     big = FlatScene(np.ones((12, 20000)), case.flat.point_lights, case.flat.eye, [0.1], (1.0, 1.0, 1.0))
     with pytest.raises(RuntimeError):
-        renderer.render_rows(big, _camera(case), 0, 1)
+        rt("exact", accel=False).render_rows(big, _camera(case), 0, 1)
 
 
 def test_quantize_kernel_bit_exact(rt, c_oracle):
@@ -406,3 +406,63 @@ def test_turntable_batch_writes_reference_frames(rt, c_oracle, tmp_path):
     assert_png_parity(got, c_oracle.quantize(case.rgb), "turntable frame 37")
     again = turntable.render_turntable(renderer, 256, tmp_path, 160, 90, rank=37, world=64, encoder_threads=4)
     assert again["frames"] == 0 and again["skipped"] == 4
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_bvh_gives_the_same_picture_as_testing_every_sphere(precision, c_oracle):
+    """rt_env.accel_dev: the tree only skips sphere tests that miss, so frames, 8-bit images
+    and ray / hit / depth counters are identical to the exhaustive kernels', bit for bit --
+    on the 49- and 1025-shape scenes, on every stress scene (forced on tiny scenes too), with
+    explicit rays, strips and the all-lights extension -- and equal to the reference fixtures."""
+    from python_ray_tracer_b200.infrastructure import CudaRenderer, NumpyVector3D
+    from python_ray_tracer_b200.infrastructure.cuda import sharding
+
+    def pair(**kw):
+        return (CudaRenderer(precision=precision, collect_stats=True, accel=False, **kw),
+                CudaRenderer(precision=precision, collect_stats=True, accel=True, **kw))
+
+    tol = EXACT_TOL if precision == "exact" else 1e-4
+    names = ["c3_small_48_192x108", "c3_small_48_192x108_depth8", "c3_small_48_192x108_depth1", "readme_160x90",
+             "main_160x90", "readme_1x7"] + [f"{n}_48x27" for n in __import__("_cases").STRESS_CASES]
+    for name in names:
+        case = load_case(name)
+        plain, tree = pair(max_depth=case.max_depth or None)
+        a, b = _render(plain, case), _render(tree, case)
+        assert np.array_equal(a.numpy(), b.numpy()), name
+        assert np.array_equal(a.rgba8.cpu().numpy(), b.rgba8.cpu().numpy()), name
+        ca, cb = a.counters(), b.counters()
+        assert (ca["rays_traced"], ca["hits_shaded"], ca["generations"]) == (cb["rays_traced"], cb["hits_shaded"], cb["generations"]), name
+        assert cb["sphere_tests"] <= ca["sphere_tests"] + ca["rays_traced"] + ca["hits_shaded"], name
+        assert_linear_parity(b.numpy(), case.rgb, tol, f"{name}/{precision} with the tree vs reference fixture")
+    # config 3 at size: 1025 shapes, 4K, depth 8 -- a band, the reference's pixel subset, strips
+    case = load_case("c3_1024_4k_subset_depth8")
+    plain, tree = pair(max_depth=8)
+    a, b = _render(plain, case, rows=(1400, 1408)), _render(tree, case, rows=(1400, 1408))
+    assert np.array_equal(a.numpy(), b.numpy())
+    assert b.counters()["sphere_tests"] * 8 < a.counters()["sphere_tests"]  # and it does skip most of them
+    d = c_oracle.ray_directions(case.flat.eye, case.width, case.height, case.pixels)
+    rays = tree.trace_rays(case.flat, NumpyVector3D(*case.flat.eye), NumpyVector3D(d[0], d[1], d[2]))
+    assert_linear_parity(rays.numpy(), case.rgb, tol, f"c3 subset/{precision} with the tree")
+    shard = sharding.StripShard(case.height, 64, 5, 16)
+    assert np.array_equal(plain.render_strips(case.flat, _camera(case), shard).numpy(),
+                          tree.render_strips(case.flat, _camera(case), shard).numpy())
+    # the all-lights extension walks the tree once per light
+    case = load_case("c3_small_48_192x108_depth8")
+    plain, tree = pair(max_depth=8, all_point_lights=True)
+    assert np.array_equal(_render(plain, case).numpy(), _render(tree, case).numpy())
+
+
+def test_bvh_lifts_the_shared_memory_limit(rt, c_oracle):
+    """4 000 spheres do not fit one block's shared memory: without a tree the call is refused,
+    with one (the default for large scenes) it renders and matches the oracle."""
+    from python_ray_tracer_b200 import scenes
+    from python_ray_tracer_b200.infrastructure import CudaRenderer
+    from python_ray_tracer_b200.infrastructure.flatten import DefaultMaterial, flatten_scene
+
+    scene = scenes.random_spheres_scene(96, 54, n_spheres=4000, seed=5)
+    flat = flatten_scene(scene, DefaultMaterial(**scenes.README_GAINS))
+    with pytest.raises(RuntimeError):
+        CudaRenderer(precision="fast", accel=False, max_depth=4).render_rows(flat, scene.camera, 0, 54)
+    got = CudaRenderer(precision="fast", max_depth=4).render_rows(flat, scene.camera, 0, 54).numpy()
+    want, _ = c_oracle.render(flat, 96, 54, max_depth=4)
+    assert_linear_parity(got, want, 1e-4, "4001 shapes through the tree")

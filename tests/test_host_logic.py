@@ -173,7 +173,7 @@ def test_abi_library_exports_every_declared_symbol():
         assert hasattr(lib, name), name
     assert lib.rt_abi_version() == abi.RT_ABI_VERSION
     # struct layouts the header promises
-    assert ctypes.sizeof(abi.RtCamera) == 32 and ctypes.sizeof(abi.RtEnv) == 144
+    assert ctypes.sizeof(abi.RtCamera) == 32 and ctypes.sizeof(abi.RtEnv) == 160
 
 
 def test_ctypes_structs_match_the_header_as_compiled(tmp_path):
@@ -256,3 +256,63 @@ def test_new_entry_points_reject_bad_arguments_without_a_gpu():
     assert lib.rt_peer_buffer_create(0, 64, None, handle) == -1
     assert lib.rt_peer_buffer_open(0, None, ctypes.byref(ptr)) == -1
     assert lib.rt_peer_buffer_close(0, None) == 0 and lib.rt_peer_buffer_destroy(0, None) == 0
+
+
+def _parse_accel(blob: bytes):
+    import struct
+
+    magic, n, n_nodes, n_tree, n_large, _ = struct.unpack_from("<Iiiiii", blob, 0)
+    offs = struct.unpack_from("<7q", blob, 24)
+    local_bound, gain_bound = struct.unpack_from("<2d", blob, 24 + 56)
+    off_nodes, off_order, off_leaf, off_geom, off_aux, off_large, total = offs
+    nodes = np.frombuffer(blob, dtype=np.dtype([("lo", "<f8", 3), ("hi", "<f8", 3), ("first", "<i4"), ("count", "<i4"), ("pad", "<i8")]),
+                          count=n_nodes, offset=off_nodes)
+    order = np.frombuffer(blob, dtype="<i4", count=n_tree, offset=off_order)
+    leaf_geom = np.frombuffer(blob, dtype="<f8", count=4 * n_tree, offset=off_leaf).reshape(-1, 4)
+    geom = np.frombuffer(blob, dtype="<f8", count=4 * n, offset=off_geom).reshape(-1, 4)
+    aux = np.frombuffer(blob, dtype="<f8", count=2 * n, offset=off_aux).reshape(-1, 2)
+    large = np.frombuffer(blob, dtype="<i4", count=n_large, offset=off_large)
+    return dict(magic=magic, n=n, nodes=nodes, order=order, leaf_geom=leaf_geom, geom=geom, aux=aux, large=large,
+                total=total, local_bound=local_bound, gain_bound=gain_bound)
+
+
+@pytest.mark.parametrize("n_spheres", [1, 2, 5, 48, 1024])
+def test_accel_blob_is_a_valid_tree(n_spheres):
+    """rt_accel_build_host: every shape is in exactly one leaf slot or in the always-tested
+    list, every node's box contains the boxes of everything below it, records equal the table."""
+    from python_ray_tracer_b200 import scenes
+    from python_ray_tracer_b200.infrastructure.flatten import DefaultMaterial, flatten_scene
+
+    lib = abi.load()
+    flat = flatten_scene(scenes.random_spheres_scene(64, 36, n_spheres=n_spheres, seed=77), DefaultMaterial())
+    n = flat.n_spheres  # + the ground sphere
+    env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, mode=abi.RT_MODE_FAST)
+    cap = int(lib.rt_accel_bytes(n))
+    buf = np.zeros(cap, dtype=np.uint8)
+    used = ctypes.c_int64(0)
+    assert lib.rt_accel_build_host(flat.spheres.ctypes.data, n, ctypes.byref(env), buf.ctypes.data, cap, ctypes.byref(used)) == 0
+    assert lib.rt_accel_build_host(flat.spheres.ctypes.data, n, ctypes.byref(env), buf.ctypes.data, 64, ctypes.byref(used)) == -1
+    a = _parse_accel(buf[: used.value].tobytes())
+    assert a["magic"] == 0x52544256 and a["n"] == n and a["total"] == used.value <= cap
+    assert sorted(a["order"].tolist() + a["large"].tolist()) == list(range(n))
+    if n > 2:
+        assert (n - 1) in a["large"].tolist()  # the radius-99999 ground stays out of the tree
+    c, r = flat.spheres[0:3].T, np.abs(flat.spheres[3])
+    assert np.array_equal(a["geom"][:, :3], c) and np.array_equal(a["geom"][:, 3], flat.spheres[3] ** 2)
+    assert np.array_equal(a["leaf_geom"], a["geom"][a["order"]]) and np.array_equal(a["aux"][:, 0], 1.0 / flat.spheres[3])
+    assert a["gain_bound"] == np.abs(flat.spheres[5]).max() and a["local_bound"] > 0
+
+    def check(node):  # returns the shapes below `node`
+        nd = a["nodes"][node]
+        if nd["count"] > 0:
+            shapes = a["order"][nd["first"]: nd["first"] + nd["count"]].tolist()
+            assert 1 <= nd["count"] <= 4
+        else:
+            assert nd["count"] in (-1, -2, -3)
+            shapes = check(nd["first"]) + check(nd["first"] + 1)
+        lo, hi = (c[shapes] - r[shapes, None]).min(axis=0), (c[shapes] + r[shapes, None]).max(axis=0)
+        assert (nd["lo"] < lo).all() and (nd["hi"] > hi).all()
+        return shapes
+
+    if len(a["nodes"]):
+        assert sorted(check(0)) == sorted(a["order"].tolist())

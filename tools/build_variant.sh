@@ -11,7 +11,7 @@ mkdir -p "$out"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function --expt-relaxed-constexpr"
 pids=()
-for f in trace_exact trace_fast rt_abi rt_abi_host rt_peaks; do
+for f in trace_exact trace_fast rt_abi rt_abi_host rt_peaks rt_accel_build; do
   extra=""; [ "$f" = trace_exact ] && extra="-fmad=false"
   $NVCC $FLAGS $extra "$@" -c "$src/$f.cu" -o "$out/$f.o" &
   pids+=($!)
