@@ -109,6 +109,8 @@ typedef enum rt_flags {
     RT_FLAG_ALL_POINT_LIGHTS = 1, /* extension (main.py:45 TODO): sum diffuse/specular and
                                     shadow over every point light.  Off = reference
                                     semantics: only lights[0] shades (shader.py:75).     */
+    RT_FLAG_NO_ACCEL = 4,         /* host-buffer entry points only: never build the tree
+                                    themselves (see RT_ACCEL_AUTO_SPHERES)               */
     RT_FLAG_IMAGE_ORDER = 2       /* rt_render_rows_dev / rt_render_strips_dev: rgb_dev and
                                     rgba8_dev are WHOLE frames (height x width) and every
                                     pixel is stored at row*width + col, whatever rows the
@@ -157,6 +159,10 @@ int rt_measure_fma_peak(int device, int32_t dtype, double* flops_out);
  *   env                dome lights and mode of the render calls the blob will serve (it
  *                      carries the material bound of the fast policy's chain cut-off)
  */
+#define RT_ACCEL_AUTO_SPHERES 64 /* measured break-even on B200 (profiles/r01/accel_sweep.txt):
+                                   the host-buffer entry points build and upload the tree
+                                   themselves for scenes at least this large when
+                                   env->accel_dev is NULL and RT_FLAG_NO_ACCEL is not set */
 int64_t rt_accel_bytes(int32_t n_spheres);
 int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_env* env,
                         void* blob_out, int64_t capacity, int64_t* bytes_out);

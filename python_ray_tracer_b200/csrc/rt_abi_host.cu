@@ -8,6 +8,7 @@
 
 #include <cstdio>
 #include <cstring>
+#include <vector>
 
 #include "../../include/rt_abi.h"
 #include "rt_launch.h"
@@ -27,7 +28,7 @@ struct DeviceCache {
     cudaStream_t stream = nullptr;       // uploads and kernels
     cudaStream_t copy_stream = nullptr;  // downloads, overlapped with the next chunk's kernel
     cudaEvent_t rendered[kMaxChunks] = {};
-    Scratch scene, rays, rgb, rgb8, stats;
+    Scratch scene, rays, rgb, rgb8, stats, accel;
 };
 
 thread_local DeviceCache g_cache[kMaxDevices];
@@ -88,6 +89,26 @@ int upload_scene(DeviceCache& c, const double* spheres_host, int32_t n_spheres, 
     return RT_OK;
 }
 
+// Scenes of RT_ACCEL_AUTO_SPHERES shapes or more get a bounding-volume tree unless the caller
+// brought one (env->accel_dev) or opted out (RT_FLAG_NO_ACCEL): built here on the host, uploaded
+// on the call's stream, named in `*use` (a copy of the caller's env).
+int attach_accel(DeviceCache& c, const double* spheres_host, int32_t n_spheres, const rt_env* env, rt_env* use) {
+    *use = *env;
+    if (env->accel_dev != nullptr || (env->flags & RT_FLAG_NO_ACCEL) || n_spheres < RT_ACCEL_AUTO_SPHERES) return RT_OK;
+    thread_local std::vector<unsigned char> blob;
+    const int64_t capacity = rt_accel_bytes(n_spheres);
+    if ((int64_t)blob.size() < capacity) blob.resize((size_t)capacity);
+    int64_t used = 0;
+    const int rc = rt_accel_build_host(spheres_host, n_spheres, env, blob.data(), capacity, &used);
+    if (rc != RT_OK) return host_fail(rc, "host entry point: building the sphere tree failed");
+    HOST_CUDA(reserve(c.accel, (size_t)used));
+    // pageable source: the copy is staged before the call returns, so `blob` may be reused
+    HOST_CUDA(cudaMemcpyAsync(c.accel.ptr, blob.data(), (size_t)used, cudaMemcpyHostToDevice, c.stream));
+    use->accel_dev = c.accel.ptr;
+    use->accel_bytes = used;
+    return RT_OK;
+}
+
 int enter(int device, Restore& restore, DeviceCache** cache) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return host_fail(RT_ERR_NO_DEVICE, "host entry point: no CUDA device or device index out of range");
@@ -123,6 +144,7 @@ int rt_release_cache(void) {
         release(c.rgb);
         release(c.rgb8);
         release(c.stats);
+        release(c.accel);
         if (c.stream != nullptr) {
             cudaStreamDestroy(c.stream);
             cudaStreamDestroy(c.copy_stream);
@@ -148,6 +170,9 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
 
     const double *spheres_dev, *lights_dev;
     if ((rc = upload_scene(*c, spheres_host, n_spheres, point_lights_host, env->n_point_lights, &spheres_dev, &lights_dev)) != RT_OK) return rc;
+    rt_env with_tree;
+    if ((rc = attach_accel(*c, spheres_host, n_spheres, env, &with_tree)) != RT_OK) return rc;
+    env = &with_tree;
     const int64_t n = (int64_t)(row1 - row0) * cam->width;
     const size_t elem = rgb_dtype == RT_DTYPE_F64 ? 8 : 4;
     // the quantiser reads the linear planes, so they are rendered even if only bytes are wanted
@@ -216,6 +241,9 @@ int rt_trace_rays_host(int device, const double* spheres_host, int32_t n_spheres
 
     const double *spheres_dev, *lights_dev;
     if ((rc = upload_scene(*c, spheres_host, n_spheres, point_lights_host, env->n_point_lights, &spheres_dev, &lights_dev)) != RT_OK) return rc;
+    rt_env with_tree;
+    if ((rc = attach_accel(*c, spheres_host, n_spheres, env, &with_tree)) != RT_OK) return rc;
+    env = &with_tree;
     const size_t plane = sizeof(double) * 3 * (size_t)n_rays;
     HOST_CUDA(reserve(c->rays, 2 * plane + 16));
     double* dirs_dev = static_cast<double*>(c->rays.ptr);

@@ -135,7 +135,7 @@ class CudaRenderer(Renderer):
                    not depend on it.
     """
 
-    ACCEL_MIN_SPHERES = 32
+    ACCEL_MIN_SPHERES = abi.RT_ACCEL_AUTO_SPHERES  # measured break-even (profiles/r01/accel_sweep.txt)
 
     def __init__(
         self,

@@ -200,6 +200,29 @@ def test_host_buffer_entry_points(c_oracle):
                                 None, ptr(d), n, ptr(out), abi.RT_DTYPE_F64, None)
     abi.check(rc, "rt_trace_rays_host")
     assert_linear_parity(out, want, EXACT_TOL, "host rays")
+    # scenes of RT_ACCEL_AUTO_SPHERES shapes or more: the entry points build the tree themselves
+    big = load_case("c3_1024_4k_subset_depth8")
+    assert big.flat.n_spheres >= abi.RT_ACCEL_AUTO_SPHERES
+    bcam = abi.make_camera(big.flat.eye, big.width, big.height)
+    outs = []
+    for flags in (abi.RT_FLAG_NONE, abi.RT_FLAG_NO_ACCEL):
+        benv = abi.make_env(big.flat.eye, len(big.flat.point_lights), big.flat.dome_intensity, big.flat.dome_color,
+                            max_depth=8, mode=abi.RT_MODE_FAST, flags=flags, cutoff=1e-7)
+        band = np.empty((3, 8 * big.width), dtype=np.float64)
+        st = np.zeros(4, dtype=np.uint64)
+        abi.check(lib.rt_render_frame_host(0, ptr(big.flat.spheres), big.flat.n_spheres, ptr(big.flat.point_lights),
+                                           C.byref(benv), C.byref(bcam), 1400, 1408, ptr(band), abi.RT_DTYPE_F64, None,
+                                           ptr(st)), "rt_render_frame_host (auto tree)")
+        db = c_oracle.ray_directions(big.flat.eye, big.width, big.height, big.pixels)
+        rays = np.empty((3, db.shape[1]), dtype=np.float64)
+        eye = (C.c_double * 3)(*big.flat.eye)
+        abi.check(lib.rt_trace_rays_host(0, ptr(big.flat.spheres), big.flat.n_spheres, ptr(big.flat.point_lights),
+                                         C.byref(benv), None, eye, ptr(db), db.shape[1], ptr(rays), abi.RT_DTYPE_F64,
+                                         None), "rt_trace_rays_host (auto tree)")
+        assert_linear_parity(rays, big.rgb, 1e-4, "host rays, 1025 shapes")
+        outs.append((band, rays, st.copy()))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    assert tuple(outs[0][2][:3]) == tuple(outs[1][2][:3]) and outs[0][2][3] * 8 < outs[1][2][3]
     # bad arguments fail loudly
     assert lib.rt_render_frame_host(0, None, 3, None, C.byref(env), C.byref(cam), 0, h, None, 0, None, None) == -1
     assert lib.rt_render_frame_host(99, ptr(flat.spheres), flat.n_spheres, ptr(flat.point_lights), C.byref(env),
