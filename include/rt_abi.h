@@ -159,7 +159,7 @@ int rt_measure_fma_peak(int device, int32_t dtype, double* flops_out);
  *   env                dome lights and mode of the render calls the blob will serve (it
  *                      carries the material bound of the fast policy's chain cut-off)
  */
-#define RT_ACCEL_AUTO_SPHERES 64 /* measured break-even on B200 (profiles/r01/accel_sweep.txt):
+#define RT_ACCEL_AUTO_SPHERES 32 /* measured break-even on B200 (profiles/r01/accel_sweep.txt):
                                    the host-buffer entry points build and upload the tree
                                    themselves for scenes at least this large when
                                    env->accel_dev is NULL and RT_FLAG_NO_ACCEL is not set */

@@ -21,6 +21,7 @@ struct AccelView {
     const int* large;
     int n_nodes, n_large;
     double local_bound, gain_bound;
+    float extent;
 };
 
 __device__ __forceinline__ AccelView accel_view(const unsigned char* blob) {
@@ -36,6 +37,7 @@ __device__ __forceinline__ AccelView accel_view(const unsigned char* blob) {
     v.n_large = h->n_large;
     v.local_bound = h->local_bound;
     v.gain_bound = h->gain_bound;
+    v.extent = h->extent;
     return v;
 }
 
@@ -53,31 +55,58 @@ __device__ __forceinline__ double accel_sphere_t(Vec3 o, Vec3 d, const SphereGeo
     return can_hit(q) ? near_root(q) : kMiss;
 }
 
+// ---- the slab test: FP32, conservative ------------------------------------------------------
+// FP64 min/max cost ~8 instructions each on sm_100a (NaN rules emulated), and a slab test needs a
+// dozen: in FP64 it was half of all instructions the tree kernels issued.  In FP32 it is one
+// FMNMX each -- but the test may then never reject a box the FP64 sphere test would hit in.
+//
+// Per axis, with A = plane - origin and t = A / d:   computed t_lo must not exceed the true
+// one, computed t_hi must not fall below it (whatever the sign of d, that is "A_lo too small,
+// A_hi too large").  Roundings on the way: origin to FP32 (2^-24 |o|), the subtraction
+// (2^-24 (|plane| + |o|)), 1/d (float(d), then an FP32 division: 2^-23) and the product (2^-24);
+// relative errors of t are relative errors of A, and |A| <= |o| + extent.  All of it is below
+// 2^-21 (|o| + extent); the origin is shifted by eps = 2^-20 (|o|_max + extent) towards each
+// plane, twice that.  Boxes are already rounded outward by the builder.
+//   d = +-0 (or below FP32 range): 1/d = +-inf, t = +-inf with the right sign, or NaN when A is
+//   exactly 0, which FMNMX drops (that axis then does not constrain: the origin is in the slab).
+//   Overflow to +-inf keeps the sign; comparisons are written so that inf never rejects a box
+//   the limit would admit.
 struct RaySlabs {
-    Vec3 o, inv;  // origin and 1/direction (IEEE division: a zero component gives +-inf)
+    float lox, loy, loz;  // origin + eps: subtracted from the low planes
+    float hix, hiy, hiz;  // origin - eps: subtracted from the high planes
+    float ix, iy, iz;     // 1 / direction
 };
-__device__ __forceinline__ RaySlabs ray_slabs(Vec3 o, Vec3 d) { return {o, {1.0 / d.x, 1.0 / d.y, 1.0 / d.z}}; }
-
-// does the ray enter the box before `limit`?  fmin/fmax drop the NaN of 0 * inf
-__device__ __forceinline__ bool slab_hit(const RaySlabs& r, const AccelNode& n, double limit) {
-    const double ax = (n.lo[0] - r.o.x) * r.inv.x, bx = (n.hi[0] - r.o.x) * r.inv.x;
-    const double ay = (n.lo[1] - r.o.y) * r.inv.y, by = (n.hi[1] - r.o.y) * r.inv.y;
-    const double az = (n.lo[2] - r.o.z) * r.inv.z, bz = (n.hi[2] - r.o.z) * r.inv.z;
-    const double t_near = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmin(az, bz));
-    const double t_far = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
-    return t_far >= fmax(t_near, 0.0) && t_near < limit;
+__device__ __forceinline__ RaySlabs ray_slabs(Vec3 o, Vec3 d, float extent) {
+    const float ox = __double2float_rn(o.x), oy = __double2float_rn(o.y), oz = __double2float_rn(o.z);
+    const float reach = fmaxf(fmaxf(fabsf(ox), fabsf(oy)), fabsf(oz)) + extent;
+    const float eps = fmaf(reach, 9.5367431640625e-07f, 1e-30f);  // 2^-20
+    RaySlabs r;
+    r.lox = ox + eps, r.loy = oy + eps, r.loz = oz + eps;
+    r.hix = ox - eps, r.hiy = oy - eps, r.hiz = oz - eps;
+    r.ix = 1.0f / __double2float_rn(d.x);
+    r.iy = 1.0f / __double2float_rn(d.y);
+    r.iz = 1.0f / __double2float_rn(d.z);
+    return r;
 }
 
-__device__ __forceinline__ AccelNode ldg_node(const AccelNode* p) {
-    AccelNode n;
-    const double2* q = reinterpret_cast<const double2*>(p);
-    const double2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
-    const int4 t = __ldg(reinterpret_cast<const int4*>(p) + 3);
-    n.lo[0] = a.x, n.lo[1] = a.y, n.lo[2] = b.x;
-    n.hi[0] = b.y, n.hi[1] = c.x, n.hi[2] = c.y;
-    n.first = t.x;
-    n.count = t.y;
-    return n;
+struct NodeView {
+    float lox, loy, loz, hix, hiy, hiz;
+    int first, count;
+};
+__device__ __forceinline__ NodeView ldg_node(const AccelNode* p) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    return {a.x, a.y, a.z, a.w, b.x, b.y, __float_as_int(b.z), __float_as_int(b.w)};
+}
+
+// may the ray meet the box at a distance in (0, limit]?  (limit rounded up from the FP64 one)
+__device__ __forceinline__ bool slab_hit(const RaySlabs& r, const NodeView& n, float limit) {
+    const float ax = (n.lox - r.lox) * r.ix, bx = (n.hix - r.hix) * r.ix;
+    const float ay = (n.loy - r.loy) * r.iy, by = (n.hiy - r.hiy) * r.iy;
+    const float az = (n.loz - r.loz) * r.iz, bz = (n.hiz - r.hiz) * r.iz;
+    const float t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), limit));
+    return !(t_near > t_far);
 }
 
 // Nearest hit (base.py:97-105): smallest t, lowest shape index among equal t.
@@ -96,13 +125,13 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
     }
     evaluated += (unsigned long long)av.n_large;
     if (av.n_nodes == 0) return;
-    const RaySlabs ray = ray_slabs(o, d);
+    const RaySlabs ray = ray_slabs(o, d, av.extent);
     int stack[kAccelStack];
     int top = 0, node = 0;
     while (true) {
-        const AccelNode n = ldg_node(av.nodes + node);
+        const NodeView n = ldg_node(av.nodes + node);
         bool descend = false;
-        if (slab_hit(ray, n, tmin)) {
+        if (slab_hit(ray, n, __double2float_ru(tmin))) {
             if (n.count > 0) {
                 for (int k = 0; k < n.count; ++k) {
                     const int slot = n.first + k;
@@ -141,13 +170,14 @@ __device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, V
     }
     evaluated += (unsigned long long)av.n_large;
     if (av.n_nodes == 0) return false;
-    const RaySlabs ray = ray_slabs(p, l);
+    const RaySlabs ray = ray_slabs(p, l, av.extent);
+    const float own_limit = __double2float_ru(own);
     int stack[kAccelStack];
     int top = 0, node = 0;
     while (true) {
-        const AccelNode n = ldg_node(av.nodes + node);
+        const NodeView n = ldg_node(av.nodes + node);
         bool descend = false;
-        if (slab_hit(ray, n, own)) {
+        if (slab_hit(ray, n, own_limit)) {
             if (n.count > 0) {
                 for (int k = 0; k < n.count; ++k) {
                     const int slot = n.first + k;

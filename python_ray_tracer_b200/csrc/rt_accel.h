@@ -25,6 +25,7 @@ constexpr uint32_t kAccelMagic = 0x52544256u;  // "RTBV"
 constexpr int kAccelLeafSize = 4;
 constexpr int kAccelMaxLarge = 16;
 constexpr int kAccelStack = 48;
+constexpr double kAccelMaxCoordinate = 1e30;  // beyond this FP32 boxes would overflow: builder refuses
 
 struct AccelHeader {
     uint32_t magic;
@@ -37,13 +38,16 @@ struct AccelHeader {
     int64_t bytes;
     double local_bound;  // sup over materials of |local colour| (material_bound(), rt_chain.cuh)
     double gain_bound;   // sup over materials of |specular_gain|
+    float extent;        // sup of |box coordinate| over the tree (scales the slab test's margin)
+    float reserved2[3];
 };
 
-// 64 bytes.  Boxes are the union of the spheres' boxes, grown by a relative 1e-9 so that a ray
-// the exact FP64 sphere test accepts is never rejected by the slab test's own rounding.
+// 32 bytes.  Boxes are the union of the spheres' FP64 boxes rounded OUTWARD to FP32.  The slab
+// test runs in FP32 against an origin shifted by a per-ray margin that bounds every rounding
+// in it (rt_accel.cuh: ray_slabs), so a ray the FP64 sphere test accepts is never rejected.
 struct alignas(16) AccelNode {
-    double lo[3];
-    double hi[3];
+    float lo[3];
+    float hi[3];
     int32_t first;   // inner: index of the left child (right = first + 1); leaf: first leaf slot
     int32_t count;   // inner: -(split axis + 1); leaf: number of slots (1..kAccelLeafSize)
 };

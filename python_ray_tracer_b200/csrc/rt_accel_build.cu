@@ -26,7 +26,20 @@ struct Builder {
     double centre(int s, int axis) const { return f[(size_t)axis * n + s]; }
     double radius(int s) const { return std::fabs(f[(size_t)RT_F_RADIUS * n + s]); }
 
-    void bounds(int begin, int end, double* lo, double* hi) const {
+    // largest float <= x / smallest float >= x, then one more step outward
+    static float round_down(double x) {
+        float f = (float)x;
+        if ((double)f > x) f = std::nextafterf(f, -INFINITY);
+        return std::nextafterf(f, -INFINITY);
+    }
+    static float round_up(double x) {
+        float f = (float)x;
+        if ((double)f < x) f = std::nextafterf(f, INFINITY);
+        return std::nextafterf(f, INFINITY);
+    }
+
+    void bounds(int begin, int end, float* lo_out, float* hi_out) const {
+        double lo[3], hi[3];
         for (int a = 0; a < 3; ++a) {
             lo[a] = INFINITY;
             hi[a] = -INFINITY;
@@ -39,11 +52,10 @@ struct Builder {
                 hi[a] = std::max(hi[a], centre(s, a) + r);
             }
         }
-        // grow: the slab test rounds, the sphere test must never be pre-empted by it
+        // c -+ r rounds in FP64 (relative 1e-16); the outward FP32 rounding covers it a millionfold
         for (int a = 0; a < 3; ++a) {
-            const double pad = 1e-9 * (std::fabs(lo[a]) + std::fabs(hi[a]) + (hi[a] - lo[a])) + 1e-300;
-            lo[a] -= pad;
-            hi[a] += pad;
+            lo_out[a] = round_down(lo[a]);
+            hi_out[a] = round_up(hi[a]);
         }
     }
 
@@ -121,6 +133,11 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
         return RT_ERR_BAD_ARG;
     if (capacity < rt_accel_bytes(n_spheres)) return RT_ERR_BAD_ARG;
     const int n = n_spheres;
+    for (int s = 0; s < n; ++s) {
+        double reach = std::fabs(spheres_host[(size_t)RT_F_RADIUS * n + s]);
+        for (int a = 0; a < 3; ++a) reach = std::max(reach, std::fabs(spheres_host[(size_t)a * n + s]));
+        if (!(reach <= rt::kAccelMaxCoordinate)) return RT_ERR_UNSUPPORTED;  // (NaN lands here too)
+    }
     Builder b;
     b.f = spheres_host;
     b.n = n;
@@ -172,6 +189,10 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
     }
     h.local_bound = lmax;
     h.gain_bound = gmax;
+    float extent = 0.0f;
+    for (const AccelNode& nd : b.nodes)
+        for (int a = 0; a < 3; ++a) extent = std::max(extent, std::max(std::fabs(nd.lo[a]), std::fabs(nd.hi[a])));
+    h.extent = extent;
 
     char* base = static_cast<char*>(blob_out);
     memset(base, 0, off);

@@ -264,8 +264,9 @@ def _parse_accel(blob: bytes):
     magic, n, n_nodes, n_tree, n_large, _ = struct.unpack_from("<Iiiiii", blob, 0)
     offs = struct.unpack_from("<7q", blob, 24)
     local_bound, gain_bound = struct.unpack_from("<2d", blob, 24 + 56)
+    (extent,) = struct.unpack_from("<f", blob, 24 + 56 + 16)
     off_nodes, off_order, off_leaf, off_geom, off_aux, off_large, total = offs
-    nodes = np.frombuffer(blob, dtype=np.dtype([("lo", "<f8", 3), ("hi", "<f8", 3), ("first", "<i4"), ("count", "<i4"), ("pad", "<i8")]),
+    nodes = np.frombuffer(blob, dtype=np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("first", "<i4"), ("count", "<i4")]),
                           count=n_nodes, offset=off_nodes)
     order = np.frombuffer(blob, dtype="<i4", count=n_tree, offset=off_order)
     leaf_geom = np.frombuffer(blob, dtype="<f8", count=4 * n_tree, offset=off_leaf).reshape(-1, 4)
@@ -273,7 +274,7 @@ def _parse_accel(blob: bytes):
     aux = np.frombuffer(blob, dtype="<f8", count=2 * n, offset=off_aux).reshape(-1, 2)
     large = np.frombuffer(blob, dtype="<i4", count=n_large, offset=off_large)
     return dict(magic=magic, n=n, nodes=nodes, order=order, leaf_geom=leaf_geom, geom=geom, aux=aux, large=large,
-                total=total, local_bound=local_bound, gain_bound=gain_bound)
+                total=total, local_bound=local_bound, gain_bound=gain_bound, extent=extent)
 
 
 @pytest.mark.parametrize("n_spheres", [1, 2, 5, 48, 1024])
@@ -311,8 +312,15 @@ def test_accel_blob_is_a_valid_tree(n_spheres):
             assert nd["count"] in (-1, -2, -3)
             shapes = check(nd["first"]) + check(nd["first"] + 1)
         lo, hi = (c[shapes] - r[shapes, None]).min(axis=0), (c[shapes] + r[shapes, None]).max(axis=0)
-        assert (nd["lo"] < lo).all() and (nd["hi"] > hi).all()
+        # FP32 boxes, rounded outward: strictly outside the FP64 box, by no more than a few ulp
+        assert (nd["lo"].astype(np.float64) < lo).all() and (nd["hi"].astype(np.float64) > hi).all()
+        assert (np.nextafter(np.nextafter(np.nextafter(nd["lo"], np.float32(np.inf)), np.float32(np.inf)), np.float32(np.inf)).astype(np.float64) > lo).all()
+        assert a["extent"] >= np.abs(nd["lo"]).max() and a["extent"] >= np.abs(nd["hi"]).max()
         return shapes
 
     if len(a["nodes"]):
         assert sorted(check(0)) == sorted(a["order"].tolist())
+    # coordinates FP32 boxes cannot hold: refused, never silently clamped
+    far = flat.spheres.copy()
+    far[0, 0] = 1e31
+    assert lib.rt_accel_build_host(far.ctypes.data, n, ctypes.byref(env), buf.ctypes.data, cap, ctypes.byref(used)) == -4  # RT_ERR_UNSUPPORTED
