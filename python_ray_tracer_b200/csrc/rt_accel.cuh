@@ -99,17 +99,28 @@ __device__ __forceinline__ NodeView ldg_node(const AccelNode* p) {
     return {a.x, a.y, a.z, a.w, b.x, b.y, __float_as_int(b.z), __float_as_int(b.w)};
 }
 
-// may the ray meet the box at a distance in (0, limit]?  (limit rounded up from the FP64 one)
-__device__ __forceinline__ bool slab_hit(const RaySlabs& r, const NodeView& n, float limit) {
+// Distance at which the ray enters the box (0 if it starts inside); `hit` = it may meet the box
+// at a distance in (0, limit]  (limit rounded up from the FP64 one).
+__device__ __forceinline__ float slab_enter(const RaySlabs& r, const NodeView& n, float limit, bool& hit) {
     const float ax = (n.lox - r.lox) * r.ix, bx = (n.hix - r.hix) * r.ix;
     const float ay = (n.loy - r.loy) * r.iy, by = (n.hiy - r.hiy) * r.iy;
     const float az = (n.loz - r.loz) * r.iz, bz = (n.hiz - r.hiz) * r.iz;
     const float t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), limit));
-    return !(t_near > t_far);
+    hit = !(t_near > t_far);
+    return t_near;
+}
+
+// A node reference as the traversal carries it: first << 3 | leaf count (0 = inner node).
+__device__ __forceinline__ unsigned int node_ref(const NodeView& n) {
+    return ((unsigned int)n.first << 3) | (unsigned int)(n.count > 0 ? n.count : 0);
 }
 
 // Nearest hit (base.py:97-105): smallest t, lowest shape index among equal t.
+// Both children of an inner node are tested together (their boxes are adjacent in memory, so
+// the four loads are in flight at once); the one entered first is visited next, the other is
+// pushed with its entry distance only if the ray meets it, and dropped on the way back up if a
+// closer hit has been found meanwhile.
 template <int MODE>
 __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 d, double& tmin, int& sid,
                                               unsigned long long& evaluated) {
@@ -126,33 +137,55 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
     evaluated += (unsigned long long)av.n_large;
     if (av.n_nodes == 0) return;
     const RaySlabs ray = ray_slabs(o, d, av.extent);
-    int stack[kAccelStack];
-    int top = 0, node = 0;
+    float stack_t[kAccelStack];  // entry distance of a pushed box
+    unsigned int stack_ref[kAccelStack];
+    int top = 0;
+    float limit = __double2float_ru(tmin);
+    bool hit;
+    const NodeView root = ldg_node(av.nodes);
+    slab_enter(ray, root, limit, hit);
+    if (!hit) return;
+    unsigned int ref = node_ref(root);
     while (true) {
-        const NodeView n = ldg_node(av.nodes + node);
-        bool descend = false;
-        if (slab_hit(ray, n, __double2float_ru(tmin))) {
-            if (n.count > 0) {
-                for (int k = 0; k < n.count; ++k) {
-                    const int slot = n.first + k;
-                    const int s = __ldg(av.order + slot);
-                    consider(s, accel_sphere_t<MODE>(o, d, ldg_geom(av.leaf_geom + slot),
-                                                     MODE == kModeExact ? __ldg(&av.aux[s].cc) : 0.0));
+        const int first = (int)(ref >> 3), count = (int)(ref & 7u);
+        bool popped = true;
+        if (count > 0) {
+            for (int k = 0; k < count; ++k) {
+                const int slot = first + k;
+                const int s = __ldg(av.order + slot);
+                consider(s, accel_sphere_t<MODE>(o, d, ldg_geom(av.leaf_geom + slot),
+                                                 MODE == kModeExact ? __ldg(&av.aux[s].cc) : 0.0));
+            }
+            evaluated += (unsigned long long)count;
+            limit = __double2float_ru(tmin);
+        } else {
+            const NodeView a = ldg_node(av.nodes + first), b = ldg_node(av.nodes + first + 1);
+            bool hit_a, hit_b;
+            const float ta = slab_enter(ray, a, limit, hit_a), tb = slab_enter(ray, b, limit, hit_b);
+            const unsigned int ref_a = node_ref(a), ref_b = node_ref(b);
+            if (hit_a && hit_b) {
+                const bool b_first = tb < ta;
+                if (top < kAccelStack) {
+                    stack_t[top] = b_first ? ta : tb;
+                    stack_ref[top] = b_first ? ref_a : ref_b;
+                    ++top;
                 }
-                evaluated += (unsigned long long)n.count;
-            } else {
-                // near child first: its hits shrink tmin before the far child is looked at
-                const int axis = -n.count - 1;
-                const bool backwards = is_neg(axis == 0 ? d.x : (axis == 1 ? d.y : d.z));
-                const int near_child = n.first + (backwards ? 1 : 0);
-                if (top < kAccelStack) stack[top++] = n.first + (backwards ? 0 : 1);
-                node = near_child;
-                descend = true;
+                ref = b_first ? ref_b : ref_a;
+                popped = false;
+            } else if (hit_a || hit_b) {
+                ref = hit_a ? ref_a : ref_b;
+                popped = false;
             }
         }
-        if (!descend) {
-            if (top == 0) break;
-            node = stack[--top];
+        if (popped) {
+            while (true) {
+                if (top == 0) return;
+                --top;
+                if (!(stack_t[top] > limit)) {
+                    ref = stack_ref[top];
+                    break;
+                }
+            }
         }
     }
 }
@@ -171,35 +204,43 @@ __device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, V
     evaluated += (unsigned long long)av.n_large;
     if (av.n_nodes == 0) return false;
     const RaySlabs ray = ray_slabs(p, l, av.extent);
-    const float own_limit = __double2float_ru(own);
-    int stack[kAccelStack];
-    int top = 0, node = 0;
+    const float limit = __double2float_ru(own);
+    unsigned int stack[kAccelStack];
+    int top = 0;
+    bool hit;
+    const NodeView root = ldg_node(av.nodes);
+    slab_enter(ray, root, limit, hit);
+    if (!hit) return false;
+    unsigned int ref = node_ref(root);
     while (true) {
-        const NodeView n = ldg_node(av.nodes + node);
-        bool descend = false;
-        if (slab_hit(ray, n, own_limit)) {
-            if (n.count > 0) {
-                for (int k = 0; k < n.count; ++k) {
-                    const int slot = n.first + k;
-                    const int s = __ldg(av.order + slot);
-                    if (s == s_own) continue;
-                    const double t = accel_sphere_t<MODE>(p, l, ldg_geom(av.leaf_geom + slot),
-                                                          MODE == kModeExact ? __ldg(&av.aux[s].cc) : 0.0);
-                    if (t < own) return true;
-                }
-                evaluated += (unsigned long long)n.count;
-            } else {
-                if (top < kAccelStack) stack[top++] = n.first + 1;
-                node = n.first;
-                descend = true;
+        const int first = (int)(ref >> 3), count = (int)(ref & 7u);
+        bool popped = true;
+        if (count > 0) {
+            for (int k = 0; k < count; ++k) {
+                const int slot = first + k;
+                const int s = __ldg(av.order + slot);
+                if (s == s_own) continue;
+                const double t = accel_sphere_t<MODE>(p, l, ldg_geom(av.leaf_geom + slot),
+                                                      MODE == kModeExact ? __ldg(&av.aux[s].cc) : 0.0);
+                if (t < own) return true;
+            }
+            evaluated += (unsigned long long)count;
+        } else {
+            const NodeView a = ldg_node(av.nodes + first), b = ldg_node(av.nodes + first + 1);
+            bool hit_a, hit_b;
+            slab_enter(ray, a, limit, hit_a);
+            slab_enter(ray, b, limit, hit_b);
+            if (hit_a || hit_b) {
+                if (hit_a && hit_b && top < kAccelStack) stack[top++] = node_ref(b);
+                ref = node_ref(hit_a ? a : b);
+                popped = false;
             }
         }
-        if (!descend) {
-            if (top == 0) break;
-            node = stack[--top];
+        if (popped) {
+            if (top == 0) return false;
+            ref = stack[--top];
         }
     }
-    return false;
 }
 
 }  // namespace rt

@@ -133,6 +133,7 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
         return RT_ERR_BAD_ARG;
     if (capacity < rt_accel_bytes(n_spheres)) return RT_ERR_BAD_ARG;
     const int n = n_spheres;
+    if (n > (1 << 26)) return RT_ERR_UNSUPPORTED;  // traversal packs a node index and a leaf count into 32 bits
     for (int s = 0; s < n; ++s) {
         double reach = std::fabs(spheres_host[(size_t)RT_F_RADIUS * n + s]);
         for (int a = 0; a < 3; ++a) reach = std::max(reach, std::fabs(spheres_host[(size_t)a * n + s]));

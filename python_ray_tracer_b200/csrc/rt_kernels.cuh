@@ -7,6 +7,9 @@
 namespace rt {
 
 // Tuning knobs (overridable with -D for the variant sweeps of profiles/).
+#ifndef RT_ACCEL_MIN_BLOCKS
+#define RT_ACCEL_MIN_BLOCKS 6  // tree kernels: latency-bound, more resident warps beat fewer spills (profiles/r01/accel_sweep.txt)
+#endif
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 5  // resident 128-thread blocks per SM the register allocator must allow
 #endif
@@ -139,7 +142,7 @@ __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p
 // Camera rows of one band or interleaved shard (CameraParams): ray generation + trace + stores, one thread per pixel of a
 // patch.  Persistent: the grid is sized to the resident block slots of the GPU.
 template <int MODE, bool STATS, int BLOCK, bool ACCEL>
-__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS : 1)
+__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_ACCEL_MIN_BLOCKS : RT_MIN_BLOCKS) : 1)
     render_rows_kernel(SceneParams sp, CameraParams cp, OutputParams out, Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
     AccelView av = {};
@@ -217,7 +220,7 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS 
 
 // Explicit ray batch, one thread per ray, same work distribution (an item = 32 rays).
 template <int MODE, bool STATS, int BLOCK, bool ACCEL>
-__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? RT_MIN_BLOCKS : 1)
+__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_ACCEL_MIN_BLOCKS : RT_MIN_BLOCKS) : 1)
     trace_rays_kernel(SceneParams sp, RayBatch rb, OutputParams out, Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
     AccelView av = {};

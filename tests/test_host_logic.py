@@ -307,7 +307,7 @@ def test_accel_blob_is_a_valid_tree(n_spheres):
         nd = a["nodes"][node]
         if nd["count"] > 0:
             shapes = a["order"][nd["first"]: nd["first"] + nd["count"]].tolist()
-            assert 1 <= nd["count"] <= 4
+            assert 1 <= nd["count"] <= 2  # kAccelLeafSize
         else:
             assert nd["count"] in (-1, -2, -3)
             shapes = check(nd["first"]) + check(nd["first"] + 1)
