@@ -62,58 +62,61 @@ __device__ __forceinline__ double accel_sphere_t(Vec3 o, Vec3 d, const SphereGeo
 //
 // Per axis, with A = plane - origin and t = A / d:   computed t_lo must not exceed the true
 // one, computed t_hi must not fall below it (whatever the sign of d, that is "A_lo too small,
-// A_hi too large").  Roundings on the way: origin to FP32 (2^-24 |o|), the subtraction
-// (2^-24 (|plane| + |o|)), 1/d (float(d), then an FP32 division: 2^-23) and the product (2^-24);
-// relative errors of t are relative errors of A, and |A| <= |o| + extent.  All of it is below
-// 2^-21 (|o| + extent); the origin is shifted by eps = 2^-20 (|o|_max + extent) towards each
-// plane, twice that.  Boxes are already rounded outward by the builder.
-//   d = +-0 (or below FP32 range): 1/d = +-inf, t = +-inf with the right sign, or NaN when A is
-//   exactly 0, which FMNMX drops (that axis then does not constrain: the origin is in the slab).
-//   Overflow to +-inf keeps the sign; comparisons are written so that inf never rejects a box
-//   the limit would admit.
+// A_hi too large").  t = fma(plane, inv, c) with inv = rcp(float(d)) and c = -(o -+ eps) * inv,
+// one FFMA per plane.  Roundings on the way, as displacements of the plane: origin to FP32
+// (2^-24 |o|), o +- eps (2^-24 (|o| + eps)), the product c (the same again), the fma
+// (2^-24 |A|), inv (float(d) 2^-24 + rcp.approx 2^-23, relative to t, i.e. 3 * 2^-24 |A|), and
+// |A| <= |o| + extent + eps: below 7 * 2^-24 (|o| + extent) in all.  The origin is shifted by
+// eps = 2^-20 (|o|_max + extent) = 16 * 2^-24 (...) towards each plane.  Boxes are already
+// rounded outward by the builder.
+//   d = +-0 (or below FP32 range): inv = +-inf; t is +-inf with the right sign when plane and
+//   origin have opposite signs, else NaN (inf - inf, or 0 * inf), which FMNMX drops: that axis
+//   then does not constrain.  Conservative; only rays exactly parallel to an axis lose culling.
+//   Overflow to +-inf keeps the sign, or gives NaN the same way; comparisons are written so
+//   that inf never rejects a box the limit would admit.
 struct RaySlabs {
-    float lox, loy, loz;  // origin + eps: subtracted from the low planes
-    float hix, hiy, hiz;  // origin - eps: subtracted from the high planes
     float ix, iy, iz;     // 1 / direction
+    float lox, loy, loz;  // -(origin + eps) / direction: added to low plane / direction
+    float hix, hiy, hiz;  // -(origin - eps) / direction: added to high plane / direction
 };
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ RaySlabs ray_slabs(Vec3 o, Vec3 d, float extent) {
     const float ox = __double2float_rn(o.x), oy = __double2float_rn(o.y), oz = __double2float_rn(o.z);
     const float reach = fmaxf(fmaxf(fabsf(ox), fabsf(oy)), fabsf(oz)) + extent;
     const float eps = fmaf(reach, 9.5367431640625e-07f, 1e-30f);  // 2^-20
     RaySlabs r;
-    r.lox = ox + eps, r.loy = oy + eps, r.loz = oz + eps;
-    r.hix = ox - eps, r.hiy = oy - eps, r.hiz = oz - eps;
-    r.ix = 1.0f / __double2float_rn(d.x);
-    r.iy = 1.0f / __double2float_rn(d.y);
-    r.iz = 1.0f / __double2float_rn(d.z);
+    r.ix = rcp_approx(__double2float_rn(d.x));
+    r.iy = rcp_approx(__double2float_rn(d.y));
+    r.iz = rcp_approx(__double2float_rn(d.z));
+    r.lox = -(ox + eps) * r.ix, r.loy = -(oy + eps) * r.iy, r.loz = -(oz + eps) * r.iz;
+    r.hix = -(ox - eps) * r.ix, r.hiy = -(oy - eps) * r.iy, r.hiz = -(oz - eps) * r.iz;
     return r;
 }
 
 struct NodeView {
     float lox, loy, loz, hix, hiy, hiz;
-    int first, count;
+    unsigned int ref;
 };
 __device__ __forceinline__ NodeView ldg_node(const AccelNode* p) {
     const float4 a = __ldg(reinterpret_cast<const float4*>(p));
     const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
-    return {a.x, a.y, a.z, a.w, b.x, b.y, __float_as_int(b.z), __float_as_int(b.w)};
+    return {a.x, a.y, a.z, a.w, b.x, b.y, __float_as_uint(b.z)};
 }
 
 // Distance at which the ray enters the box (0 if it starts inside); `hit` = it may meet the box
 // at a distance in (0, limit]  (limit rounded up from the FP64 one).
 __device__ __forceinline__ float slab_enter(const RaySlabs& r, const NodeView& n, float limit, bool& hit) {
-    const float ax = (n.lox - r.lox) * r.ix, bx = (n.hix - r.hix) * r.ix;
-    const float ay = (n.loy - r.loy) * r.iy, by = (n.hiy - r.hiy) * r.iy;
-    const float az = (n.loz - r.loz) * r.iz, bz = (n.hiz - r.hiz) * r.iz;
+    const float ax = fmaf(n.lox, r.ix, r.lox), bx = fmaf(n.hix, r.ix, r.hix);
+    const float ay = fmaf(n.loy, r.iy, r.loy), by = fmaf(n.hiy, r.iy, r.hiy);
+    const float az = fmaf(n.loz, r.iz, r.loz), bz = fmaf(n.hiz, r.iz, r.hiz);
     const float t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float t_far = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), limit));
     hit = !(t_near > t_far);
     return t_near;
-}
-
-// A node reference as the traversal carries it: first << 3 | leaf count (0 = inner node).
-__device__ __forceinline__ unsigned int node_ref(const NodeView& n) {
-    return ((unsigned int)n.first << 3) | (unsigned int)(n.count > 0 ? n.count : 0);
 }
 
 // Nearest hit (base.py:97-105): smallest t, lowest shape index among equal t.
@@ -145,7 +148,7 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
     const NodeView root = ldg_node(av.nodes);
     slab_enter(ray, root, limit, hit);
     if (!hit) return;
-    unsigned int ref = node_ref(root);
+    unsigned int ref = root.ref;
     while (true) {
         const int first = (int)(ref >> 3), count = (int)(ref & 7u);
         bool popped = true;
@@ -162,7 +165,7 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
             const NodeView a = ldg_node(av.nodes + first), b = ldg_node(av.nodes + first + 1);
             bool hit_a, hit_b;
             const float ta = slab_enter(ray, a, limit, hit_a), tb = slab_enter(ray, b, limit, hit_b);
-            const unsigned int ref_a = node_ref(a), ref_b = node_ref(b);
+            const unsigned int ref_a = a.ref, ref_b = b.ref;
             if (hit_a && hit_b) {
                 const bool b_first = tb < ta;
                 if (top < kAccelStack) {
@@ -211,7 +214,7 @@ __device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, V
     const NodeView root = ldg_node(av.nodes);
     slab_enter(ray, root, limit, hit);
     if (!hit) return false;
-    unsigned int ref = node_ref(root);
+    unsigned int ref = root.ref;
     while (true) {
         const int first = (int)(ref >> 3), count = (int)(ref & 7u);
         bool popped = true;
@@ -231,8 +234,8 @@ __device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, V
             slab_enter(ray, a, limit, hit_a);
             slab_enter(ray, b, limit, hit_b);
             if (hit_a || hit_b) {
-                if (hit_a && hit_b && top < kAccelStack) stack[top++] = node_ref(b);
-                ref = node_ref(hit_a ? a : b);
+                if (hit_a && hit_b && top < kAccelStack) stack[top++] = b.ref;
+                ref = hit_a ? a.ref : b.ref;
                 popped = false;
             }
         }

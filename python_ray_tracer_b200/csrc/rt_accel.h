@@ -51,8 +51,11 @@ struct AccelHeader {
 struct alignas(16) AccelNode {
     float lo[3];
     float hi[3];
-    int32_t first;   // inner: index of the left child (right = first + 1); leaf: first leaf slot
-    int32_t count;   // inner: -(split axis + 1); leaf: number of slots (1..kAccelLeafSize)
+    uint32_t ref;    // first << 3 | count.  Inner node: first = index of the left child (the right
+                     // one follows it), count = 0.  Leaf: first = first leaf slot, count = slots used
+                     // (1..kAccelLeafSize <= 7)
+    int32_t axis;    // inner: split axis (0..2); leaf: -1.  Not read by the traversal.
 };
+static_assert(kAccelLeafSize >= 1 && kAccelLeafSize <= 7, "leaf count is packed into 3 bits");
 
 }  // namespace rt

@@ -65,8 +65,8 @@ struct Builder {
         bounds(begin, end, nd.lo, nd.hi);
         const int count = end - begin;
         if (count <= rt::kAccelLeafSize) {
-            nd.first = (int32_t)order.size();
-            nd.count = count;
+            nd.ref = ((uint32_t)order.size() << 3) | (uint32_t)count;
+            nd.axis = -1;
             for (int i = begin; i < end; ++i) order.push_back(items[i]);
             nodes[node] = nd;
             return;
@@ -88,8 +88,8 @@ struct Builder {
         const int left = (int)nodes.size();
         nodes.push_back(AccelNode());
         nodes.push_back(AccelNode());
-        nd.first = left;
-        nd.count = -(axis + 1);
+        nd.ref = (uint32_t)left << 3;
+        nd.axis = axis;
         nodes[node] = nd;
         build(left, begin, mid);
         build(left + 1, mid, end);

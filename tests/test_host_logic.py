@@ -266,7 +266,7 @@ def _parse_accel(blob: bytes):
     local_bound, gain_bound = struct.unpack_from("<2d", blob, 24 + 56)
     (extent,) = struct.unpack_from("<f", blob, 24 + 56 + 16)
     off_nodes, off_order, off_leaf, off_geom, off_aux, off_large, total = offs
-    nodes = np.frombuffer(blob, dtype=np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("first", "<i4"), ("count", "<i4")]),
+    nodes = np.frombuffer(blob, dtype=np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("ref", "<u4"), ("axis", "<i4")]),
                           count=n_nodes, offset=off_nodes)
     order = np.frombuffer(blob, dtype="<i4", count=n_tree, offset=off_order)
     leaf_geom = np.frombuffer(blob, dtype="<f8", count=4 * n_tree, offset=off_leaf).reshape(-1, 4)
@@ -305,12 +305,13 @@ def test_accel_blob_is_a_valid_tree(n_spheres):
 
     def check(node):  # returns the shapes below `node`
         nd = a["nodes"][node]
-        if nd["count"] > 0:
-            shapes = a["order"][nd["first"]: nd["first"] + nd["count"]].tolist()
-            assert 1 <= nd["count"] <= 2  # kAccelLeafSize
+        first, count = int(nd["ref"]) >> 3, int(nd["ref"]) & 7
+        if count > 0:
+            shapes = a["order"][first: first + count].tolist()
+            assert 1 <= count <= 2 and nd["axis"] == -1  # kAccelLeafSize
         else:
-            assert nd["count"] in (-1, -2, -3)
-            shapes = check(nd["first"]) + check(nd["first"] + 1)
+            assert nd["axis"] in (0, 1, 2)
+            shapes = check(first) + check(first + 1)
         lo, hi = (c[shapes] - r[shapes, None]).min(axis=0), (c[shapes] + r[shapes, None]).max(axis=0)
         # FP32 boxes, rounded outward: strictly outside the FP64 box, by no more than a few ulp
         assert (nd["lo"].astype(np.float64) < lo).all() and (nd["hi"].astype(np.float64) > hi).all()
