@@ -99,7 +99,11 @@ int attach_accel(DeviceCache& c, const double* spheres_host, int32_t n_spheres, 
     const int64_t capacity = rt_accel_bytes(n_spheres);
     if ((int64_t)blob.size() < capacity) blob.resize((size_t)capacity);
     int64_t used = 0;
-    const int rc = rt_accel_build_host(spheres_host, n_spheres, env, blob.data(), capacity, &used);
+    // built inside the call, used once: the quick median build (the call is bound by the
+    // copy of the frame to the host; a better tree would not pay for its own construction)
+    rt_env build_env = *env;
+    build_env.flags |= RT_FLAG_ACCEL_FAST_BUILD;
+    const int rc = rt_accel_build_host(spheres_host, n_spheres, &build_env, blob.data(), capacity, &used);
     if (rc != RT_OK) return host_fail(rc, "host entry point: building the sphere tree failed");
     HOST_CUDA(reserve(c.accel, (size_t)used));
     // pageable source: the copy is staged before the call returns, so `blob` may be reused

@@ -27,7 +27,8 @@ constexpr uint32_t kAccelMagic = 0x52544256u;  // "RTBV"
 #endif
 constexpr int kAccelLeafSize = RT_ACCEL_LEAF;
 constexpr int kAccelMaxLarge = 16;
-constexpr int kAccelStack = 48;
+constexpr int kAccelSahDepth = 36;  // surface-area splits above this depth, median splits below:
+constexpr int kAccelStack = 64;     // depth <= 36 + log2(2^26 shapes) = 62 pending far children
 constexpr double kAccelMaxCoordinate = 1e30;  // beyond this FP32 boxes would overflow: builder refuses
 
 struct AccelHeader {

@@ -1,7 +1,7 @@
 // rt_accel_build.cu -- host-side builder of the sphere BVH blob (rt_accel.h) and its C ABI.
-// Plain C++ (no device code): a top-down median split over sphere centres, leaves of up to
-// kAccelLeafSize shapes.  Building 1 025 spheres takes tens of microseconds; the blob is
-// uploaded once per scene.
+// Plain C++ (no device code): top-down binned surface-area splits (median splits as the fallback
+// and below kAccelSahDepth), leaves of up to kAccelLeafSize shapes, all on FP32 boxes rounded
+// outward from the FP64 spheres.  The blob is uploaded once per scene.
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -16,17 +16,38 @@ namespace {
 using rt::AccelHeader;
 using rt::AccelNode;
 
+// One shape while the tree is built: its FP64 box rounded OUTWARD to FP32 (node boxes are
+// unions of these, and min / max do not round) and its index in the caller's table.  The
+// records themselves are permuted while splitting, so every node works on a contiguous run.
+struct Item {
+    float lo[3];
+    float hi[3];
+    int32_t index;
+    int32_t pad;
+};
+
+struct Box {
+    float lo[3], hi[3];
+    void clear() {
+        for (int a = 0; a < 3; ++a) lo[a] = INFINITY, hi[a] = -INFINITY;
+    }
+    void grow(const float* l, const float* h) {
+        for (int a = 0; a < 3; ++a) lo[a] = std::min(lo[a], l[a]), hi[a] = std::max(hi[a], h[a]);
+    }
+    float half_area() const {
+        const float x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+        return x * y + y * z + z * x;
+    }
+};
+
 struct Builder {
-    const double* f;  // sphere SoA
-    int n;
     std::vector<AccelNode> nodes;
     std::vector<int32_t> order;  // leaf slots
-    std::vector<int32_t> items;  // shapes in the tree, permuted in place while splitting
+    std::vector<Item> items;     // shapes in the tree
+    int sah_depth = rt::kAccelSahDepth;  // 0: median splits only (RT_FLAG_ACCEL_FAST_BUILD)
 
-    double centre(int s, int axis) const { return f[(size_t)axis * n + s]; }
-    double radius(int s) const { return std::fabs(f[(size_t)RT_F_RADIUS * n + s]); }
-
-    // largest float <= x / smallest float >= x, then one more step outward
+    // largest float <= x / smallest float >= x, then one more step outward (c -+ r itself
+    // rounds in FP64, relative 1e-16: covered a millionfold)
     static float round_down(double x) {
         float f = (float)x;
         if ((double)f > x) f = std::nextafterf(f, -INFINITY);
@@ -37,62 +58,190 @@ struct Builder {
         if ((double)f < x) f = std::nextafterf(f, INFINITY);
         return std::nextafterf(f, INFINITY);
     }
-
-    void bounds(int begin, int end, float* lo_out, float* hi_out) const {
-        double lo[3], hi[3];
+    void add(const double* f, int n, int s) {
+        Item it;
+        const double r = std::fabs(f[(size_t)RT_F_RADIUS * n + s]);
         for (int a = 0; a < 3; ++a) {
-            lo[a] = INFINITY;
-            hi[a] = -INFINITY;
+            it.lo[a] = round_down(f[(size_t)a * n + s] - r);
+            it.hi[a] = round_up(f[(size_t)a * n + s] + r);
         }
-        for (int i = begin; i < end; ++i) {
-            const int s = items[i];
-            const double r = radius(s);
-            for (int a = 0; a < 3; ++a) {
-                lo[a] = std::min(lo[a], centre(s, a) - r);
-                hi[a] = std::max(hi[a], centre(s, a) + r);
-            }
-        }
-        // c -+ r rounds in FP64 (relative 1e-16); the outward FP32 rounding covers it a millionfold
-        for (int a = 0; a < 3; ++a) {
-            lo_out[a] = round_down(lo[a]);
-            hi_out[a] = round_up(hi[a]);
-        }
+        it.index = s;
+        it.pad = 0;
+        items.push_back(it);
+    }
+    Box bounds(int begin, int end) const {
+        Box b;
+        b.clear();
+        for (int i = begin; i < end; ++i) b.grow(items[i].lo, items[i].hi);
+        return b;
     }
 
-    // fills nodes[node] for items[begin, end)
-    void build(int node, int begin, int end) {
-        AccelNode nd;
-        bounds(begin, end, nd.lo, nd.hi);
-        const int count = end - begin;
-        if (count <= rt::kAccelLeafSize) {
-            nd.ref = ((uint32_t)order.size() << 3) | (uint32_t)count;
-            nd.axis = -1;
-            for (int i = begin; i < end; ++i) order.push_back(items[i]);
-            nodes[node] = nd;
-            return;
-        }
-        double clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    static constexpr int kBins = 16;
+    static int bin_of(const Item& it, int axis, float origin2, float scale) {
+        // twice the centroid: (lo + hi) against twice the lower bound
+        const int k = (int)(((it.lo[axis] + it.hi[axis]) - origin2) * scale);
+        return std::min(kBins - 1, std::max(0, k));
+    }
+
+    // Binned surface-area heuristic over all three axes in one pass: the split (axis, plane
+    // between two of kBins centroid bins) minimising  area(left) n_left + area(right) n_right.
+    // Partitions items[begin, end) and returns the first index of the right half, or -1 if no
+    // plane separates the centroids.
+    int sah_partition(int begin, int end, int* axis_out, Box* left_out, Box* right_out) {
+        float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
         for (int i = begin; i < end; ++i)
             for (int a = 0; a < 3; ++a) {
-                clo[a] = std::min(clo[a], centre(items[i], a));
-                chi[a] = std::max(chi[a], centre(items[i], a));
+                const float c2 = items[i].lo[a] + items[i].hi[a];
+                clo[a] = std::min(clo[a], c2);
+                chi[a] = std::max(chi[a], c2);
+            }
+        float scale[3];
+        bool usable[3];
+        for (int a = 0; a < 3; ++a) {
+            const float width = chi[a] - clo[a];
+            usable[a] = width > 0.0f && std::isfinite(width);
+            scale[a] = usable[a] ? kBins / width : 0.0f;
+        }
+        Box bins[3][kBins];
+        int counts[3][kBins];
+        for (int a = 0; a < 3; ++a)
+            for (int k = 0; k < kBins; ++k) bins[a][k].clear(), counts[a][k] = 0;
+        for (int i = begin; i < end; ++i) {
+            const Item& it = items[i];
+            for (int a = 0; a < 3; ++a) {
+                const int k = bin_of(it, a, clo[a], scale[a]);
+                bins[a][k].grow(it.lo, it.hi);
+                counts[a][k] += 1;
+            }
+        }
+        float best = INFINITY;
+        int best_axis = -1, best_plane = 0;
+        for (int a = 0; a < 3; ++a) {
+            if (!usable[a]) continue;
+            float right_cost[kBins];
+            Box acc;
+            acc.clear();
+            int n_acc = 0;
+            for (int k = kBins - 1; k > 0; --k) {
+                if (counts[a][k]) acc.grow(bins[a][k].lo, bins[a][k].hi), n_acc += counts[a][k];
+                right_cost[k] = n_acc ? acc.half_area() * (float)n_acc : -1.0f;
+            }
+            acc.clear();
+            n_acc = 0;
+            for (int k = 1; k < kBins; ++k) {  // plane between bins k-1 and k
+                if (counts[a][k - 1]) acc.grow(bins[a][k - 1].lo, bins[a][k - 1].hi), n_acc += counts[a][k - 1];
+                if (n_acc == 0 || right_cost[k] < 0.0f) continue;
+                const float cost = acc.half_area() * (float)n_acc + right_cost[k];
+                if (cost < best) best = cost, best_axis = a, best_plane = k;
+            }
+        }
+        if (best_axis < 0) return -1;
+        left_out->clear();
+        right_out->clear();
+        for (int k = 0; k < kBins; ++k)
+            if (counts[best_axis][k]) (k < best_plane ? left_out : right_out)->grow(bins[best_axis][k].lo, bins[best_axis][k].hi);
+        const float origin2 = clo[best_axis], sc = scale[best_axis];
+        auto mid = std::partition(items.begin() + begin, items.begin() + end,
+                                  [&](const Item& it) { return bin_of(it, best_axis, origin2, sc) < best_plane; });
+        *axis_out = best_axis;
+        return (int)(mid - items.begin());
+    }
+
+    // Few shapes: the exact surface-area sweep (every split of the centroid order on every axis);
+    // binning would spend more time clearing bins than looking at shapes.
+    static constexpr int kSmall = 8;
+    int small_partition(int begin, int end, int* axis_out, Box* left_out, Box* right_out) {
+        const int count = end - begin;
+        Item sorted[kSmall], best_order[kSmall];
+        Box suffix[kSmall];
+        float best = INFINITY;
+        int best_axis = -1, best_k = 0;
+        for (int a = 0; a < 3; ++a) {
+            for (int i = 0; i < count; ++i) {  // insertion sort by (centroid, index)
+                const Item it = items[begin + i];
+                const float c = it.lo[a] + it.hi[a];
+                int j = i;
+                while (j > 0) {
+                    const float cj = sorted[j - 1].lo[a] + sorted[j - 1].hi[a];
+                    if (cj < c || (cj == c && sorted[j - 1].index < it.index)) break;
+                    sorted[j] = sorted[j - 1];
+                    --j;
+                }
+                sorted[j] = it;
+            }
+            Box acc;
+            acc.clear();
+            for (int i = count - 1; i > 0; --i) {
+                acc.grow(sorted[i].lo, sorted[i].hi);
+                suffix[i] = acc;
+            }
+            acc.clear();
+            bool improved = false;
+            for (int k = 1; k < count; ++k) {  // left = sorted[0, k)
+                acc.grow(sorted[k - 1].lo, sorted[k - 1].hi);
+                const float cost = acc.half_area() * (float)k + suffix[k].half_area() * (float)(count - k);
+                if (cost < best) best = cost, best_axis = a, best_k = k, improved = true, *left_out = acc, *right_out = suffix[k];
+            }
+            if (improved)
+                for (int i = 0; i < count; ++i) best_order[i] = sorted[i];
+        }
+        if (best_axis < 0) return -1;  // (non-finite boxes only)
+        for (int i = 0; i < count; ++i) items[begin + i] = best_order[i];
+        *axis_out = best_axis;
+        return begin + best_k;
+    }
+
+    // median of the centroids along the widest axis: the fallback, and the rule below
+    // kAccelSahDepth (it bounds the depth of what remains by log2 of the count)
+    int median_partition(int begin, int end, int* axis_out, Box* left_out, Box* right_out) {
+        float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (int i = begin; i < end; ++i)
+            for (int a = 0; a < 3; ++a) {
+                const float c2 = items[i].lo[a] + items[i].hi[a];
+                clo[a] = std::min(clo[a], c2);
+                chi[a] = std::max(chi[a], c2);
             }
         int axis = 0;
         for (int a = 1; a < 3; ++a)
             if (chi[a] - clo[a] > chi[axis] - clo[axis]) axis = a;
-        const int mid = begin + count / 2;
-        std::nth_element(items.begin() + begin, items.begin() + mid, items.begin() + end, [&](int x, int y) {
-            const double cx = centre(x, axis), cy = centre(y, axis);
-            return cx < cy || (cx == cy && x < y);
+        const int mid = begin + (end - begin) / 2;
+        std::nth_element(items.begin() + begin, items.begin() + mid, items.begin() + end, [&](const Item& x, const Item& y) {
+            const float cx = x.lo[axis] + x.hi[axis], cy = y.lo[axis] + y.hi[axis];
+            return cx < cy || (cx == cy && x.index < y.index);
         });
+        *left_out = bounds(begin, mid);
+        *right_out = bounds(mid, end);
+        *axis_out = axis;
+        return mid;
+    }
+
+    // fills nodes[node] for items[begin, end), whose box is `box`
+    void build(int node, int begin, int end, int depth, const Box& box) {
+        AccelNode nd;
+        for (int a = 0; a < 3; ++a) nd.lo[a] = box.lo[a], nd.hi[a] = box.hi[a];
+        const int count = end - begin;
+        if (count <= rt::kAccelLeafSize) {
+            nd.ref = ((uint32_t)order.size() << 3) | (uint32_t)count;
+            nd.axis = -1;
+            for (int i = begin; i < end; ++i) order.push_back(items[i].index);
+            nodes[node] = nd;
+            return;
+        }
+        int axis = 0;
+        Box left_box, right_box;
+        int mid = -1;
+        if (depth < sah_depth)
+            mid = count <= kSmall ? small_partition(begin, end, &axis, &left_box, &right_box)
+                                  : sah_partition(begin, end, &axis, &left_box, &right_box);
+        if (mid <= begin || mid >= end) mid = median_partition(begin, end, &axis, &left_box, &right_box);
         const int left = (int)nodes.size();
         nodes.push_back(AccelNode());
         nodes.push_back(AccelNode());
         nd.ref = (uint32_t)left << 3;
         nd.axis = axis;
         nodes[node] = nd;
-        build(left, begin, mid);
-        build(left + 1, mid, end);
+        build(left, begin, mid, depth + 1, left_box);
+        build(left + 1, mid, end, depth + 1, right_box);
     }
 };
 
@@ -140,11 +289,10 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
         if (!(reach <= rt::kAccelMaxCoordinate)) return RT_ERR_UNSUPPORTED;  // (NaN lands here too)
     }
     Builder b;
-    b.f = spheres_host;
-    b.n = n;
+    if (env->flags & RT_FLAG_ACCEL_FAST_BUILD) b.sah_depth = 0;
     // shapes far larger than the typical one stay out of the tree
     std::vector<double> radii(n);
-    for (int s = 0; s < n; ++s) radii[s] = b.radius(s);
+    for (int s = 0; s < n; ++s) radii[s] = std::fabs(spheres_host[(size_t)RT_F_RADIUS * n + s]);
     std::vector<double> sorted = radii;
     std::nth_element(sorted.begin(), sorted.begin() + n / 2, sorted.end());
     const double median = sorted[n / 2];
@@ -153,12 +301,12 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
         if ((int)large.size() < rt::kAccelMaxLarge && radii[s] > 64.0 * median)
             large.push_back(s);
         else
-            b.items.push_back(s);
+            b.add(spheres_host, n, s);
     }
     if (!b.items.empty()) {
         b.nodes.reserve(2 * b.items.size() + 1);
         b.nodes.push_back(AccelNode());
-        b.build(0, 0, (int)b.items.size());
+        b.build(0, 0, (int)b.items.size(), 0, b.bounds(0, (int)b.items.size()));
     }
 
     AccelHeader h;
@@ -202,9 +350,9 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
     if (!b.order.empty()) memcpy(base + h.off_order, b.order.data(), 4 * b.order.size());
     auto geom_of = [&](int s, double* out) {
         const double r = spheres_host[(size_t)RT_F_RADIUS * n + s];
-        out[0] = b.centre(s, 0);
-        out[1] = b.centre(s, 1);
-        out[2] = b.centre(s, 2);
+        out[0] = spheres_host[(size_t)RT_F_CX * n + s];
+        out[1] = spheres_host[(size_t)RT_F_CY * n + s];
+        out[2] = spheres_host[(size_t)RT_F_CZ * n + s];
         out[3] = r * r;
     };
     double* leaf_geom = reinterpret_cast<double*>(base + h.off_leaf_geom);
@@ -214,7 +362,7 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
     for (int s = 0; s < n; ++s) {
         geom_of(s, geom + 4 * (size_t)s);
         const double r = spheres_host[(size_t)RT_F_RADIUS * n + s];
-        const double cx = b.centre(s, 0), cy = b.centre(s, 1), cz = b.centre(s, 2);
+        const double cx = geom[4 * (size_t)s], cy = geom[4 * (size_t)s + 1], cz = geom[4 * (size_t)s + 2];
         aux[2 * (size_t)s] = 1.0 / r;                                 // shader.py:74
         aux[2 * (size_t)s + 1] = (cx * cx) + (cy * cy) + (cz * cz);  // shape.py:35
     }

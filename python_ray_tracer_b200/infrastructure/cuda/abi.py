@@ -24,6 +24,7 @@ RT_FLAG_NONE = 0
 RT_FLAG_ALL_POINT_LIGHTS = 1
 RT_FLAG_IMAGE_ORDER = 2
 RT_FLAG_NO_ACCEL = 4
+RT_FLAG_ACCEL_FAST_BUILD = 8
 RT_ACCEL_AUTO_SPHERES = 32
 RT_IPC_HANDLE_BYTES = 64
 RT_DTYPE_F32 = 0

@@ -277,8 +277,9 @@ def _parse_accel(blob: bytes):
                 total=total, local_bound=local_bound, gain_bound=gain_bound, extent=extent)
 
 
+@pytest.mark.parametrize("fast_build", [False, True])
 @pytest.mark.parametrize("n_spheres", [1, 2, 5, 48, 1024])
-def test_accel_blob_is_a_valid_tree(n_spheres):
+def test_accel_blob_is_a_valid_tree(n_spheres, fast_build):
     """rt_accel_build_host: every shape is in exactly one leaf slot or in the always-tested
     list, every node's box contains the boxes of everything below it, records equal the table."""
     from python_ray_tracer_b200 import scenes
@@ -287,7 +288,8 @@ def test_accel_blob_is_a_valid_tree(n_spheres):
     lib = abi.load()
     flat = flatten_scene(scenes.random_spheres_scene(64, 36, n_spheres=n_spheres, seed=77), DefaultMaterial())
     n = flat.n_spheres  # + the ground sphere
-    env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, mode=abi.RT_MODE_FAST)
+    env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, mode=abi.RT_MODE_FAST,
+                       flags=abi.RT_FLAG_ACCEL_FAST_BUILD if fast_build else abi.RT_FLAG_NONE)  # median / surface-area splits
     cap = int(lib.rt_accel_bytes(n))
     buf = np.zeros(cap, dtype=np.uint8)
     used = ctypes.c_int64(0)
