@@ -489,3 +489,22 @@ def test_bvh_lifts_the_shared_memory_limit(rt, c_oracle):
     got = CudaRenderer(precision="fast", max_depth=4).render_rows(flat, scene.camera, 0, 54).numpy()
     want, _ = c_oracle.render(flat, 96, 54, max_depth=4)
     assert_linear_parity(got, want, 1e-4, "4001 shapes through the tree")
+
+
+def test_cli_renders_a_scene_file_like_the_programmatic_scene(tmp_path):
+    """N4: `python -m python_ray_tracer_b200 render` on an exported scene file writes the PNG
+    that render_image_pipeline writes for the scene built in Python, byte for byte in pixels."""
+    from python_ray_tracer_b200 import render_image_pipeline, scene_io, scenes
+    from python_ray_tracer_b200.__main__ import main
+    from python_ray_tracer_b200.infrastructure import CudaRenderer
+    from python_ray_tracer_b200.infrastructure.flatten import DefaultMaterial
+    from python_ray_tracer_b200.infrastructure.png import read_png
+
+    scene = scenes.random_spheres_scene(96, 54, n_spheres=40, seed=9)
+    settings = scene_io.RenderSettings(max_specular_depth=4, output_path=str(tmp_path / "from_file.png"))
+    scene_io.save_scene(scene, tmp_path / "scene.json", tmp_path / "settings.json", settings,
+                        default=DefaultMaterial(**scenes.README_GAINS))
+    assert main(["render", "--scene", str(tmp_path / "scene.json"), "--settings", str(tmp_path / "settings.json")]) == 0
+    render_image_pipeline(scene, tmp_path / "direct.png", CudaRenderer(**scenes.README_GAINS, max_depth=4))
+    a, b = read_png(tmp_path / "from_file.png"), read_png(tmp_path / "direct.png")
+    assert a.shape == (54, 96, 3) and np.array_equal(a, b) and a.max() > 0
