@@ -69,11 +69,13 @@ __device__ __forceinline__ double accel_sphere_t(Vec3 o, Vec3 d, const SphereGeo
 // |A| <= |o| + extent + eps: below 7 * 2^-24 (|o| + extent) in all.  The origin is shifted by
 // eps = 2^-20 (|o|_max + extent) = 16 * 2^-24 (...) towards each plane.  Boxes are already
 // rounded outward by the builder.
-//   d = +-0 (or below FP32 range): inv = +-inf; t is +-inf with the right sign when plane and
-//   origin have opposite signs, else NaN (inf - inf, or 0 * inf), which FMNMX drops: that axis
-//   then does not constrain.  Conservative; only rays exactly parallel to an axis lose culling.
-//   Overflow to +-inf keeps the sign, or gives NaN the same way; comparisons are written so
-//   that inf never rejects a box the limit would admit.
+//   |inv| is capped at 2^64 (d = +-0 included): the test then sees a ray whose direction
+//   component is +-2^-64 instead of something smaller, i.e. displaced by less than 2^-64 t at
+//   distance t -- nothing against the margin -- and no product is ever inf * 0 or inf - inf.
+//   (Uncapped, a ray exactly parallel to an axis got NaN for one plane and +inf for the other,
+//   and dropping the NaN rejected boxes the ray runs through: tests/test_accel_slabs.py.)
+//   Products stay finite because the builder refuses coordinates beyond kAccelMaxCoordinate
+//   (1e15) and rays that start further out than that are not culled at all.
 struct RaySlabs {
     float ix, iy, iz;     // 1 / direction
     float lox, loy, loz;  // -(origin + eps) / direction: added to low plane / direction
@@ -89,11 +91,18 @@ __device__ __forceinline__ RaySlabs ray_slabs(Vec3 o, Vec3 d, float extent) {
     const float reach = fmaxf(fmaxf(fabsf(ox), fabsf(oy)), fabsf(oz)) + extent;
     const float eps = fmaf(reach, 9.5367431640625e-07f, 1e-30f);  // 2^-20
     RaySlabs r;
-    r.ix = rcp_approx(__double2float_rn(d.x));
-    r.iy = rcp_approx(__double2float_rn(d.y));
-    r.iz = rcp_approx(__double2float_rn(d.z));
+    constexpr float kCap = 18446744073709551616.0f;  // 2^64
+    r.ix = fminf(fmaxf(rcp_approx(__double2float_rn(d.x)), -kCap), kCap);
+    r.iy = fminf(fmaxf(rcp_approx(__double2float_rn(d.y)), -kCap), kCap);
+    r.iz = fminf(fmaxf(rcp_approx(__double2float_rn(d.z)), -kCap), kCap);
     r.lox = -(ox + eps) * r.ix, r.loy = -(oy + eps) * r.iy, r.loz = -(oz + eps) * r.iz;
     r.hix = -(ox - eps) * r.ix, r.hiy = -(oy - eps) * r.iy, r.hiz = -(oz - eps) * r.iz;
+    if (!(reach <= (float)kAccelMaxCoordinate)) {
+        // an origin FP32 slabs cannot place (or NaN): every box is accepted, nothing is culled
+        r.ix = r.iy = r.iz = 0.0f;
+        r.lox = r.loy = r.loz = -INFINITY;
+        r.hix = r.hiy = r.hiz = INFINITY;
+    }
     return r;
 }
 

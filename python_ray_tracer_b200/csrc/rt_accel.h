@@ -29,7 +29,7 @@ constexpr int kAccelLeafSize = RT_ACCEL_LEAF;
 constexpr int kAccelMaxLarge = 16;
 constexpr int kAccelSahDepth = 36;  // surface-area splits above this depth, median splits below:
 constexpr int kAccelStack = 64;     // depth <= 36 + log2(2^26 shapes) = 62 pending far children
-constexpr double kAccelMaxCoordinate = 1e30;  // beyond this FP32 boxes would overflow: builder refuses
+constexpr double kAccelMaxCoordinate = 1e15;  // beyond this plane * (1/d capped at 2^64) could overflow FP32: builder refuses
 
 struct AccelHeader {
     uint32_t magic;

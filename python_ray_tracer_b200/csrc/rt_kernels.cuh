@@ -69,12 +69,18 @@ struct Tickets {
     unsigned int n_items;
     unsigned int reversed;       // take items from the last one backwards
 };
-__device__ __forceinline__ unsigned int draw_ticket(const Tickets& tk, int lane) {
+// A draw is split in two so that its round trip to L2 (~1 us) runs under the item being
+// rendered: issue_ticket() only starts the atomic, nothing reads its result until
+// take_ticket(), which is called after the item.  (As one function the self-reset test
+// consumed the result on the next instruction: 17 % of the stall samples of the 1080p frame.)
+__device__ __forceinline__ unsigned int issue_ticket(const Tickets& tk, int lane) {
     unsigned int t = 0;
-    if (lane == 0) {
-        t = atomicAdd(tk.counter, 1u);
-        if (t == tk.n_tickets + tk.n_warps - 1u) atomicExch(tk.counter, 0u);
-    }
+    if (lane == 0) t = atomicAdd(tk.counter, 1u);
+    return t;
+}
+__device__ __forceinline__ unsigned int take_ticket(const Tickets& tk, unsigned int t, int lane) {
+    // the last draw of a launch (every warp ends on one draw past the tickets) re-arms the counter
+    if (lane == 0 && t == tk.n_tickets + tk.n_warps - 1u) atomicExch(tk.counter, 0u);
     return __shfl_sync(0xffffffffu, t, 0);
 }
 
@@ -114,8 +120,13 @@ __device__ __forceinline__ void flush_counters(const Counters& k, unsigned long 
 }
 
 __device__ __forceinline__ unsigned int quantize_channel(double v) {
-    // base.py:143-151: uint8(255 * clip(v, 0, 1)), truncating
-    return (unsigned int)(255.0 * clip01(v));
+    // base.py:143-151: uint8(255 * clip(v, 0, 1)), truncating.  The clip is two tests of the
+    // high word (FP64 fmin / fmax cost ~8 instructions each on sm_100a): same bytes for every
+    // v that is not NaN.
+    const int hi = __double2hiint(v);
+    if (hi < 0) return 0u;               // v < 0 and -0.0
+    if (hi >= 0x3ff00000) return 255u;   // v >= 1
+    return (unsigned int)(255.0 * v);
 }
 
 __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p, Vec3 c) {
@@ -197,15 +208,16 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_AC
     if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
 #endif
     auto render_item = [&](unsigned int idx) { render_patch(tk.reversed ? tk.n_items - 1u - idx : idx); };
-    unsigned int next = draw_ticket(tk, lane);  // in flight during the static rounds
+    unsigned int drawn = issue_ticket(tk, lane);  // in flight during the static rounds
 #pragma unroll 1
     for (unsigned int r = 0; r < tk.static_rounds; ++r) render_item(r * tk.n_warps + warp_id);
     const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
+    unsigned int next = take_ticket(tk, drawn, lane);
 #pragma unroll 1
     while (next < tk.n_tickets) {
-        const unsigned int idx = first_dynamic + next;
-        next = draw_ticket(tk, lane);
-        render_item(idx);
+        drawn = issue_ticket(tk, lane);  // in flight during this item
+        render_item(first_dynamic + next);
+        next = take_ticket(tk, drawn, lane);
     }
 #ifdef RT_TIMING_DEBUG
     if (STATS && out.stats != nullptr && lane == 0) {
@@ -241,15 +253,16 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_AC
         }
     };
 
-    unsigned int next = draw_ticket(tk, lane);
+    unsigned int drawn = issue_ticket(tk, lane);
 #pragma unroll 1
     for (unsigned int r = 0; r < tk.static_rounds; ++r) trace_item(r * tk.n_warps + warp_id);
     const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
+    unsigned int next = take_ticket(tk, drawn, lane);
 #pragma unroll 1
     while (next < tk.n_tickets) {
-        const unsigned int item = first_dynamic + next;
-        next = draw_ticket(tk, lane);
-        trace_item(item);
+        drawn = issue_ticket(tk, lane);
+        trace_item(first_dynamic + next);
+        next = take_ticket(tk, drawn, lane);
     }
     flush_counters<STATS>(k, out.stats);
 }

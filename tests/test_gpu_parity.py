@@ -469,8 +469,27 @@ def test_bvh_gives_the_same_picture_as_testing_every_sphere(precision, c_oracle)
     shard = sharding.StripShard(case.height, 64, 5, 16)
     assert np.array_equal(plain.render_strips(case.flat, _camera(case), shard).numpy(),
                           tree.render_strips(case.flat, _camera(case), shard).numpy())
-    # the all-lights extension walks the tree once per light
+    # rays exactly parallel to an axis (1/d = inf on two axes), from outside and inside the boxes,
+    # through and beside every sphere: the degenerate inputs of the slab test
     case = load_case("c3_small_48_192x108_depth8")
+    centres, radii = case.flat.spheres[0:3, :-1].T, case.flat.spheres[3, :-1]
+    origins, directions = [], []
+    for axis in range(3):
+        for sign in (-1.0, 1.0):
+            for shift, aside in ((30.0, 0.0), (30.0, 0.999), (30.0, 1.5), (0.5, 0.3)):
+                o = centres.copy()
+                o[:, axis] -= sign * shift * np.maximum(radii, 0.2)
+                o[:, (axis + 1) % 3] += aside * radii
+                d = np.zeros_like(o)
+                d[:, axis] = sign
+                origins.append(o)
+                directions.append(d)
+    o, d = np.concatenate(origins).T.copy(), np.concatenate(directions).T.copy()
+    plain, tree = pair(max_depth=8)
+    a = plain.trace_rays(case.flat, NumpyVector3D(o[0], o[1], o[2]), NumpyVector3D(d[0], d[1], d[2]))
+    b = tree.trace_rays(case.flat, NumpyVector3D(o[0], o[1], o[2]), NumpyVector3D(d[0], d[1], d[2]))
+    assert np.array_equal(a.numpy(), b.numpy()) and a.counters()["hits_shaded"] == b.counters()["hits_shaded"] > o.shape[1] // 2
+    # the all-lights extension walks the tree once per light
     plain, tree = pair(max_depth=8, all_point_lights=True)
     assert np.array_equal(_render(plain, case).numpy(), _render(tree, case).numpy())
 
