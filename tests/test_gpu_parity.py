@@ -527,3 +527,62 @@ def test_cli_renders_a_scene_file_like_the_programmatic_scene(tmp_path):
     render_image_pipeline(scene, tmp_path / "direct.png", CudaRenderer(**scenes.README_GAINS, max_depth=4))
     a, b = read_png(tmp_path / "from_file.png"), read_png(tmp_path / "direct.png")
     assert a.shape == (54, 96, 3) and np.array_equal(a, b) and a.max() > 0
+
+
+@pytest.mark.parametrize("scale, spread, n_spheres, seed", [(1.0, 12.0, 33, 1), (1e-3, 0.03, 200, 2), (50.0, 4e4, 700, 3),
+                                                             (0.2, 3.0, 1300, 4), (1e4, 1e7, 64, 5)])
+def test_bvh_equals_exhaustive_on_random_scenes_and_rays(scale, spread, n_spheres, seed):
+    """Random scenes from millimetres to 1e7 units (coincident, nested and touching spheres
+    included) and rays chosen to stress the FP32 slab test -- origins inside spheres, on
+    surfaces and far away; directions with components of 0, 1e-20, 1e-45 (below FP32) and
+    1e-300 -- give bit-identical colours and equal counters with and without the tree."""
+    from python_ray_tracer_b200.infrastructure import CudaRenderer, NumpyVector3D
+    from python_ray_tracer_b200.infrastructure.flatten import FlatScene
+
+    rng = np.random.default_rng(seed)
+    centres = rng.uniform(-spread, spread, (n_spheres, 3))
+    radii = scale * rng.uniform(0.05, 1.0, n_spheres)
+    centres[1], radii[1] = centres[0], radii[0]                    # the same sphere twice (tie -> lowest index)
+    centres[2], radii[2] = centres[3], 0.5 * radii[3]              # nested
+    centres[4] = centres[5] + [radii[4] + radii[5], 0.0, 0.0]      # touching
+    table = np.zeros((12, n_spheres))
+    table[0:3], table[3] = centres.T, radii
+    table[4], table[5], table[6], table[7] = 1.0, rng.uniform(0.2, 1.0, n_spheres), 0.5, 0.05
+    table[8:11] = rng.uniform(0.1, 1.0, (3, n_spheres))
+    table[11, ::7] = 1.0
+    flat = FlatScene(np.ascontiguousarray(table), np.array([[0.3 * spread, 2.0 * spread, -1.5 * spread]]),
+                     (0.0, 0.0, -2.0 * spread), [0.1], (1.0, 1.0, 1.0))
+    k = 20000
+    target = centres[rng.integers(0, n_spheres, k)] + rng.normal(size=(k, 3)) * (radii[rng.integers(0, n_spheres, k)] * 0.7)[:, None]
+    kind = rng.integers(0, 4, k)
+    u = rng.normal(size=(k, 3))
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    which = rng.integers(0, n_spheres, k)
+    o = np.select([(kind == 0)[:, None], (kind == 1)[:, None], (kind == 2)[:, None]],
+                  [target + rng.normal(size=(k, 3)) * spread * 3,               # far away
+                   centres[which] + u * (radii[which] * rng.random(k))[:, None],  # inside a sphere
+                   centres[which] + u * radii[which][:, None]],                # on a surface
+                  target + rng.normal(size=(k, 3)) * scale * 2)                # close by
+    d = target - o
+    tiny = rng.random(k) < 0.4  # squash one or two components to (almost) nothing
+    comp = rng.integers(0, 3, k)
+    value = rng.choice([0.0, 1e-20, -1e-20, 1e-45, -1e-45, 1e-300], k)
+    d[tiny, comp[tiny]] = value[tiny] * np.abs(d[tiny]).max(axis=1)
+    two = tiny & (rng.random(k) < 0.5)
+    d[two, (comp[two] + 1) % 3] = 0.0
+    norm = np.linalg.norm(d, axis=1, keepdims=True)
+    d = d / np.where(norm > 0, norm, 1.0)
+    d[norm[:, 0] == 0] = [0.0, 0.0, 1.0]
+    for precision in PRECISIONS:
+        plain = CudaRenderer(precision=precision, accel=False, max_depth=3, collect_stats=True)
+        tree = CudaRenderer(precision=precision, accel=True, max_depth=3, collect_stats=True)
+        if n_spheres > 1000 and precision == "exact":
+            continue  # (time: the exhaustive exact kernel on 1 300 spheres x 20 000 rays x 3 generations)
+        a = plain.trace_rays(flat, NumpyVector3D(o[:, 0], o[:, 1], o[:, 2]), NumpyVector3D(d[:, 0], d[:, 1], d[:, 2]))
+        b = tree.trace_rays(flat, NumpyVector3D(o[:, 0], o[:, 1], o[:, 2]), NumpyVector3D(d[:, 0], d[:, 1], d[:, 2]))
+        A, B = a.numpy(), b.numpy()
+        same = (A == B) | (np.isnan(A) & np.isnan(B))
+        assert same.all(), f"{precision}: {(~same.all(axis=0)).sum()} of {k} rays differ"
+        ca, cb = a.counters(), b.counters()
+        assert (ca["rays_traced"], ca["hits_shaded"]) == (cb["rays_traced"], cb["hits_shaded"]) and ca["hits_shaded"] > k // 4
+        assert cb["sphere_tests"] < ca["sphere_tests"]
