@@ -3,6 +3,10 @@
 
 #include "rt_accel.cuh"
 
+#ifndef RT_PEEL_PRIMARY
+#define RT_PEEL_PRIMARY 1
+#endif
+
 namespace rt {
 
 struct Counters {
@@ -114,175 +118,196 @@ __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned ch
 // CAMERA: generation 0 starts at sp.eye (the camera kernel), so the fast policy uses the
 // staged per-sphere constants of that origin.
 // ACCEL: nearest hit and shadow test walk the BVH blob (av) instead of the staged table.
-template <int MODE, bool STATS, bool CAMERA, bool ACCEL>
-__device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged& st, const AccelView& av, Vec3 o,
-                                            Vec3 d, Counters& k) {
+// One generation of a chain: nearest hit, NumpyShader.create, the mirror ray.  Returns false
+// when the chain ends here.  PRIMARY: the ray starts at the camera eye (generation 0 of the
+// camera kernel, fast policy): staged per-sphere constants of that origin, to_eye = -d.
+template <int MODE, bool STATS, bool PRIMARY, bool ACCEL>
+__device__ __forceinline__ bool bounce(const SceneParams& sp, const Staged& st, const AccelView& av, const int generation,
+                                       Vec3& o, Vec3& d, Vec3& color, double& weight, unsigned long long& tests,
+                                       Counters& k) {
     const int n = sp.n_spheres;
     const Vec3 eye = {sp.eye[0], sp.eye[1], sp.eye[2]};
-    Vec3 color = {0.0, 0.0, 0.0};
-    double weight = 1.0;
-    unsigned long long tests = 0;
+    if (sp.max_depth > 0 && generation >= sp.max_depth) return false;
+    if (STATS) {
+        k.traced += 1;
+        k.deepest = generation + 1 > (int)k.deepest ? generation + 1 : k.deepest;
+        if (!ACCEL) tests += (unsigned long long)n;
+    }
 
-    for (int generation = 0;; ++generation) {
-        if (sp.max_depth > 0 && generation >= sp.max_depth) break;
-        if (STATS) {
-            k.traced += 1;
-            k.deepest = generation + 1 > (int)k.deepest ? generation + 1 : k.deepest;
-            if (!ACCEL) tests += (unsigned long long)n;
+    // ---- nearest hit (base.py:97-105)
+    double tmin = kMiss;
+    int sid = -1;
+    if (ACCEL) {
+        accel_nearest<MODE>(av, o, d, tmin, sid, tests);
+    } else if (MODE == kModeExact) {
+        for (int s = 0; s < n; ++s) {
+            double t = sphere_distance_exact(o, d, load_geom(st, s), load_aux(st, s).cc);
+            if (t < tmin) {
+                tmin = t;
+                sid = s;
+            }
         }
-
-        // ---- nearest hit (base.py:97-105)
-        double tmin = kMiss;
-        int sid = -1;
-        if (ACCEL) {
-            accel_nearest<MODE>(av, o, d, tmin, sid, tests);
-        } else if (MODE == kModeExact) {
-            for (int s = 0; s < n; ++s) {
-                double t = sphere_distance_exact(o, d, load_geom(st, s), load_aux(st, s).cc);
+    } else {
+        // two spheres per trip: their FP64 chains are independent and interleave
+        constexpr bool primary = PRIMARY;
+        int s = 0;
+        for (; s + 1 < n; s += 2) {
+            HalfB q0 = primary ? half_b_primary(d, load_prim(st, s)) : half_b(o, d, load_geom(st, s));
+            HalfB q1 = primary ? half_b_primary(d, load_prim(st, s + 1)) : half_b(o, d, load_geom(st, s + 1));
+            if (can_hit(q0)) {
+                double t = near_root(q0);
                 if (t < tmin) {
                     tmin = t;
                     sid = s;
                 }
             }
-        } else {
-            // two spheres per trip: their FP64 chains are independent and interleave
-            const bool primary = CAMERA && generation == 0;
-            int s = 0;
-            for (; s + 1 < n; s += 2) {
-                HalfB q0 = primary ? half_b_primary(d, load_prim(st, s)) : half_b(o, d, load_geom(st, s));
-                HalfB q1 = primary ? half_b_primary(d, load_prim(st, s + 1)) : half_b(o, d, load_geom(st, s + 1));
-                if (can_hit(q0)) {
-                    double t = near_root(q0);
-                    if (t < tmin) {
-                        tmin = t;
-                        sid = s;
-                    }
-                }
-                if (can_hit(q1)) {
-                    double t = near_root(q1);
-                    if (t < tmin) {
-                        tmin = t;
-                        sid = s + 1;
-                    }
-                }
-            }
-            if (s < n) {
-                HalfB q = primary ? half_b_primary(d, load_prim(st, s)) : half_b(o, d, load_geom(st, s));
-                if (can_hit(q)) {
-                    double t = near_root(q);
-                    if (t < tmin) {
-                        tmin = t;
-                        sid = s;
-                    }
+            if (can_hit(q1)) {
+                double t = near_root(q1);
+                if (t < tmin) {
+                    tmin = t;
+                    sid = s + 1;
                 }
             }
         }
-        if (sid < 0) break;
-        if (STATS) k.hits += 1;
-
-        // ---- NumpyShader.create (shader.py:63-112)
-        const SphereGeom g = ACCEL ? ldg_geom(av.geom + sid) : load_geom(st, sid);
-        const double inv_r = ACCEL ? __ldg(&av.aux[sid].inv_r) : load_aux(st, sid).inv_r;
-        const Material m = ACCEL ? load_material(sp, sid) : load_material(st, sid);
-        const Vec3 centre = {g.cx, g.cy, g.cz};
-        Vec3 hit, normal, nudged, to_eye;
-        if (MODE == kModeExact) {
-            hit = o + d * tmin;
-            normal = (hit - centre) * inv_r;
-            to_eye = norm_exact(eye - hit);
-            nudged = hit + normal * kNudge;
-        } else {
-            hit = {fma(d.x, tmin, o.x), fma(d.y, tmin, o.y), fma(d.z, tmin, o.z)};
-            normal = (hit - centre) * inv_r;
-            to_eye = norm_fast(eye - hit);
-            nudged = {fma(normal.x, kNudge, hit.x), fma(normal.y, kNudge, hit.y), fma(normal.z, kNudge, hit.z)};
-        }
-
-        Vec3 local = {kAmbient, kAmbient, kAmbient};
-        Vec3 tex = {m.r, m.g, m.b};
-        if (m.checker) {
-            double on = checker_on(hit) ? 1.0 : 0.0;
-            tex = {on, on, on};
-        }
-
-        bool lit0 = false;
-        double spec_sum = 0.0;
-        for (int li = 0; li < sp.n_lights_used; ++li) {
-            Vec3 lp = load_light(st, li);
-            Vec3 to_light = MODE == kModeExact ? norm_exact(lp - hit) : norm_fast(lp - hit);
-            bool lit;
-            if (ACCEL) {
-                const double own = accel_sphere_t<MODE>(nudged, to_light, g, MODE == kModeExact ? __ldg(&av.aux[sid].cc) : 0.0);
-                tests += 1;
-                lit = !accel_occluded<MODE>(av, sid, nudged, to_light, own, tests);
-            } else {
-                lit = in_light<MODE>(st, n, sid, nudged, to_light, tests);
-            }
-            if (li == 0) lit0 = lit;
-            if (MODE == kModeExact) {
-                double litf = lit ? 1.0 : 0.0;
-                double lambert = fmax(dot(normal, to_light), 0.0);
-                local.x += tex.x * lambert * litf * m.diffuse_gain;
-                local.y += tex.y * lambert * litf * m.diffuse_gain;
-                local.z += tex.z * lambert * litf * m.diffuse_gain;
-                double spec = specular_exact(normal, to_light, to_eye, m.roughness, m.specular_gain);
-                spec_sum += spec * litf;
-            } else if (lit) {
-                double lambert = pos_part(fdot(normal, to_light)) * m.diffuse_gain;
-                local.x = fma(tex.x, lambert, local.x);
-                local.y = fma(tex.y, lambert, local.y);
-                local.z = fma(tex.z, lambert, local.z);
-                if (m.specular_gain != 0.0)
-                    spec_sum += specular_fast(normal, to_light, to_eye, m.roughness, m.specular_gain);
+        if (s < n) {
+            HalfB q = primary ? half_b_primary(d, load_prim(st, s)) : half_b(o, d, load_geom(st, s));
+            if (can_hit(q)) {
+                double t = near_root(q);
+                if (t < tmin) {
+                    tmin = t;
+                    sid = s;
+                }
             }
         }
+    }
+    if (sid < 0) return false;
+    if (STATS) k.hits += 1;
 
-        // dome light (shader.py:234-244)
-        double ny = MODE == kModeExact ? fmax((normal.x * 0.0) + (normal.y * 1.0) + (normal.z * 0.0), 0.0) : pos_part(normal.y);
-        double dome;
-        if (MODE == kModeExact) {
-            dome = 0.0;
-            for (int li = 0; li < sp.n_dome; ++li) dome += sp.dome_intensity[li] * ny;
+    // ---- NumpyShader.create (shader.py:63-112)
+    const SphereGeom g = ACCEL ? ldg_geom(av.geom + sid) : load_geom(st, sid);
+    const double inv_r = ACCEL ? __ldg(&av.aux[sid].inv_r) : load_aux(st, sid).inv_r;
+    const Material m = ACCEL ? load_material(sp, sid) : load_material(st, sid);
+    const Vec3 centre = {g.cx, g.cy, g.cz};
+    Vec3 hit, normal, nudged, to_eye;
+    if (MODE == kModeExact) {
+        hit = o + d * tmin;
+        normal = (hit - centre) * inv_r;
+        to_eye = norm_exact(eye - hit);
+        nudged = hit + normal * kNudge;
+    } else {
+        hit = {fma(d.x, tmin, o.x), fma(d.y, tmin, o.y), fma(d.z, tmin, o.z)};
+        normal = (hit - centre) * inv_r;
+        // a primary ray leaves the eye: the direction back to it is -d (to rounding; fast policy only)
+        to_eye = PRIMARY ? Vec3{-d.x, -d.y, -d.z} : norm_fast(eye - hit);
+        nudged = {fma(normal.x, kNudge, hit.x), fma(normal.y, kNudge, hit.y), fma(normal.z, kNudge, hit.z)};
+    }
+
+    Vec3 local = {kAmbient, kAmbient, kAmbient};
+    Vec3 tex = {m.r, m.g, m.b};
+    if (m.checker) {
+        double on = checker_on(hit) ? 1.0 : 0.0;
+        tex = {on, on, on};
+    }
+
+    bool lit0 = false;
+    double spec_sum = 0.0;
+    for (int li = 0; li < sp.n_lights_used; ++li) {
+        Vec3 lp = load_light(st, li);
+        Vec3 to_light = MODE == kModeExact ? norm_exact(lp - hit) : norm_fast(lp - hit);
+        bool lit;
+        if (ACCEL) {
+            const double own = accel_sphere_t<MODE>(nudged, to_light, g, MODE == kModeExact ? __ldg(&av.aux[sid].cc) : 0.0);
+            tests += 1;
+            lit = !accel_occluded<MODE>(av, sid, nudged, to_light, own, tests);
         } else {
-            dome = sp.dome_sum * ny;
+            lit = in_light<MODE>(st, n, sid, nudged, to_light, tests);
         }
-        local.x += sp.dome_color[0] * dome;
-        local.y += sp.dome_color[1] * dome;
-        local.z += sp.dome_color[2] * dome;
-
-        // specular enters as spec * gain * lit (shader.py:106)
-        double spec_term = spec_sum * m.specular_gain;
-        local.x += spec_term;
-        local.y += spec_term;
-        local.z += spec_term;
-
-        // iridescence (shader.py:110)
-        if (MODE == kModeExact || m.irid_gain != 0.0) {
-            Vec3 film = film_color<MODE>(normal, to_eye);
-            local.x += film.x * kFilmWeight * m.irid_gain;
-            local.y += film.y * kFilmWeight * m.irid_gain;
-            local.z += film.z * kFilmWeight * m.irid_gain;
-        }
-
-        color.x += weight * local.x;
-        color.y += weight * local.y;
-        color.z += weight * local.z;
-
-        // the mirror ray enters the parent as refl * 0.5 * gain * lit (shader.py:106)
-        weight *= (lit0 ? 0.5 : 0.0) * m.specular_gain;
-        // Exact keeps tracing a weightless chain, as the reference's unconditional recursion
-        // does (shader.py:90): its children add exactly 0 but count in the ray totals.
-        if (MODE != kModeExact && weight == 0.0) break;
-        if (MODE == kModeFast && st.chain_bound > 0.0 && fabs(weight) * st.chain_bound < sp.cutoff) break;
-
-        // mirror direction (shader.py:151): D - (N*2)*(D.N), normalised
+        if (li == 0) lit0 = lit;
         if (MODE == kModeExact) {
-            d = norm_exact(d - (normal * 2.0) * dot(d, normal));
-        } else {
-            double dn2 = 2.0 * fdot(d, normal);
-            d = norm_fast({fma(-dn2, normal.x, d.x), fma(-dn2, normal.y, d.y), fma(-dn2, normal.z, d.z)});
+            double litf = lit ? 1.0 : 0.0;
+            double lambert = fmax(dot(normal, to_light), 0.0);
+            local.x += tex.x * lambert * litf * m.diffuse_gain;
+            local.y += tex.y * lambert * litf * m.diffuse_gain;
+            local.z += tex.z * lambert * litf * m.diffuse_gain;
+            double spec = specular_exact(normal, to_light, to_eye, m.roughness, m.specular_gain);
+            spec_sum += spec * litf;
+        } else if (lit) {
+            double lambert = pos_part(fdot(normal, to_light)) * m.diffuse_gain;
+            local.x = fma(tex.x, lambert, local.x);
+            local.y = fma(tex.y, lambert, local.y);
+            local.z = fma(tex.z, lambert, local.z);
+            if (m.specular_gain != 0.0)
+                spec_sum += specular_fast(normal, to_light, to_eye, m.roughness, m.specular_gain);
         }
-        o = nudged;
+    }
+
+    // dome light (shader.py:234-244)
+    double ny = MODE == kModeExact ? fmax((normal.x * 0.0) + (normal.y * 1.0) + (normal.z * 0.0), 0.0) : pos_part(normal.y);
+    double dome;
+    if (MODE == kModeExact) {
+        dome = 0.0;
+        for (int li = 0; li < sp.n_dome; ++li) dome += sp.dome_intensity[li] * ny;
+    } else {
+        dome = sp.dome_sum * ny;
+    }
+    local.x += sp.dome_color[0] * dome;
+    local.y += sp.dome_color[1] * dome;
+    local.z += sp.dome_color[2] * dome;
+
+    // specular enters as spec * gain * lit (shader.py:106)
+    double spec_term = spec_sum * m.specular_gain;
+    local.x += spec_term;
+    local.y += spec_term;
+    local.z += spec_term;
+
+    // iridescence (shader.py:110)
+    if (MODE == kModeExact || m.irid_gain != 0.0) {
+        Vec3 film = film_color<MODE>(normal, to_eye);
+        local.x += film.x * kFilmWeight * m.irid_gain;
+        local.y += film.y * kFilmWeight * m.irid_gain;
+        local.z += film.z * kFilmWeight * m.irid_gain;
+    }
+
+    color.x += weight * local.x;
+    color.y += weight * local.y;
+    color.z += weight * local.z;
+
+    // the mirror ray enters the parent as refl * 0.5 * gain * lit (shader.py:106)
+    weight *= (lit0 ? 0.5 : 0.0) * m.specular_gain;
+    // Exact keeps tracing a weightless chain, as the reference's unconditional recursion
+    // does (shader.py:90): its children add exactly 0 but count in the ray totals.
+    if (MODE != kModeExact && weight == 0.0) return false;
+    if (MODE == kModeFast && st.chain_bound > 0.0 && fabs(weight) * st.chain_bound < sp.cutoff) return false;
+
+    // mirror direction (shader.py:151): D - (N*2)*(D.N), normalised
+    if (MODE == kModeExact) {
+        d = norm_exact(d - (normal * 2.0) * dot(d, normal));
+    } else {
+        double dn2 = 2.0 * fdot(d, normal);
+        d = norm_fast({fma(-dn2, normal.x, d.x), fma(-dn2, normal.y, d.y), fma(-dn2, normal.z, d.z)});
+    }
+    o = nudged;
+    return true;
+}
+
+template <int MODE, bool STATS, bool CAMERA, bool ACCEL>
+__device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged& st, const AccelView& av, Vec3 o,
+                                            Vec3 d, Counters& k) {
+    Vec3 color = {0.0, 0.0, 0.0};
+    double weight = 1.0;
+    unsigned long long tests = 0;
+    int generation = 0;
+    bool alive = true;
+    // generation 0 of the camera kernel is four fifths of the 1080p frame: its own copy of the
+    // body, with what is known about a primary ray folded in at compile time
+    if (RT_PEEL_PRIMARY && CAMERA && MODE == kModeFast) {
+        alive = bounce<MODE, STATS, true, ACCEL>(sp, st, av, 0, o, d, color, weight, tests, k);
+        generation = 1;
+    }
+    if (alive) {
+#pragma unroll 1
+        for (;; ++generation)
+            if (!bounce<MODE, STATS, false, ACCEL>(sp, st, av, generation, o, d, color, weight, tests, k)) break;
     }
     if (STATS) k.tests += tests;
     return color;
