@@ -160,7 +160,12 @@ int rt_measure_fma_peak(int device, int32_t dtype, double* flops_out);
  * hit, and so that scenes too large for shared memory can be rendered at all.
  *   rt_accel_bytes(n)  capacity to allocate for n spheres (an upper bound)
  *   env                dome lights and mode of the render calls the blob will serve (it
- *                      carries the material bound of the fast policy's chain cut-off)
+ *                      carries the material bound of the fast policy's chain cut-off);
+ *                      RT_FLAG_ACCEL_FAST_BUILD in env->flags: median splits instead of
+ *                      surface-area splits
+ * Returns RT_ERR_UNSUPPORTED for more than 2^26 spheres or a coordinate / radius beyond
+ * 1e15 (the tree's boxes are FP32), RT_ERR_BAD_ARG if `capacity` is too small.  The tree
+ * only skips sphere tests that provably miss: results with and without it are identical.
  */
 #define RT_ACCEL_AUTO_SPHERES 32 /* measured break-even on B200 (profiles/r01/accel_sweep.txt):
                                    the host-buffer entry points build and upload the tree
