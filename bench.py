@@ -54,11 +54,13 @@ NCU_DRAM_BYTES_PER_LAUNCH = {"c2": 560896}
 def workload(name: str, rank: int, step: int, world: int):
     """(label, flat scene, width, height, max_depth) of one step on one rank."""
     if name == "c2":
-        if world == 1:
-            return "README scene 1920x1080, all effects (configs[1])", flatten_scene(scenes.readme_scene(1920, 1080), README_DEFAULT), 1920, 1080, 0
-        frame = (step * world + rank) % 256
-        return ("256-frame turntable of the README scene at 1080p, frame-sharded (configs[4]); one frame per rank per step",
-                flatten_scene(scenes.turntable_scene(frame, 256, 1920, 1080), README_DEFAULT), 1920, 1080, 0)
+        # N > 1: a batch of N frames of configs[1] per step, one per rank (frame-sharded, nothing
+        # exchanged): per-GPU work is exactly the N = 1 work, which is what weak scaling compares.
+        # (Turntable frames differ in cost by +-20 %; that batch is workload c5.)
+        label = "README scene 1920x1080, all effects (configs[1])"
+        if world > 1:
+            label += "; batch of %d such frames per step, one per rank" % world
+        return label, flatten_scene(scenes.readme_scene(1920, 1080), README_DEFAULT), 1920, 1080, 0
     if name == "c5":
         frame = (step * world + rank) % 256
         return ("256-frame turntable of the README scene at 1080p, frame-sharded (configs[4])",
@@ -224,7 +226,7 @@ def run_b200_arm(args) -> None:
     import torch
     import torch.distributed as dist
 
-    from python_ray_tracer_b200.infrastructure.cuda import abi, sharding
+    from python_ray_tracer_b200.infrastructure.cuda import abi, affinity, sharding
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -233,6 +235,7 @@ def run_b200_arm(args) -> None:
         raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    bound = affinity.bind_to_device(local) if world > 1 else None  # pinned buffers next to this rank's GPU
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = abi.load()
@@ -321,6 +324,10 @@ def run_b200_arm(args) -> None:
     wall0 = time.perf_counter()
     for s in range(args.warmup, total):
         flush.fill_(s & 0xFF)  # evict the previous frame's lines from L2 (not timed)
+        if banded and world > 1:
+            # one frame over all ranks: start it together, after every rank's flush (a rank
+            # still flushing would compete with the others' peer stores into rank 0)
+            dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         launch(s)
@@ -418,7 +425,8 @@ def run_b200_arm(args) -> None:
                                    if args.exchange == "peer" else ("interleaved 16-row strips x%d + NCCL gather of RGBA8 to rank 0 + row permutation" % world)) if banded else ("frame-sharded x%d, no collective" % world),
                    "l2": "512 MiB buffer written between timed steps (L2 flush); each step timed by its own CUDA event pair"},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_value, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h,
+                "d2h_bytes_per_step": d2h, "d2h_gb_per_s_per_gpu": d2h / (e2e_ms_value * 1e-3) / 1e9,
+                "host_cpus_bound": len(bound) if bound else None,
                 "api": "rt_render_frame_host: scene upload + kernel + D2H of the f32 linear planes into pinned host memory, row chunks pipelined (kernel of chunk i+1 under the copy of chunk i)",
                 "with_rgb8": {"ms_per_step": e2e_rgb8_ms, "value": pixels_per_step / (e2e_rgb8_ms * 1e-3) / 1e6,
                               "d2h_bytes_per_step": d2h + rgb8_host.numel()}},

@@ -51,7 +51,7 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
     out_dir.mkdir(parents=True, exist_ok=True)
     device = renderer.device
     todo = [k for k in frames_of_rank(n_frames, world, rank) if not (resume and frame_path(out_dir, k).exists())]
-    threads = encoder_threads or max(1, (os.cpu_count() or 2) // max(1, world))
+    threads = encoder_threads or max(1, min(len(os.sched_getaffinity(0)), (os.cpu_count() or 2) // max(1, world)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 2) // max(1, world))
     stats = {"frames": 0, "skipped": len(list(frames_of_rank(n_frames, world, rank))) - len(todo),
              "wall_s": 0.0, "gpu_s": 0.0, "encode_s": 0.0, "encoder_threads": threads}
     if not todo:
@@ -139,7 +139,10 @@ def main() -> None:
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     from .infrastructure import CudaRenderer
+    from .infrastructure.cuda import affinity
 
+    if world > 1:
+        affinity.bind_to_device(local)  # encoder threads and pinned slots on the GPU's own socket
     renderer = CudaRenderer(**scenes.README_GAINS, device=local, output_dtype="float32")
     stats = render_turntable(renderer, args.frames, args.out, args.width, args.height, rank=rank, world=world,
                              encoder_threads=args.encoder_threads, compress_level=args.compress_level,
