@@ -69,18 +69,23 @@ struct Tickets {
     unsigned int n_items;
     unsigned int reversed;       // take items from the last one backwards
 };
-// A draw is split in two so that its round trip to L2 (~1 us) runs under the item being
-// rendered: issue_ticket() only starts the atomic, nothing reads its result until
-// take_ticket(), which is called after the item.  (As one function the self-reset test
-// consumed the result on the next instruction: 17 % of the stall samples of the 1080p frame.)
+// A draw is split in two: issue_ticket() starts the atomic, take_ticket() broadcasts its result
+// after the item.  The atomic is atom.inc with the launch's last draw as its bound (every warp
+// ends on one draw past the tickets, n_tickets + n_warps draws in all): the counter re-arms
+// itself for the next launch, and -- unlike atom.add under a lane == 0 predicate -- ptxas does
+// not wrap it in its warp-aggregation sequence (vote, popc, shuffle of the result).
+// What this does NOT achieve is hiding the round trip (~0.8 us): at 96 registers the result is
+// spilled on the next instruction, and the spill store waits for it.  Measured consequences
+// (profiles/r01/schedule_sweep.txt): a 1080p frame of trivial items takes 68 us (22 draws per
+// warp), handing out 8/4/2/1 items per draw lowers that floor to 51 us but costs the README
+// frame 6 us in balance (its costly patches cluster), so single tickets stay.
 __device__ __forceinline__ unsigned int issue_ticket(const Tickets& tk, int lane) {
     unsigned int t = 0;
-    if (lane == 0) t = atomicAdd(tk.counter, 1u);
+    if (lane == 0)
+        asm volatile("atom.global.inc.u32 %0, [%1], %2;" : "=r"(t) : "l"(tk.counter), "r"(tk.n_tickets + tk.n_warps - 1u));
     return t;
 }
 __device__ __forceinline__ unsigned int take_ticket(const Tickets& tk, unsigned int t, int lane) {
-    // the last draw of a launch (every warp ends on one draw past the tickets) re-arms the counter
-    if (lane == 0 && t == tk.n_tickets + tk.n_warps - 1u) atomicExch(tk.counter, 0u);
     return __shfl_sync(0xffffffffu, t, 0);
 }
 
