@@ -48,7 +48,7 @@ FLOP_PER_HIT = 280.0          # NumpyShader.create without its S shadow tests
 BYTES_PER_PIXEL = 12.0 + 4.0  # planar f32 RGB + RGBA8, each written once
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, one `ncu --set full` capture per workload
 # (profiles/r01/*_details.txt); None where no capture was taken
-NCU_DRAM_BYTES_PER_LAUNCH = {"c2": 560896}
+NCU_DRAM_BYTES_PER_LAUNCH = {"c2": 639488}
 
 
 def workload(name: str, rank: int, step: int, world: int):
