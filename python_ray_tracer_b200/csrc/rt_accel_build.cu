@@ -45,6 +45,7 @@ struct Builder {
     std::vector<int32_t> order;  // leaf slots
     std::vector<Item> items;     // shapes in the tree
     int sah_depth = rt::kAccelSahDepth;  // 0: median splits only (RT_FLAG_ACCEL_FAST_BUILD)
+    int deepest = 0;                     // depth of the deepest node (root = 0)
 
     // largest float <= x / smallest float >= x, then one more step outward (c -+ r itself
     // rounds in FP64, relative 1e-16: covered a millionfold)
@@ -219,6 +220,7 @@ struct Builder {
     void build(int node, int begin, int end, int depth, const Box& box) {
         AccelNode nd;
         for (int a = 0; a < 3; ++a) nd.lo[a] = box.lo[a], nd.hi[a] = box.hi[a];
+        deepest = std::max(deepest, depth);
         const int count = end - begin;
         if (count <= rt::kAccelLeafSize) {
             nd.ref = ((uint32_t)order.size() << 3) | (uint32_t)count;
@@ -307,6 +309,8 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
         b.nodes.reserve(2 * b.items.size() + 1);
         b.nodes.push_back(AccelNode());
         b.build(0, 0, (int)b.items.size(), 0, b.bounds(0, (int)b.items.size()));
+        // the traversal keeps at most one pending sibling per level on its stack
+        if (b.deepest + 1 > rt::kAccelStack) return RT_ERR_UNSUPPORTED;
     }
 
     AccelHeader h;

@@ -305,7 +305,10 @@ def test_accel_blob_is_a_valid_tree(n_spheres, fast_build):
     assert np.array_equal(a["leaf_geom"], a["geom"][a["order"]]) and np.array_equal(a["aux"][:, 0], 1.0 / flat.spheres[3])
     assert a["gain_bound"] == np.abs(flat.spheres[5]).max() and a["local_bound"] > 0
 
-    def check(node):  # returns the shapes below `node`
+    depths = []
+
+    def check(node, depth=0):  # returns the shapes below `node`
+        depths.append(depth)
         nd = a["nodes"][node]
         first, count = int(nd["ref"]) >> 3, int(nd["ref"]) & 7
         if count > 0:
@@ -313,7 +316,7 @@ def test_accel_blob_is_a_valid_tree(n_spheres, fast_build):
             assert 1 <= count <= 2 and nd["axis"] == -1  # kAccelLeafSize
         else:
             assert nd["axis"] in (0, 1, 2)
-            shapes = check(first) + check(first + 1)
+            shapes = check(first, depth + 1) + check(first + 1, depth + 1)
         lo, hi = (c[shapes] - r[shapes, None]).min(axis=0), (c[shapes] + r[shapes, None]).max(axis=0)
         # FP32 boxes, rounded outward: strictly outside the FP64 box, by no more than a few ulp
         assert (nd["lo"].astype(np.float64) < lo).all() and (nd["hi"].astype(np.float64) > hi).all()
@@ -323,7 +326,40 @@ def test_accel_blob_is_a_valid_tree(n_spheres, fast_build):
 
     if len(a["nodes"]):
         assert sorted(check(0)) == sorted(a["order"].tolist())
+        assert max(depths) < 64  # kAccelStack: one pending sibling per level
     # coordinates FP32 boxes cannot hold: refused, never silently clamped
     far = flat.spheres.copy()
     far[0, 0] = 1e16
     assert lib.rt_accel_build_host(far.ctypes.data, n, ctypes.byref(env), buf.ctypes.data, cap, ctypes.byref(used)) == -4  # RT_ERR_UNSUPPORTED
+
+
+def test_accel_depth_stays_within_the_traversal_stack():
+    """Geometrically spaced spheres make surface-area splits peel one shape per level; past
+    kAccelSahDepth the builder switches to median splits, so the depth stays below the 64
+    entries of the traversal stack.  Identical spheres (no separating plane) fall back too."""
+    lib = abi.load()
+    for centres, radii in (
+        (np.stack([1.2 ** np.arange(180), np.zeros(180), np.zeros(180)], axis=1), 0.01 * 1.2 ** np.arange(180)),
+        (np.zeros((300, 3)) + [1.0, 2.0, 3.0], np.full(300, 0.5)),
+    ):
+        n = len(radii)
+        table = np.zeros((12, n))
+        table[0:3], table[3], table[4:8] = centres.T, radii, 1.0
+        table = np.ascontiguousarray(table)
+        env = abi.make_env((0.0, 0.0, -2.0), 1, [0.1], (1.0, 1.0, 1.0), mode=abi.RT_MODE_FAST)
+        cap = int(lib.rt_accel_bytes(n))
+        buf = np.zeros(cap, dtype=np.uint8)
+        used = ctypes.c_int64(0)
+        assert lib.rt_accel_build_host(table.ctypes.data, n, ctypes.byref(env), buf.ctypes.data, cap, ctypes.byref(used)) == 0
+        a = _parse_accel(buf[: used.value].tobytes())
+        seen, deepest, todo = [], 0, [(0, 0)] if len(a["nodes"]) else []
+        while todo:
+            node, depth = todo.pop()
+            deepest = max(deepest, depth)
+            ref = int(a["nodes"][node]["ref"])
+            first, count = ref >> 3, ref & 7
+            if count:
+                seen += a["order"][first: first + count].tolist()
+            else:
+                todo += [(first, depth + 1), (first + 1, depth + 1)]
+        assert sorted(seen + a["large"].tolist()) == list(range(n)) and deepest < 63
