@@ -114,6 +114,25 @@ typedef enum rt_flags {
                                     points use for the tree they build per call           */
     RT_FLAG_NO_ACCEL = 4,         /* host-buffer entry points only: never build the tree
                                     themselves (see RT_ACCEL_AUTO_SPHERES)               */
+    RT_FLAG_WIDE_STORES = 16,     /* rt_render_rows_dev / rt_render_strips_dev: warps render 32x1
+                                    pixel patches instead of 8x4, so each of their stores is a
+                                    128-byte line (96 bytes with RT_FLAG_RGB8) instead of a
+                                    32-byte sector.  For frames written into peer memory
+                                    (RT_FLAG_IMAGE_ORDER): NVLink carries the wide stores at
+                                    about twice the rate; tracing itself is ~4 % slower at 8K.
+                                    Same pixels either way.                                */
+    RT_FLAG_EVEN_STORES = 64,     /* with RT_FLAG_WIDE_STORES: patches are taken two from the
+                                    bottom, one from the top of the rows of the call instead of
+                                    bottom-up.  The reference camera (base.py:130-141) sees sky
+                                    in the upper rows, which trace several times faster than
+                                    the rest; taken last they arrive as a burst of stores
+                                    that one NVLink port cannot take from seven writers.    */
+    RT_FLAG_RGB8 = 32,            /* rt_render_rows_dev / rt_render_strips_dev: rgba8_dev holds
+                                    3 bytes per pixel (R,G,B -- the array save_image hands to
+                                    PIL, base.py:143-151) instead of 4.  With RT_FLAG_WIDE_STORES
+                                    and cam->width and the pointer multiples of 4 the warp
+                                    packs a patch row into 32-bit words; byte stores
+                                    otherwise.                                              */
     RT_FLAG_IMAGE_ORDER = 2       /* rt_render_rows_dev / rt_render_strips_dev: rgb_dev and
                                     rgba8_dev are WHOLE frames (height x width) and every
                                     pixel is stored at row*width + col, whatever rows the
@@ -186,7 +205,8 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
  *                     inside the band, p = (row-row0)*width + col) is at
  *                     rgb_dev[c*plane_stride + p], element type rgb_dtype.  May be NULL.
  *   rgba8_dev         optional: 4 bytes per pixel, uint8(255*clip(v,0,1)) truncating
- *                     (base.py:143-151) in R,G,B and 255 in A.  May be NULL.
+ *                     (base.py:143-151) in R,G,B and 255 in A -- or 3 bytes per pixel
+ *                     (R,G,B) with RT_FLAG_RGB8.  May be NULL.
  *   stats_dev         optional RT_STATS_WORDS x uint64 counters, or NULL.
  */
 int rt_render_rows_dev(int device, const double* spheres_dev, int32_t n_spheres,

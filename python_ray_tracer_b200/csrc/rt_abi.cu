@@ -240,8 +240,14 @@ int render_camera(int device, const double* spheres_dev, int32_t n_spheres, cons
     if (rgb_dev != nullptr && plane_stride < n) return fail(RT_ERR_BAD_ARG, "plane_stride %lld < %lld pixels", (long long)plane_stride, (long long)n);
     DeviceScope scope(device);
     if (scope.status != RT_OK) return scope.status;
+    // 3-byte pixels go out as packed words from the wide-store kernels when every patch row starts on a word boundary
+    int bytes8 = rt::kRgba8;
+    if (env->flags & RT_FLAG_RGB8)
+        bytes8 = ((env->flags & RT_FLAG_WIDE_STORES) && cp.width % 4 == 0 && reinterpret_cast<uintptr_t>(rgba8_dev) % 4 == 0)
+                     ? rt::kRgb8Words : rt::kRgb8Bytes;
     rt::OutputParams out = {rgb_dev, rgba8_dev, reinterpret_cast<unsigned long long*>(stats_dev), plane_stride,
-                            rgb_dtype == RT_DTYPE_F64, image_order ? 1 : 0};
+                            rgb_dtype == RT_DTYPE_F64, image_order ? 1 : 0, bytes8,
+                            (env->flags & RT_FLAG_WIDE_STORES) ? 1 : 0, (env->flags & RT_FLAG_EVEN_STORES) ? 1 : 0};
     cudaError_t err = launchers(env->mode).render_rows(stats_dev != nullptr, scene_params(spheres_dev, n_spheres, point_lights_dev, env),
                                                       cp, out, static_cast<cudaStream_t>(stream));
     if (err != cudaSuccess) return cuda_fail(err, "render_rows launch");

@@ -84,15 +84,23 @@ struct RayBatch {
     long long n;
 };
 
+enum Bytes8 : int {
+    kRgba8 = 0,       // 4 bytes per pixel, one 32-bit store per pixel
+    kRgb8Words = 1,   // 3 bytes per pixel, a patch row packed into 32-bit words by the warp (width % 4 == 0)
+    kRgb8Bytes = 2    // 3 bytes per pixel, byte stores (any width)
+};
 struct OutputParams {
     void* rgb;            // planar, may be nullptr
-    uint8_t* rgba8;       // 4 bytes per pixel, may be nullptr
+    uint8_t* rgba8;       // 8-bit image (layout: bytes8), may be nullptr
     unsigned long long* stats;
     long long plane_stride;
     int rgb_is_f64;
     int image_order;      // camera kernel: index outputs by image pixel (row*W + col) instead of
                           // the shard's packed order -- the buffers are whole frames, possibly
                           // peer memory of another GPU (RT_FLAG_IMAGE_ORDER)
+    int bytes8;           // Bytes8 (RT_FLAG_RGB8)
+    int wide_patches;     // camera kernel: 32x1 patches instead of 8x4 (RT_FLAG_WIDE_STORES); host-side choice
+    int even_stores;      // wide patches only: items alternately from both ends of the frame (RT_FLAG_EVEN_STORES)
 };
 
 // Per-sphere records staged in shared memory.  Reads are warp-uniform (every lane tests

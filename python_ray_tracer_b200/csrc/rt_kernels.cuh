@@ -26,8 +26,12 @@ namespace rt {
 #ifndef RT_PATCH_W
 #define RT_PATCH_W 8
 #endif
-constexpr int kWarpTileW = RT_PATCH_W;       // each warp renders 8x4 pixel patches: bounce coherence, and
-constexpr int kWarpTileH = 32 / RT_PATCH_W;  // every row segment it stores is one full 32-byte sector
+// Each warp renders a patch of 32 pixels.  8x4 by default: bounce coherence, and every row
+// segment it stores is one full 32-byte sector.  32x1 (RT_FLAG_WIDE_STORES) when the frame is
+// written into another GPU's memory: a warp's store is then one 128-byte line per plane or
+// 8-bit row, which is what NVLink moves efficiently (about +4 % tracing time at 8K).
+constexpr int kWarpTileW = RT_PATCH_W;
+constexpr int kWideTileW = 32;
 // Two block shapes.  Small scenes: 128-thread blocks, RT_MIN_BLOCKS resident per SM, each
 // with its own copy of the (small) sphere table.  Scenes whose table would not fit that
 // many times in an SM's shared memory: one 640-thread block per SM sharing one copy, the
@@ -67,7 +71,7 @@ struct Tickets {
     unsigned int n_warps;        // gridDim.x * (block threads / 32)
     unsigned int static_rounds;  // items [0, static_rounds * n_warps) are dealt statically
     unsigned int n_items;
-    unsigned int reversed;       // take items from the last one backwards
+    unsigned int reversed;       // 1: take items from the last one backwards; 2: alternately from both ends (wide-store kernels)
 };
 // A draw is split in two: issue_ticket() starts the atomic, take_ticket() broadcasts its result
 // after the item.  The atomic is atom.inc with the launch's last draw as its bound (every warp
@@ -87,6 +91,24 @@ __device__ __forceinline__ unsigned int issue_ticket(const Tickets& tk, int lane
 }
 __device__ __forceinline__ unsigned int take_ticket(const Tickets& tk, unsigned int t, int lane) {
     return __shfl_sync(0xffffffffu, t, 0);
+}
+
+// The item loop of a warp: the static rounds, then tickets, the next one kept in flight under
+// the item.  (Drawing only when the ticket is needed -- no draw live across the item body -- was
+// measured for the big blocks, whose items take >= 100 us: 17.99 against 18.07 ms on c3, not kept.)
+template <typename Item>
+__device__ __forceinline__ void run_items(const Tickets& tk, const int lane, const unsigned int warp_id, Item&& item) {
+    unsigned int drawn = issue_ticket(tk, lane);  // in flight during the static rounds
+#pragma unroll 1
+    for (unsigned int r = 0; r < tk.static_rounds; ++r) item(r * tk.n_warps + warp_id);
+    const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
+    unsigned int next = take_ticket(tk, drawn, lane);
+#pragma unroll 1
+    while (next < tk.n_tickets) {
+        drawn = issue_ticket(tk, lane);  // in flight during this item
+        item(first_dynamic + next);
+        next = take_ticket(tk, drawn, lane);
+    }
 }
 
 // np.linspace sample i (base.py:132-139): i*step + start, last sample = stop exactly.
@@ -134,6 +156,28 @@ __device__ __forceinline__ unsigned int quantize_channel(double v) {
     return (unsigned int)(255.0 * v);
 }
 
+// 3-byte pixels of one patch row, packed into 32-bit words by the warp (Bytes8::kRgb8Words):
+// lane px of a row segment of PW pixels stores word px of its 3*PW/4 words, taking the bytes of
+// pixels 4*px/3 and 4*px/3 + 1 from their lanes.  The segment starts at a multiple of four
+// pixels and the frame width is one too, so every word is aligned and no word straddles two
+// rows or two patches.  Called by all 32 lanes; `valid` = this lane owns a pixel of the frame.
+template <int PW>
+__device__ __forceinline__ void store_rgb8_words(const OutputParams& out, bool valid, long long p, int px, int cols_left,
+                                                 Vec3 c) {
+    unsigned int q = 0u;
+    if (valid) q = quantize_channel(c.x) | (quantize_channel(c.y) << 8) | (quantize_channel(c.z) << 16);
+    const int lane = threadIdx.x & 31;
+    const int first = (4 * px) / 3, shift = 8 * ((4 * px) % 3);
+    const int seg = lane - px;  // lane of the segment's first pixel
+    const unsigned int qa = __shfl_sync(0xffffffffu, q, seg + (first < PW ? first : PW - 1));
+    const unsigned int qb = __shfl_sync(0xffffffffu, q, seg + (first + 1 < PW ? first + 1 : PW - 1));
+    const int n_valid = cols_left < PW ? cols_left : PW;
+    if (valid && 4 * px < 3 * n_valid) {
+        const unsigned long long both = (unsigned long long)qa | ((unsigned long long)qb << 24);
+        *reinterpret_cast<unsigned int*>(out.rgba8 + (p - px) * 3 + 4 * px) = (unsigned int)(both >> shift);
+    }
+}
+
 __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p, Vec3 c) {
     if (out.rgb != nullptr) {
         if (out.rgb_is_f64) {
@@ -149,17 +193,24 @@ __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p
         }
     }
     if (out.rgba8 != nullptr) {
-        uchar4 q = make_uchar4((unsigned char)quantize_channel(c.x), (unsigned char)quantize_channel(c.y),
-                               (unsigned char)quantize_channel(c.z), 255);
-        reinterpret_cast<uchar4*>(out.rgba8)[p] = q;
+        if (out.bytes8 == kRgba8) {
+            uchar4 q = make_uchar4((unsigned char)quantize_channel(c.x), (unsigned char)quantize_channel(c.y),
+                                   (unsigned char)quantize_channel(c.z), 255);
+            reinterpret_cast<uchar4*>(out.rgba8)[p] = q;
+        } else if (out.bytes8 == kRgb8Bytes) {
+            out.rgba8[3 * p + 0] = (unsigned char)quantize_channel(c.x);
+            out.rgba8[3 * p + 1] = (unsigned char)quantize_channel(c.y);
+            out.rgba8[3 * p + 2] = (unsigned char)quantize_channel(c.z);
+        }  // kRgb8Words: stored by the warp, store_rgb8_words()
     }
 }
 
 // Camera rows of one band or interleaved shard (CameraParams): ray generation + trace + stores, one thread per pixel of a
 // patch.  Persistent: the grid is sized to the resident block slots of the GPU.
-template <int MODE, bool STATS, int BLOCK, bool ACCEL>
+template <int MODE, bool STATS, int BLOCK, bool ACCEL, int PW>
 __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_ACCEL_MIN_BLOCKS : RT_MIN_BLOCKS) : 1)
     render_rows_kernel(SceneParams sp, CameraParams cp, OutputParams out, Tickets tk) {
+    constexpr int kWarpTileW = PW, kWarpTileH = 32 / PW;
     extern __shared__ __align__(16) unsigned char smem[];
     AccelView av = {};
     if (ACCEL) av = accel_view(sp.accel);
@@ -188,7 +239,20 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_AC
         }
         const int local_row = (int)ty * kWarpTileH + py;
         const int col = (int)tx * kWarpTileW + px;
-        if (col < cp.width && local_row < cp.n_rows) {
+        const bool valid = col < cp.width && local_row < cp.n_rows;
+        if constexpr (PW == kWideTileW) {
+            // the wide-store kernels can pack 3-byte pixels across the warp: all lanes reach the store
+            long long p = 0;
+            Vec3 c = {0.0, 0.0, 0.0};
+            if (valid) {
+                const int row = image_row(cp, local_row);
+                Vec3 d = primary_direction<MODE>(cp, col, row);
+                c = trace_chain<MODE, STATS, !ACCEL, ACCEL>(sp, st, av, eye, d, k);
+                p = (long long)(out.image_order ? row : local_row) * cp.width + col;
+                store_pixel(out, p, c);
+            }
+            if (out.bytes8 == kRgb8Words && out.rgba8 != nullptr) store_rgb8_words<PW>(out, valid, p, px, cp.width - col + px, c);
+        } else if (valid) {
             const int row = image_row(cp, local_row);
             Vec3 d = primary_direction<MODE>(cp, col, row);
             Vec3 c = trace_chain<MODE, STATS, !ACCEL, ACCEL>(sp, st, av, eye, d, k);
@@ -212,18 +276,22 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_AC
     unsigned long long t_start = 0;
     if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
 #endif
-    auto render_item = [&](unsigned int idx) { render_patch(tk.reversed ? tk.n_items - 1u - idx : idx); };
-    unsigned int drawn = issue_ticket(tk, lane);  // in flight during the static rounds
-#pragma unroll 1
-    for (unsigned int r = 0; r < tk.static_rounds; ++r) render_item(r * tk.n_warps + warp_id);
-    const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
-    unsigned int next = take_ticket(tk, drawn, lane);
-#pragma unroll 1
-    while (next < tk.n_tickets) {
-        drawn = issue_ticket(tk, lane);  // in flight during this item
-        render_item(first_dynamic + next);
-        next = take_ticket(tk, drawn, lane);
-    }
+    auto render_item = [&](unsigned int idx) {
+        unsigned int item = tk.reversed ? tk.n_items - 1u - idx : idx;
+        if constexpr (PW == kWideTileW) {
+            // frames that several GPUs write (RT_FLAG_EVEN_STORES): two patches from the bottom, then one
+            // from the top, so that cheap rows (many stores per microsecond) and costly ones mix over the
+            // launch; the two fronts meet a third of the way down, where the reference camera still sees
+            // sky, so the launch still ends on cheap patches
+            if (tk.reversed == 2u) {
+                const unsigned int third = tk.n_items / 3u, group = idx / 3u, r = idx - 3u * group;
+                if (group >= third) item = tk.n_items - 1u - (idx - third);  // the last n_items % 3
+                else item = r == 2u ? group : tk.n_items - 1u - (2u * group + r);
+            }
+        }
+        render_patch(item);
+    };
+    run_items(tk, lane, warp_id, render_item);
 #ifdef RT_TIMING_DEBUG
     if (STATS && out.stats != nullptr && lane == 0) {
         unsigned long long t_end;
@@ -258,17 +326,7 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_AC
         }
     };
 
-    unsigned int drawn = issue_ticket(tk, lane);
-#pragma unroll 1
-    for (unsigned int r = 0; r < tk.static_rounds; ++r) trace_item(r * tk.n_warps + warp_id);
-    const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
-    unsigned int next = take_ticket(tk, drawn, lane);
-#pragma unroll 1
-    while (next < tk.n_tickets) {
-        drawn = issue_ticket(tk, lane);
-        trace_item(first_dynamic + next);
-        next = take_ticket(tk, drawn, lane);
-    }
+    run_items(tk, lane, warp_id, trace_item);
     flush_counters<STATS>(k, out.stats);
 }
 

@@ -61,7 +61,7 @@ cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParam
     const unsigned int rounds = n_items / tk.n_warps;
     const bool all_tickets = rounds <= RT_SHORT_LAUNCH_ROUNDS || sp.n_spheres >= RT_COSTLY_ITEM_SPHERES;
     if (all_tickets) {
-        tk.reversed = camera ? 1u : 0u;
+        tk.reversed = camera ? (out.wide_patches && out.even_stores ? 2u : 1u) : 0u;
         tk.static_rounds = rounds >= 1u ? 1u : 0u;
     } else {
         tk.reversed = 0u;
@@ -72,23 +72,31 @@ cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParam
     return cudaGetLastError();
 }
 
-cudaError_t render_rows(bool stats, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
-                        cudaStream_t stream) {
+template <int PW>
+cudaError_t render_rows_patch(bool stats, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
+                              cudaStream_t stream) {
     const int rows = cp.n_rows;
-    if (rows <= 0 || cp.width <= 0) return cudaSuccess;
-    const unsigned long long tiles_x = (unsigned long long)(cp.width + kWarpTileW - 1) / kWarpTileW;
-    const unsigned long long tiles_y = (unsigned long long)(rows + kWarpTileH - 1) / kWarpTileH;
+    constexpr int kPatchH = 32 / PW;
+    const unsigned long long tiles_x = (unsigned long long)(cp.width + PW - 1) / PW;
+    const unsigned long long tiles_y = (unsigned long long)(rows + kPatchH - 1) / kPatchH;
     const unsigned long long n = tiles_x * tiles_y;
     if (sp.accel != nullptr) {
-        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, true>, kBlockThreads, sp, cp, out, n, stream, true);
-        return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, true>, kBlockThreads, sp, cp, out, n, stream, true);
+        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, true, PW>, kBlockThreads, sp, cp, out, n, stream, true);
+        return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, true, PW>, kBlockThreads, sp, cp, out, n, stream, true);
     }
     if (big_blocks(sp.n_spheres)) {
-        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads, false>, kBigBlockThreads, sp, cp, out, n, stream, true);
-        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads, false>, kBigBlockThreads, sp, cp, out, n, stream, true);
+        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads, false, PW>, kBigBlockThreads, sp, cp, out, n, stream, true);
+        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads, false, PW>, kBigBlockThreads, sp, cp, out, n, stream, true);
     }
-    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, false>, kBlockThreads, sp, cp, out, n, stream, true);
-    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, false>, kBlockThreads, sp, cp, out, n, stream, true);
+    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, false, PW>, kBlockThreads, sp, cp, out, n, stream, true);
+    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, false, PW>, kBlockThreads, sp, cp, out, n, stream, true);
+}
+
+cudaError_t render_rows(bool stats, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
+                        cudaStream_t stream) {
+    if (cp.n_rows <= 0 || cp.width <= 0) return cudaSuccess;
+    if (out.wide_patches) return render_rows_patch<kWideTileW>(stats, sp, cp, out, stream);
+    return render_rows_patch<kWarpTileW>(stats, sp, cp, out, stream);
 }
 
 cudaError_t trace_rays(bool stats, const SceneParams& sp, const RayBatch& rb, const OutputParams& out,

@@ -25,6 +25,9 @@ RT_FLAG_ALL_POINT_LIGHTS = 1
 RT_FLAG_IMAGE_ORDER = 2
 RT_FLAG_NO_ACCEL = 4
 RT_FLAG_ACCEL_FAST_BUILD = 8
+RT_FLAG_WIDE_STORES = 16
+RT_FLAG_RGB8 = 32
+RT_FLAG_EVEN_STORES = 64
 RT_ACCEL_AUTO_SPHERES = 32
 RT_IPC_HANDLE_BYTES = 64
 RT_DTYPE_F32 = 0

@@ -273,9 +273,12 @@ class CudaRenderer(Renderer):
         return CameraRays(self, camera, row0, row1)
 
     def render_rows(self, flat: FlatScene, camera: Camera, row0: int, row1: int, *, planes=None,
-                    rgba8=None, want_rgba8: bool = False) -> DeviceColor:
+                    rgba8=None, want_rgba8: bool = False, flags: int = 0) -> DeviceColor:
         """Launch the camera-ray kernel for rows ``[row0, row1)`` into (optionally
-        caller-supplied) device buffers.  Asynchronous on torch's current stream."""
+        caller-supplied) device buffers.  ``flags``: launch options of ``include/rt_abi.h``
+        (``RT_FLAG_WIDE_STORES``: 32x1 patches; ``RT_FLAG_RGB8``: the 8-bit image has 3 bytes per
+        pixel) -- they change how the frame is stored, never its values.  Asynchronous on
+        torch's current stream."""
         torch = _require_cuda(self.device)
         lib = abi.load()
         dev = torch.device("cuda", self.device)
@@ -284,9 +287,9 @@ class CudaRenderer(Renderer):
         if planes is None:
             planes = torch.empty((3, n), dtype=self._torch_dtype(), device=dev)
         if rgba8 is None and want_rgba8:
-            rgba8 = torch.empty((n, 4), dtype=torch.uint8, device=dev)
+            rgba8 = torch.empty((n, 3 if flags & abi.RT_FLAG_RGB8 else 4), dtype=torch.uint8, device=dev)
         stats = self._new_stats()
-        env = self._env(flat)
+        env = self._env(flat, flags)
         cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
         abi.check(
             lib.rt_render_rows_dev(
@@ -300,7 +303,7 @@ class CudaRenderer(Renderer):
         return DeviceColor(planes, rgba8, stats, self.device)
 
     def render_strips(self, flat: FlatScene, camera: Camera, shard: Any, *, planes=None, rgba8=None,
-                      want_rgba8: bool = False) -> DeviceColor:
+                      want_rgba8: bool = False, flags: int = 0) -> DeviceColor:
         """Launch the camera-ray kernel for an interleaved shard of the frame
         (``sharding.StripShard``: strips ``rank, rank + world, ...`` of ``strip_rows`` rows)
         through ``rt_render_strips_dev``.  The result holds the shard's rows packed in strip
@@ -318,9 +321,9 @@ class CudaRenderer(Renderer):
         if planes is None:
             planes = torch.empty((3, n), dtype=self._torch_dtype(), device=dev)
         if rgba8 is None and want_rgba8:
-            rgba8 = torch.empty((n, 4), dtype=torch.uint8, device=dev)
+            rgba8 = torch.empty((n, 3 if flags & abi.RT_FLAG_RGB8 else 4), dtype=torch.uint8, device=dev)
         stats = self._new_stats()
-        env = self._env(flat)
+        env = self._env(flat, flags)
         cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
         abi.check(
             lib.rt_render_strips_dev(
@@ -333,15 +336,17 @@ class CudaRenderer(Renderer):
         )
         return DeviceColor(planes, rgba8, stats, self.device)
 
-    def render_strips_into(self, flat: FlatScene, camera: Camera, shard: Any, frame_rgba8_ptr: int) -> None:
+    def render_strips_into(self, flat: FlatScene, camera: Camera, shard: Any, frame_rgba8_ptr: int, *,
+                           flags: int = 0) -> None:
         """Render this rank's strips straight into a whole-frame RGBA8 buffer at
         ``frame_rgba8_ptr`` (``RT_FLAG_IMAGE_ORDER``): local memory or a peer GPU's
-        framebuffer (``sharding.PeerFrame``).  No linear planes are written.
-        Asynchronous on torch's current stream."""
+        framebuffer (``sharding.PeerFrame``).  No linear planes are written.  ``flags`` as in
+        ``render_rows`` (a ``PeerFrame(channels=3)`` needs ``RT_FLAG_RGB8``; peer frames of many
+        writers want ``RT_FLAG_WIDE_STORES``).  Asynchronous on torch's current stream."""
         _require_cuda(self.device)
         lib = abi.load()
         spheres, lights = self.upload_scene(flat)
-        env = self._env(flat, abi.RT_FLAG_IMAGE_ORDER)
+        env = self._env(flat, abi.RT_FLAG_IMAGE_ORDER | flags)
         cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
         abi.check(
             lib.rt_render_strips_dev(

@@ -156,7 +156,8 @@ class _DeviceBytes:
 
 
 class PeerFrame:
-    """A whole-frame RGBA8 buffer on rank ``dst`` that every rank of the node can write.
+    """A whole-frame RGBA8 (or, ``channels=3``, RGB8) buffer on rank ``dst`` that every rank of
+    the node can write.
 
     Rank ``dst`` owns the memory (``rt_peer_buffer_create``) and sends the 64-byte IPC handle
     to the other ranks (``broadcast_object_list``); they map it (``rt_peer_buffer_open``)
@@ -168,7 +169,7 @@ class PeerFrame:
     """
 
     def __init__(self, height: int, width: int, rank: int, world: int, device: int, dst: int = 0,
-                 group: Any = None) -> None:
+                 group: Any = None, channels: int = 4) -> None:
         import ctypes as C
 
         import torch
@@ -176,14 +177,16 @@ class PeerFrame:
 
         from . import abi
 
+        if channels not in (3, 4):
+            raise ValueError(f"a peer frame has 3 (RT_FLAG_RGB8) or 4 bytes per pixel, not {channels}")
         self.height, self.width, self.rank, self.world, self.device, self.dst = height, width, rank, world, device, dst
-        self.group = group
+        self.group, self.channels = group, channels
         self._lib = abi.load()
         self._owner = rank == dst
         ptr = C.c_void_p()
         handle = C.create_string_buffer(abi.RT_IPC_HANDLE_BYTES)
         if self._owner:
-            abi.check(self._lib.rt_peer_buffer_create(device, height * width * 4, C.byref(ptr), handle), "rt_peer_buffer_create")
+            abi.check(self._lib.rt_peer_buffer_create(device, height * width * channels, C.byref(ptr), handle), "rt_peer_buffer_create")
         box = [handle.raw if self._owner else None]
         if world > 1:
             dist.broadcast_object_list(box, src=dst, group=group)
@@ -193,7 +196,7 @@ class PeerFrame:
         # the owner reads the frame through torch; the writers only need the pointer
         self.frame = None
         if self._owner:
-            self.frame = torch.as_tensor(_DeviceBytes(self.ptr, (height, width, 4), "|u1"), device=torch.device("cuda", device))
+            self.frame = torch.as_tensor(_DeviceBytes(self.ptr, (height, width, channels), "|u1"), device=torch.device("cuda", device))
 
     def complete(self) -> Optional[Any]:
         """Wait until every rank's kernel has finished writing; returns the frame on the owner."""

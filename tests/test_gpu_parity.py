@@ -362,6 +362,56 @@ def test_image_order_shards_fill_one_framebuffer(rt):
         assert np.array_equal(frame.cpu().numpy(), want8), name
 
 
+def test_wide_stores_and_rgb8_keep_every_pixel(rt):
+    """RT_FLAG_WIDE_STORES (32x1 patches, 128-byte stores) and RT_FLAG_RGB8 (3-byte pixels,
+    packed into words by the warp where the width allows, byte stores elsewhere) change how a
+    frame is stored, never what is stored: linear planes bit-identical to the default launch,
+    8-bit pixels equal to its RGBA8 without the A; RT_FLAG_EVEN_STORES only reorders the patches.  Widths that are and are not multiples of
+    4 and 32, bands, strips, image order, with and without the sphere tree."""
+    import torch
+
+    from python_ray_tracer_b200.infrastructure.cuda import abi, sharding
+
+    wide, rgb8, even = abi.RT_FLAG_WIDE_STORES, abi.RT_FLAG_RGB8, abi.RT_FLAG_EVEN_STORES
+    for name in ("readme_160x90", "readme_37x23", "readme_1x7", "readme_9x1", "c2_readme_1080p_subset", "c3_small_48_192x108_depth8"):
+        case = load_case(name)
+        cam = _camera(case)
+        w, h = case.width, case.height
+        for precision in PRECISIONS:
+            renderer = rt(precision)
+            full = _render(renderer, case)
+            want, want8 = full.numpy(), full.rgba8.cpu().numpy()
+            for flags in (wide, rgb8, wide | rgb8, wide | even, wide | rgb8 | even):
+                got = renderer.render_rows(case.flat, cam, 0, h, want_rgba8=True, flags=flags)
+                assert np.array_equal(got.numpy(), want), (name, precision, flags)
+                got8 = got.rgba8.cpu().numpy()
+                assert got8.shape == (w * h, 3 if flags & rgb8 else 4)
+                assert np.array_equal(got8[:, :3], want8[:, :3]), (name, precision, flags)
+                assert got.counters() == full.counters()
+            if h >= 8:  # a band that starts and ends off the patch grid
+                r0, r1 = 3, h - 2
+                band = renderer.render_rows(case.flat, cam, r0, r1, want_rgba8=True, flags=wide | rgb8)
+                assert np.array_equal(band.numpy(), want[:, r0 * w:r1 * w])
+                assert np.array_equal(band.rgba8.cpu().numpy(), want8[r0 * w:r1 * w, :3])
+        # image order, 3 shards into one RGB8 frame whose bytes around it must stay untouched
+        renderer = rt("fast")
+        want8 = _render(renderer, case).rgba8.cpu().numpy().reshape(h, w, 4)[:, :, :3]
+        guard = 64
+        buf = torch.full((guard + h * w * 3 + guard,), 0xA5, dtype=torch.uint8, device="cuda")
+        for s in sharding.strip_shards(h, 3, 4):
+            renderer.render_strips_into(case.flat, cam, s, buf.data_ptr() + guard, flags=wide | rgb8)
+        host = buf.cpu().numpy()
+        assert (host[:guard] == 0xA5).all() and (host[-guard:] == 0xA5).all()
+        assert np.array_equal(host[guard:-guard].reshape(h, w, 3), want8), name
+    # the tree kernels have their own instantiations of the wide patch
+    case = load_case("readme_160x90")
+    tree = rt("fast", accel=True)
+    plain = _render(tree, case)
+    got = tree.render_rows(case.flat, _camera(case), 0, case.height, want_rgba8=True, flags=wide | rgb8)
+    assert np.array_equal(got.numpy(), plain.numpy())
+    assert np.array_equal(got.rgba8.cpu().numpy(), plain.rgba8.cpu().numpy()[:, :3])
+
+
 def _peer_writer(rank, world, port, name, strip_rows, out):
     import torch
     import torch.distributed as dist

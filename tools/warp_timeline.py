@@ -49,6 +49,9 @@ dur = (items[:, 1] - items[:, 0]) / 1e3
 iend = (items[:, 1] - t0) / 1e3
 istart = (items[:, 0] - t0) / 1e3
 print(f"items {len(dur)}: duration p50 {np.median(dur):.2f} p90 {np.percentile(dur, 90):.2f} p99 {np.percentile(dur, 99):.2f} max {dur.max():.2f} us")
+good = dur > 0
+print(f"time inside items / warp residency = {dur[good].sum() / (end - start).sum():.3f}   "
+      f"(items {dur[good].sum() / len(t):.1f} us per warp, residency {np.mean(end - start):.1f} us, {good.sum() / len(t):.1f} items per warp)")
 late = np.argsort(iend)[-12:]
 tiles_x = (w + 7) // 8
 for i in late:
