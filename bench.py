@@ -281,11 +281,18 @@ def run_b200_arm(args) -> None:
     stats = torch.zeros(4, dtype=torch.int64, device=dev)
     flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
     peer = None
+    peer_layout = None
     if banded and args.exchange == "peer":
-        # rank 0 owns the whole-frame RGBA8 buffer; the other ranks map it and their kernels
-        # store into it over NVLink while they render (no gather, no permutation)
-        peer = sharding.PeerFrame(height, width, rank, world, local, dst=0)
+        # rank 0 owns the whole-frame 8-bit buffer; the other ranks map it and their kernels
+        # store into it over NVLink while they render (no gather, no permutation).  Up to four
+        # writers rank 0's port keeps up with 32-byte row segments of 8x4 patches; from eight on
+        # the frame goes out as 96-byte rows of 32x1 patches of 3-byte pixels, the patches taken
+        # from both ends of the shard (profiles/r01/c4_store_layouts.txt).
+        peer_layout = args.peer_layout if args.peer_layout != "auto" else ("rgb8-wide" if world >= 8 else "rgba8")
         env_flags = abi.RT_FLAG_IMAGE_ORDER
+        if peer_layout == "rgb8-wide":
+            env_flags |= abi.RT_FLAG_WIDE_STORES | abi.RT_FLAG_RGB8 | abi.RT_FLAG_EVEN_STORES
+        peer = sharding.PeerFrame(height, width, rank, world, local, dst=0, channels=3 if peer_layout == "rgb8-wide" else 4)
         for i, (sph, lig, env, flat_) in enumerate(tables):
             env.flags |= env_flags
 
@@ -360,7 +367,7 @@ def run_b200_arm(args) -> None:
         peer.close()
         peer = None
         for _, _, env, _ in tables:
-            env.flags &= ~abi.RT_FLAG_IMAGE_ORDER
+            env.flags &= ~(abi.RT_FLAG_IMAGE_ORDER | abi.RT_FLAG_WIDE_STORES | abi.RT_FLAG_RGB8 | abi.RT_FLAG_EVEN_STORES)
     for _, _, env, _ in tables:  # the host entry point builds its own tree (or none: --accel off)
         env.accel_dev, env.accel_bytes = None, 0
         if not use_tree:
@@ -403,7 +410,7 @@ def run_b200_arm(args) -> None:
     # ---- rooflines of the trace kernel (rank 0's launch)
     kernel_ms = float(step_ms.mean())
     peaks = measured_peaks()
-    bytes_per_pixel = 4.0 if (banded and args.exchange == "peer") else BYTES_PER_PIXEL
+    bytes_per_pixel = (3.0 if peer_layout == "rgb8-wide" else 4.0) if (banded and args.exchange == "peer") else BYTES_PER_PIXEL
     achieved_gbs = bytes_per_pixel * n / (kernel_ms * 1e-3) / 1e9
     fp64 = C.c_double(0.0)
     fp32 = C.c_double(0.0)
@@ -423,8 +430,8 @@ def run_b200_arm(args) -> None:
                    "max_depth": max_depth or None, "precision": args.precision, "cutoff": args.cutoff,
                    "accel": ("sphere BVH (rt_accel_build_host): built before the timed region for `value`, inside it for `e2e`"
                              if use_tree else "none: every ray tests every sphere"),
-                   "output": ("whole-frame RGBA8 on rank 0 (fused quantisation), no linear planes" if banded and args.exchange == "peer" else "planar f32 linear RGB + RGBA8 (fused quantisation)"),
-                   "parallelism": (("interleaved 16-row strips x%d, kernels store RGBA8 into rank 0's framebuffer over NVLink peer memory (no gather)" % world)
+                   "output": (("whole-frame %s on rank 0 (fused quantisation), no linear planes" % ("RGB8, 32x1 patches" if peer_layout == "rgb8-wide" else "RGBA8, 8x4 patches")) if banded and args.exchange == "peer" else "planar f32 linear RGB + RGBA8 (fused quantisation)"),
+                   "parallelism": (("interleaved 16-row strips x%d, kernels store the 8-bit frame into rank 0's framebuffer over NVLink peer memory (no gather)" % world)
                                    if args.exchange == "peer" else ("interleaved 16-row strips x%d + NCCL gather of RGBA8 to rank 0 + row permutation" % world)) if banded else ("frame-sharded x%d, no collective" % world),
                    "l2": "512 MiB buffer written between timed steps (L2 flush); each step timed by its own CUDA event pair"},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_value, "h2d_bytes_per_step": h2d,
@@ -478,6 +485,8 @@ def main() -> None:
     parser.add_argument("--no-cpu-baseline", action="store_true")
     parser.add_argument("--accel", choices=["auto", "on", "off"], default="auto",
                         help="sphere BVH: auto = scenes of RT_ACCEL_AUTO_SPHERES shapes or more")
+    parser.add_argument("--peer-layout", choices=["auto", "rgba8", "rgb8-wide"], default="auto",
+                        help="c4 with --exchange peer: how the frame is stored into rank 0's buffer (auto: rgb8-wide from 8 ranks on)")
     parser.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
                         help="c4 with N > 1: kernels store into rank 0's framebuffer over NVLink (peer) or "
                              "render locally and gather with NCCL (nccl)")
