@@ -194,6 +194,28 @@ def test_ctypes_structs_match_the_header_as_compiled(tmp_path):
     assert got == want
 
 
+def test_python_constants_match_the_header_as_compiled(tmp_path):
+    """Every integer constant abi.py mirrors (flags, modes, dtypes, status codes, sizes) is
+    printed by a C program compiled against include/rt_abi.h and compared by name."""
+    import re
+    import subprocess
+
+    names = [n for n in dir(abi) if re.fullmatch(r"RT_[A-Z0-9_]+", n) and isinstance(getattr(abi, n), int)]
+    assert {"RT_FLAG_WIDE_STORES", "RT_FLAG_RGB8", "RT_FLAG_EVEN_STORES", "RT_FLAG_IMAGE_ORDER", "RT_ABI_VERSION"} <= set(names)
+    status = sorted(abi.STATUS_NAMES.values())  # status codes are kept by name in abi.STATUS_NAMES
+    src = tmp_path / "constants.c"
+    src.write_text('#include <stdio.h>\n#include "rt_abi.h"\nint main(void){\n'
+                   + "".join(f'printf("{n} %lld\\n", (long long)({n}));\n' for n in names + status) + "return 0;}\n")
+    exe = tmp_path / "constants"
+    subprocess.run(["/usr/bin/gcc", "-I", str(ROOT / "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    got = dict(zip(out[0::2], (int(v) for v in out[1::2])))
+    assert {n: got[n] for n in names} == {n: getattr(abi, n) for n in names}
+    assert {got[n]: n for n in status} == abi.STATUS_NAMES
+    flags = [v for n, v in got.items() if n.startswith("RT_FLAG_") and v]
+    assert len(set(flags)) == len(flags) and all(v & (v - 1) == 0 for v in flags)  # distinct single bits
+
+
 def test_abi_rejects_bad_arguments_without_a_gpu():
     lib = abi.load()
     cam = abi.make_camera((0, 0.2, -2), 16, 9)
