@@ -437,7 +437,7 @@ def run_b200_arm(args) -> None:
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_value, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "d2h_gb_per_s_per_gpu": d2h / (e2e_ms_value * 1e-3) / 1e9,
                 "host_cpus_bound": len(bound) if bound else None,
-                "api": "rt_render_frame_host: scene upload + kernel + D2H of the f32 linear planes into pinned host memory, row chunks pipelined (kernel of chunk i+1 under the copy of chunk i)",
+                "api": "rt_render_frame_host: scene upload + kernel + D2H of the f32 linear planes into pinned host memory, row chunks pipelined (kernel of chunk i+1 under the copy of chunk i, small first chunk, one strided copy per chunk)",
                 "with_rgb8": {"ms_per_step": e2e_rgb8_ms, "value": pixels_per_step / (e2e_rgb8_ms * 1e-3) / 1e6,
                               "d2h_bytes_per_step": d2h + rgb8_host.numel()},
                 # what render_image_pipeline needs on the host: only the 8-bit image save_image writes

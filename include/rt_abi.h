@@ -302,7 +302,9 @@ int rt_quantize_dev(int device, const void* rgb_dev, int32_t rgb_dtype, int64_t 
  * Host-buffer entry points: the same operations with ordinary host memory on both
  * sides; uploads, launches, downloads and synchronises internally.
  *   rgb_host    planar, 3 x n doubles or floats (plane stride = n), may be NULL
- *   rgb8_host   interleaved RGB bytes (3 per pixel), may be NULL
+ *   rgb8_host   interleaved RGB bytes (3 per pixel), uint8(255*clip(v,0,1)) truncating of
+ *               the FP64 pixel (base.py:143-151), quantised by the trace kernel; may be
+ *               NULL.  With rgb_host NULL no linear planes are written at all.
  *   stats_host  RT_STATS_WORDS x uint64, may be NULL
  */
 int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spheres,

@@ -179,9 +179,13 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
     env = &with_tree;
     const int64_t n = (int64_t)(row1 - row0) * cam->width;
     const size_t elem = rgb_dtype == RT_DTYPE_F64 ? 8 : 4;
-    // the quantiser reads the linear planes, so they are rendered even if only bytes are wanted
-    HOST_CUDA(reserve(c->rgb, (size_t)n * 3 * elem + 16));
-    if (rgb8_host != nullptr) HOST_CUDA(reserve(c->rgb8, (size_t)n * 3 + 16));
+    // the 8-bit image is quantised by the trace kernel itself, from the FP64 pixel (what
+    // save_image does, base.py:143-151): no linear planes unless the caller wants them
+    if (rgb_host != nullptr) HOST_CUDA(reserve(c->rgb, (size_t)n * 3 * elem + 16));
+    if (rgb8_host != nullptr) {
+        HOST_CUDA(reserve(c->rgb8, (size_t)n * 3 + 16));
+        with_tree.flags |= RT_FLAG_RGB8;
+    }
     if (stats_host != nullptr) {
         HOST_CUDA(reserve(c->stats, sizeof(uint64_t) * RT_STATS_WORDS));
         HOST_CUDA(cudaMemsetAsync(c->stats.ptr, 0, sizeof(uint64_t) * RT_STATS_WORDS, c->stream));
@@ -194,29 +198,41 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
     if (n >= (int64_t)1 << 20) chunks = 4;
     if (n >= (int64_t)1 << 23) chunks = kMaxChunks;
     if (chunks > rows) chunks = rows > 0 ? rows : 1;
+    // Nothing is copied while the first chunk renders, so it is a small one: with more than one
+    // chunk the first takes 1/16 of the rows and the others share the rest evenly.
+    auto chunk_start = [&](int i) -> int {
+        if (i <= 0) return 0;
+        if (i >= chunks) return rows;
+        const int64_t head = rows / 16;
+        return (int)((head + ((int64_t)rows - head) * (i - 1) / (chunks - 1)) & ~3LL);  // multiples of 4 rows (the patch height)
+    };
     char* rgb_base = static_cast<char*>(c->rgb.ptr);
     uint64_t* stats_dev = stats_host != nullptr ? static_cast<uint64_t*>(c->stats.ptr) : nullptr;
     for (int i = 0; i < chunks && n > 0; ++i) {
-        // chunk boundaries on multiples of 4 rows (the patch height)
-        const int r0 = row0 + (int)(((int64_t)rows * i / chunks) & ~3LL);
-        const int r1 = i + 1 == chunks ? row1 : row0 + (int)(((int64_t)rows * (i + 1) / chunks) & ~3LL);
+        const int r0 = row0 + chunk_start(i), r1 = row0 + chunk_start(i + 1);
         if (r1 <= r0) continue;
         const int64_t first = (int64_t)(r0 - row0) * cam->width, count = (int64_t)(r1 - r0) * cam->width;
-        rc = rt_render_rows_dev(device, spheres_dev, n_spheres, lights_dev, env, cam, r0, r1, rgb_base + first * elem,
-                                rgb_dtype, n, nullptr, stats_dev, c->stream);
+        rc = rt_render_rows_dev(device, spheres_dev, n_spheres, lights_dev, env, cam, r0, r1,
+                                rgb_host != nullptr ? rgb_base + first * elem : nullptr, rgb_dtype, n,
+                                rgb8_host != nullptr ? static_cast<uint8_t*>(c->rgb8.ptr) + first * 3 : nullptr, stats_dev,
+                                c->stream);
         if (rc != RT_OK) return rc;
-        if (rgb8_host != nullptr) {
-            rc = rt_quantize_dev(device, rgb_base + first * elem, rgb_dtype, n, count,
-                                 static_cast<uint8_t*>(c->rgb8.ptr) + first * 3, 3, c->stream);
-            if (rc != RT_OK) return rc;
-        }
         HOST_CUDA(cudaEventRecord(c->rendered[i], c->stream));
         HOST_CUDA(cudaStreamWaitEvent(c->copy_stream, c->rendered[i], 0));
         if (rgb_host != nullptr) {
-            for (int ch = 0; ch < 3; ++ch)
-                HOST_CUDA(cudaMemcpyAsync(static_cast<char*>(rgb_host) + ((size_t)ch * n + first) * elem,
-                                          rgb_base + ((size_t)ch * n + first) * elem, (size_t)count * elem,
-                                          cudaMemcpyDeviceToHost, c->copy_stream));
+            // the chunk's rows of the three planes: one strided copy (three when a plane is
+            // longer than a 2-D copy's pitch may be)
+            const size_t pitch = (size_t)n * elem;
+            if (pitch <= ((size_t)1 << 30)) {
+                HOST_CUDA(cudaMemcpy2DAsync(static_cast<char*>(rgb_host) + (size_t)first * elem, pitch,
+                                            rgb_base + (size_t)first * elem, pitch, (size_t)count * elem, 3,
+                                            cudaMemcpyDeviceToHost, c->copy_stream));
+            } else {
+                for (int ch = 0; ch < 3; ++ch)
+                    HOST_CUDA(cudaMemcpyAsync(static_cast<char*>(rgb_host) + ((size_t)ch * n + first) * elem,
+                                              rgb_base + ((size_t)ch * n + first) * elem, (size_t)count * elem,
+                                              cudaMemcpyDeviceToHost, c->copy_stream));
+            }
         }
         if (rgb8_host != nullptr)
             HOST_CUDA(cudaMemcpyAsync(rgb8_host + first * 3, static_cast<uint8_t*>(c->rgb8.ptr) + first * 3,

@@ -184,6 +184,17 @@ def test_host_buffer_entry_points(c_oracle):
     abi.check(rc, "rt_render_frame_host")
     assert_linear_parity(rgb, case.rgb, EXACT_TOL, "host entry")
     assert np.array_equal(rgb8, c_oracle.quantize(rgb)) and int(stats[0]) == case.traced
+    # the 8-bit image alone (no linear planes are rendered), and beside float32 planes: same bytes
+    only8 = np.zeros((n, 3), dtype=np.uint8)
+    rc = lib.rt_render_frame_host(0, ptr(flat.spheres), flat.n_spheres, ptr(flat.point_lights), C.byref(env),
+                                  C.byref(cam), 0, h, None, abi.RT_DTYPE_F32, ptr(only8), None)
+    abi.check(rc, "rt_render_frame_host rgb8 only")
+    assert np.array_equal(only8, rgb8)
+    band8, band32 = np.zeros((5 * w, 3), dtype=np.uint8), np.empty((3, 5 * w), dtype=np.float32)
+    rc = lib.rt_render_frame_host(0, ptr(flat.spheres), flat.n_spheres, ptr(flat.point_lights), C.byref(env),
+                                  C.byref(cam), 41, 46, ptr(band32), abi.RT_DTYPE_F32, ptr(band8), None)
+    abi.check(rc, "rt_render_frame_host band f32 + rgb8")
+    assert np.array_equal(band8, rgb8[41 * w:46 * w]) and np.array_equal(band32, rgb[:, 41 * w:46 * w].astype(np.float32))
     # float32 output plane
     rgb32 = np.empty((3, n), dtype=np.float32)
     rc = lib.rt_render_frame_host(0, ptr(flat.spheres), flat.n_spheres, ptr(flat.point_lights), C.byref(env),
