@@ -6,6 +6,9 @@
 #ifndef RT_PEEL_PRIMARY
 #define RT_PEEL_PRIMARY 1
 #endif
+#ifndef RT_FUSE_NEXT_HIT
+#define RT_FUSE_NEXT_HIT 0  // experiment (rt_chain_fused.cuh): shadow test and the mirror ray's nearest hit in one loop
+#endif
 
 namespace rt {
 
@@ -111,6 +114,12 @@ __device__ __forceinline__ Staged stage_scene(const SceneParams& sp, unsigned ch
     }
     return st;
 }
+
+}  // namespace rt
+#if RT_FUSE_NEXT_HIT
+#include "rt_chain_fused.cuh"
+#endif
+namespace rt {
 
 // One camera or user ray through the scene: raytrace_scene (base.py:91-121) with the
 // recursion of shader.py:143-161 unrolled into a loop.  Exact ties between two shapes
@@ -293,6 +302,9 @@ __device__ __forceinline__ bool bounce(const SceneParams& sp, const Staged& st, 
 template <int MODE, bool STATS, bool CAMERA, bool ACCEL>
 __device__ __forceinline__ Vec3 trace_chain(const SceneParams& sp, const Staged& st, const AccelView& av, Vec3 o,
                                             Vec3 d, Counters& k) {
+#if RT_FUSE_NEXT_HIT
+    if constexpr (MODE == kModeFast && !ACCEL) return trace_chain_fused<STATS, CAMERA>(sp, st, o, d, k);
+#endif
     Vec3 color = {0.0, 0.0, 0.0};
     double weight = 1.0;
     unsigned long long tests = 0;
