@@ -318,6 +318,24 @@ int rt_trace_rays_host(int device, const double* spheres_host, int32_t n_spheres
                        const double* directions_host, int64_t n_rays, void* rgb_host,
                        int32_t rgb_dtype, uint64_t* stats_host);
 
+/*
+ * rt_png_deflate_rows -- the compressed stream of the PNG save_image writes (base.py:143-151:
+ * the reference hands its uint8 array to Pillow, i.e. zlib level 6, 0.45 s per 1080p frame).
+ * Host code, no GPU involved; for animation batches, where the encoder bounds the frame rate.
+ * Compresses `rows` rows of 8-bit pixels (pixel_bytes = 3: R,G,B; 4: R,G,B,A with A dropped;
+ * rows row_stride bytes apart) into RAW deflate of the PNG-filtered rows (filter 1, Sub; runs at
+ * distance 1 and 3; one dynamic-Huffman block, or stored blocks when smaller).  A band that is
+ * not the `last` of its image ends byte-aligned with BFINAL clear, so bands compressed
+ * concurrently concatenate into one stream: the IDAT payload is 0x78 0x01, the bands in order,
+ * and the big-endian Adler-32 of all filtered bytes (combine the bands' `adler_out` with their
+ * `raw_bytes_out`, as zlib's adler32_combine does).  Decoded pixels equal the input.
+ *   rt_png_deflate_bound(width, rows)  capacity `out` must have
+ */
+int64_t rt_png_deflate_bound(int32_t width, int32_t rows);
+int rt_png_deflate_rows(const uint8_t* pixels, int32_t width, int32_t rows, int32_t pixel_bytes,
+                        int64_t row_stride, int32_t last, uint8_t* out, int64_t capacity,
+                        int64_t* bytes_out, uint32_t* adler_out, int64_t* raw_bytes_out);
+
 #ifdef __cplusplus
 }
 #endif

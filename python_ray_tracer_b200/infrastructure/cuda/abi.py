@@ -155,6 +155,12 @@ PROTOTYPES = {
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), _P, C.POINTER(C.c_double), _P, C.c_int64,
          _P, C.c_int32, _P],
     ),
+    "rt_png_deflate_bound": (C.c_int64, [C.c_int32, C.c_int32]),
+    "rt_png_deflate_rows": (
+        C.c_int,
+        [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, _P, C.c_int64,
+         C.POINTER(C.c_int64), C.POINTER(C.c_uint32), C.POINTER(C.c_int64)],
+    ),
 }
 
 LIBRARY_NAME = "librt_b200.so"

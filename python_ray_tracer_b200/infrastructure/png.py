@@ -74,6 +74,79 @@ def encode_png_parallel(rgb8: np.ndarray, compress_level: int = 1, threads: int 
     return b"".join((_SIGNATURE, _chunk(b"IHDR", header), _chunk(b"IDAT", stream), _chunk(b"IEND", b"")))
 
 
+def adler32_combine(adler1: int, adler2: int, len2: int) -> int:
+    """Adler-32 of two concatenated byte strings from their own checksums and the length of
+    the second (zlib's ``adler32_combine``, which Python's ``zlib`` does not expose)."""
+    base = 65521
+    rem = len2 % base
+    sum1 = adler1 & 0xFFFF
+    sum2 = (rem * sum1) % base
+    sum1 += (adler2 & 0xFFFF) + base - 1
+    sum2 += ((adler1 >> 16) & 0xFFFF) + ((adler2 >> 16) & 0xFFFF) + base - rem
+    if sum1 >= base:
+        sum1 -= base
+    if sum1 >= base:
+        sum1 -= base
+    if sum2 >= (base << 1):
+        sum2 -= base << 1
+    if sum2 >= base:
+        sum2 -= base
+    return (sum2 << 16) | sum1
+
+
+def _fast_band(args):
+    """One band through ``rt_png_deflate_rows`` (ctypes releases the GIL for the call)."""
+    import ctypes as C
+
+    from .cuda import abi
+
+    lib, band, last = args
+    rows, width, channels = band.shape
+    capacity = int(lib.rt_png_deflate_bound(width, rows))
+    out = np.empty(capacity, dtype=np.uint8)
+    used, adler, raw = C.c_int64(0), C.c_uint32(0), C.c_int64(0)
+    abi.check(lib.rt_png_deflate_rows(band.ctypes.data, width, rows, channels, band.strides[0], 1 if last else 0,
+                                      out.ctypes.data, capacity, C.byref(used), C.byref(adler), C.byref(raw)),
+              "rt_png_deflate_rows")
+    return out[: used.value].tobytes(), int(adler.value), int(raw.value)
+
+
+def encode_png_fast(pixels: np.ndarray, threads: int = 1, pool=None) -> bytes:
+    """PNG of ``pixels`` (uint8 ``[H, W, 3]`` or ``[H, W, 4]``; alpha is dropped) through the
+    library's own deflate (``rt_png_deflate_rows``: Sub filter, runs at distance 1 and 3,
+    one dynamic-Huffman block per band): about 8x faster than zlib level 1 on rendered
+    frames at the same size.  Bands are compressed concurrently and concatenated like
+    ``encode_png_parallel``'s.  Decoded pixels are identical to every other encoder's."""
+    from .cuda import abi
+
+    if pixels.dtype != np.uint8 or pixels.ndim != 3 or pixels.shape[2] not in (3, 4):
+        raise ValueError("expected uint8 [H, W, 3] or [H, W, 4]")
+    if pixels.strides[2] != 1 or pixels.strides[1] != pixels.shape[2]:
+        pixels = np.ascontiguousarray(pixels)
+    height, width, _ = pixels.shape
+    if height == 0 or width == 0:
+        raise ValueError("empty image")
+    lib = abi.load()
+    parts = max(1, min(int(threads), height))
+    bounds = [height * i // parts for i in range(parts + 1)]
+    jobs = [(lib, pixels[bounds[i]:bounds[i + 1]], i + 1 == parts) for i in range(parts)]
+    if parts == 1:
+        done = [_fast_band(jobs[0])]
+    elif pool is not None:
+        done = list(pool.map(_fast_band, jobs))
+    else:
+        from concurrent.futures import ThreadPoolExecutor
+
+        with ThreadPoolExecutor(parts) as own:
+            done = list(own.map(_fast_band, jobs))
+    adler = done[0][1]
+    for _, a, n in done[1:]:
+        adler = adler32_combine(adler, a, n)
+    stream = b"\x78\x01" + b"".join(d[0] for d in done) + struct.pack(">I", adler & 0xFFFFFFFF)
+    header = struct.pack(">IIBBBBB", width, height, 8, 2, 0, 0, 0)
+    return b"".join((_SIGNATURE, _chunk(b"IHDR", header), _chunk(b"IDAT", stream), _chunk(b"IEND", b"")))
+
+
 def write_png(path: Path, rgb8: np.ndarray, compress_level: int = 6, threads: int = 1, pool=None) -> None:
     rgb8 = np.ascontiguousarray(rgb8)
     if threads > 1 or pool is not None:

@@ -4,7 +4,8 @@
 For a batch the three stages are overlapped instead: while the GPU traces frame ``k+1``
 (``rt_render_rows_dev`` with the fused RGBA8 store), frame ``k``'s 8-bit image is copied to
 pinned host memory on a second stream and earlier frames are being PNG-encoded by a pool
-of host threads (zlib releases the GIL).  The encoder, not the GPU, bounds the frame rate
+of host threads (the library's own deflate, ``rt_png_deflate_rows``: ~10 ms per 1080p frame
+per core; ctypes releases the GIL).  The encoder, not the GPU, bounds the frame rate
 (~0.1-0.4 s of zlib per 1080p frame per core against ~0.1 ms
 of tracing), so frames are sharded over ranks (frame ``k`` -> rank ``k mod world``, one
 process per GPU, nothing exchanged) and every rank runs its own encoder pool.
@@ -30,20 +31,33 @@ import numpy as np
 from . import scenes
 from .domain import Scene3D
 from .infrastructure.cuda.sharding import frames_of_rank
-from .infrastructure.png import encode_png_parallel
+from .infrastructure.png import encode_png_fast, encode_png_parallel
 
 
 def frame_path(out_dir: Path, frame: int) -> Path:
     return Path(out_dir) / f"frame_{frame:04d}.png"
 
 
+def encode_frame(rgba: np.ndarray, width: int, height: int, compress_level: Optional[int] = None, bands: int = 2,
+                 pool=None) -> bytes:
+    """PNG bytes of one frame as it comes off the GPU (``[n, 4]`` RGBA8, row-major).
+    ``compress_level=None``: the library's own deflate (``rt_png_deflate_rows``, about four times
+    faster than zlib level 1 on rendered frames and smaller; alpha dropped inside the encoder);
+    an integer: zlib at that level.  Decoded pixels are the same either way."""
+    if compress_level is None:
+        return encode_png_fast(rgba.reshape(height, width, 4), bands, pool)
+    rgb8 = np.ascontiguousarray(rgba[:, :3]).reshape(height, width, 3)
+    return encode_png_parallel(rgb8, compress_level, bands, pool)
+
+
 def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: int, out_dir: Path, *,
                   rank: int = 0, world: int = 1, encoder_threads: Optional[int] = None,
-                  compress_level: int = 1, resume: bool = True, bands_per_frame: int = 2) -> Dict[str, float]:
+                  compress_level: Optional[int] = None, resume: bool = True, bands_per_frame: int = 2) -> Dict[str, float]:
     """Render this rank's frames of an ``n_frames`` batch to ``out_dir/frame_NNNN.png``.
 
     ``scene_of_frame(k)`` builds frame ``k``'s ``Scene3D`` (``scenes.turntable_scene`` for the
-    BASELINE turntable).  Returns timing totals (seconds) and the number of frames written.
+    BASELINE turntable).  ``compress_level``: see ``encode_frame``.  Returns timing totals
+    (seconds) and the number of frames written.
     """
     import torch
 
@@ -76,8 +90,7 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
 
     def encode_and_write(frame: int, rgba: np.ndarray) -> float:
         t0 = time.perf_counter()
-        rgb8 = np.ascontiguousarray(rgba[:, :3]).reshape(height, width, 3)  # drop alpha off the main thread
-        data = encode_png_parallel(rgb8, compress_level, bands_per_frame, band_pool)
+        data = encode_frame(rgba, width, height, compress_level, bands_per_frame, band_pool)  # off the main thread
         frame_path(out_dir, frame).write_bytes(data)
         return time.perf_counter() - t0
 
@@ -132,7 +145,8 @@ def main() -> None:
     parser.add_argument("--out", type=Path, required=True)
     parser.add_argument("--width", type=int, default=1920)
     parser.add_argument("--height", type=int, default=1080)
-    parser.add_argument("--compress-level", type=int, default=1)
+    parser.add_argument("--compress-level", type=int, default=None,
+                        help="zlib level for the PNGs; default: the library's own faster deflate (rt_png_deflate_rows)")
     parser.add_argument("--encoder-threads", type=int, default=None)
     parser.add_argument("--no-resume", action="store_true")
     args = parser.parse_args()

@@ -16,6 +16,8 @@ for f in trace_exact trace_fast rt_abi rt_abi_host rt_peaks rt_accel_build; do
   $NVCC $FLAGS $extra "$@" -c "$src/$f.cu" -o "$out/$f.o" &
   pids+=($!)
 done
+${CXX:-g++} -O3 -std=c++17 -fPIC -Wall -c "$src/rt_png_host.cpp" -o "$out/rt_png_host.o" &
+pids+=($!)
 for p in "${pids[@]}"; do wait "$p"; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "$out/librt_b200.so" "$out"/*.o
 $NVCC $FLAGS "$@" -Xptxas -v -c "$src/trace_fast.cu" -o /dev/null 2>&1 | grep -A2 "render_rows_kernelILi1ELb0" | grep -E "Used|spill" | sed "s/^/[$name] /"
