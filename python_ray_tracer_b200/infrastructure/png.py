@@ -11,6 +11,7 @@ from __future__ import annotations
 import struct
 import zlib
 from pathlib import Path
+from typing import Optional
 
 import numpy as np
 
@@ -147,9 +148,12 @@ def encode_png_fast(pixels: np.ndarray, threads: int = 1, pool=None) -> bytes:
     return b"".join((_SIGNATURE, _chunk(b"IHDR", header), _chunk(b"IDAT", stream), _chunk(b"IEND", b"")))
 
 
-def write_png(path: Path, rgb8: np.ndarray, compress_level: int = 6, threads: int = 1, pool=None) -> None:
+def write_png(path: Path, rgb8: np.ndarray, compress_level: Optional[int] = 6, threads: int = 1, pool=None) -> None:
+    """``compress_level=None``: the library's own deflate (``encode_png_fast``); an integer: zlib."""
     rgb8 = np.ascontiguousarray(rgb8)
-    if threads > 1 or pool is not None:
+    if compress_level is None:
+        Path(path).write_bytes(encode_png_fast(rgb8, threads, pool))
+    elif threads > 1 or pool is not None:
         Path(path).write_bytes(encode_png_parallel(rgb8, compress_level, threads, pool))
     else:
         Path(path).write_bytes(encode_png(rgb8, compress_level))

@@ -159,3 +159,16 @@ def test_turntable_encode_stage_both_encoders(tmp_path):
         slow = turntable.encode_frame(flat, w, h, 1, 3, pool)
     _decode_all(fast, tmp_path, rgba[:, :, :3])
     _decode_all(slow, tmp_path, rgba[:, :, :3])
+
+
+def test_write_png_with_the_library_deflate(tmp_path):
+    rng = np.random.default_rng(17)
+    img = (rng.integers(0, 3, (33, 47, 3)) * 100).astype(np.uint8)
+    png.write_png(tmp_path / "fast.png", img, None)
+    png.write_png(tmp_path / "zlib.png", img, 6)
+    assert np.array_equal(png.read_png(tmp_path / "fast.png"), img)
+    assert np.array_equal(png.read_png(tmp_path / "zlib.png"), img)
+    from python_ray_tracer_b200.infrastructure import CudaRenderer
+
+    assert CudaRenderer(png_compress_level=None).png_compress_level is None
+    assert CudaRenderer().png_compress_level == 6
