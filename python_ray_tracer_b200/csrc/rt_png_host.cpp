@@ -303,11 +303,11 @@ int rt_png_deflate_rows(const uint8_t* pixels, int32_t width, int32_t rows, int3
         tokens[n_tokens++] = data[i];
         lit_hist[0][data[i]]++;
     }
-    while (i + 4 <= raw) {
-        uint32_t here, back1, back3;
-        memcpy(&here, data + i, 4);
-        memcpy(&back1, data + i - 1, 4);
-        memcpy(&back3, data + i - 3, 4);
+    while (i + 5 <= raw) {
+        // bytes i-3 .. i+4 in one load (little-endian): the three windows are shifts of it
+        uint64_t window;
+        memcpy(&window, data + i - 3, 8);
+        const uint32_t here = (uint32_t)(window >> 24), back1 = (uint32_t)(window >> 16), back3 = (uint32_t)window;
         if (here != back1 && here != back3) {
             tokens[n_tokens++] = data[i];
             lit_hist[i & 3][data[i]]++;
