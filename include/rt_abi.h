@@ -306,6 +306,7 @@ int rt_quantize_dev(int device, const void* rgb_dev, int32_t rgb_dtype, int64_t 
  *               the FP64 pixel (base.py:143-151), quantised by the trace kernel; may be
  *               NULL.  With rgb_host NULL no linear planes are written at all.
  *   stats_host  RT_STATS_WORDS x uint64, may be NULL
+ * RT_FLAG_IMAGE_ORDER in env->flags is ignored here (the outputs are the band's own buffers).
  */
 int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spheres,
                          const double* point_lights_host, const rt_env* env,

@@ -177,6 +177,9 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
     rt_env with_tree;
     if ((rc = attach_accel(*c, spheres_host, n_spheres, env, &with_tree)) != RT_OK) return rc;
     env = &with_tree;
+    // the scratch buffers hold the band, chunk by chunk: a caller's whole-frame addressing flag
+    // (meant for rt_render_rows_dev with its own frame buffer) must not reach the kernel
+    with_tree.flags &= ~RT_FLAG_IMAGE_ORDER;
     const int64_t n = (int64_t)(row1 - row0) * cam->width;
     const size_t elem = rgb_dtype == RT_DTYPE_F64 ? 8 : 4;
     // the 8-bit image is quantised by the trace kernel itself, from the FP64 pixel (what
