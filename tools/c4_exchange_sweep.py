@@ -57,46 +57,45 @@ def main() -> None:
     if args.all_layouts:
         layouts = [(0, 4, 0), (0, 3, 0), (1, 4, 0), (1, 3, 0), (1, 4, 1), (1, 3, 1)]
     for wide, channels, even in layouts:
-        if True:
-            flags = (abi.RT_FLAG_IMAGE_ORDER | (abi.RT_FLAG_WIDE_STORES if wide else 0) | (abi.RT_FLAG_RGB8 if channels == 3 else 0)
-                     | (abi.RT_FLAG_EVEN_STORES if even else 0))
-            env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, mode=abi.RT_MODE_FAST,
-                               cutoff=1e-7, flags=flags)
-            peer = sharding.PeerFrame(h, w, rank, world, local, dst=0, channels=channels)
+        flags = (abi.RT_FLAG_IMAGE_ORDER | (abi.RT_FLAG_WIDE_STORES if wide else 0) | (abi.RT_FLAG_RGB8 if channels == 3 else 0)
+                 | (abi.RT_FLAG_EVEN_STORES if even else 0))
+        env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, mode=abi.RT_MODE_FAST,
+                           cutoff=1e-7, flags=flags)
+        peer = sharding.PeerFrame(h, w, rank, world, local, dst=0, channels=channels)
 
-            def launch() -> None:
-                abi.check(lib.rt_render_strips_dev(local, sph.data_ptr(), flat.n_spheres, lig.data_ptr(), C.byref(env), C.byref(cam),
-                                                   shard.strip_rows, rank, cut, None, abi.RT_DTYPE_F32, 0, peer.ptr, None,
-                                                   int(stream.cuda_stream)), "rt_render_strips_dev")
+        def launch() -> None:
+            abi.check(lib.rt_render_strips_dev(local, sph.data_ptr(), flat.n_spheres, lig.data_ptr(), C.byref(env), C.byref(cam),
+                                               shard.strip_rows, rank, cut, None, abi.RT_DTYPE_F32, 0, peer.ptr, None,
+                                               int(stream.cuda_stream)), "rt_render_strips_dev")
 
-            events = []
-            for s in range(args.warmup + args.steps):
-                flush.fill_(s & 0xFF)
-                if world > 1:
-                    dist.barrier()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record(stream)
-                launch()
-                e1.record(stream)
-                if s >= args.warmup:
-                    events.append((e0, e1))
-            frame = peer.complete()
-            ms = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in events]))], dtype=torch.float64, device=dev)
-            per_rank = [ms.clone() for _ in range(world)]
+        events = []
+        for s in range(args.warmup + args.steps):
+            flush.fill_(s & 0xFF)
             if world > 1:
-                dist.all_gather(per_rank, ms)
-                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-            if rank == 0:
-                rgb = frame[:, :, :3].cpu().numpy()
-                if reference is None:
-                    reference = rgb
-                same = bool(np.array_equal(rgb, reference))
-                gbs = (world - 1) / cut * h * w * channels / (ms.item() * 1e-3) / 1e9
-                print(f"N={world} patch={'32x1' if wide else '8x4'} bytes/px={channels} order={'2 bottom : 1 top' if even else 'bottom-up'}: {ms.item():.4f} ms/frame  "
-                      f"{w * h / (ms.item() * 1e-3) / 1e6:.0f} Mrays/s  into rank 0: {gbs:.0f} GB/s  same_frame={same}  "
-                      f"per rank: {' '.join(f'{t.item():.3f}' for t in per_rank)}" + (f"  (frame cut for {cut} ranks)" if cut != world else ""),
-                      flush=True)
-            peer.close()
+                dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            launch()
+            e1.record(stream)
+            if s >= args.warmup:
+                events.append((e0, e1))
+        frame = peer.complete()
+        ms = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in events]))], dtype=torch.float64, device=dev)
+        per_rank = [ms.clone() for _ in range(world)]
+        if world > 1:
+            dist.all_gather(per_rank, ms)
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            rgb = frame[:, :, :3].cpu().numpy()
+            if reference is None:
+                reference = rgb
+            same = bool(np.array_equal(rgb, reference))
+            gbs = (world - 1) / cut * h * w * channels / (ms.item() * 1e-3) / 1e9
+            print(f"N={world} patch={'32x1' if wide else '8x4'} bytes/px={channels} order={'2 bottom : 1 top' if even else 'bottom-up'}: {ms.item():.4f} ms/frame  "
+                  f"{w * h / (ms.item() * 1e-3) / 1e6:.0f} Mrays/s  into rank 0: {gbs:.0f} GB/s  same_frame={same}  "
+                  f"per rank: {' '.join(f'{t.item():.3f}' for t in per_rank)}" + (f"  (frame cut for {cut} ranks)" if cut != world else ""),
+                  flush=True)
+        peer.close()
     if world > 1:
         dist.destroy_process_group()
 
