@@ -258,7 +258,8 @@ def run_b200_arm(args) -> None:
     tables = []
     for _, flat, _, _, _ in frames:
         env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, max_depth=max_depth,
-                           mode=mode, cutoff=args.cutoff if mode == abi.RT_MODE_FAST else 0.0)
+                           mode=mode, cutoff=args.cutoff if mode == abi.RT_MODE_FAST else 0.0,
+                           spheres_host=flat.spheres, point_lights_host=flat.point_lights)
         tables.append((torch.from_numpy(flat.spheres).to(dev), torch.from_numpy(flat.point_lights).to(dev), env, flat))
     # sphere tree (rt_accel_build_host) for scenes past the measured break-even; built and
     # uploaded before the timed region for the device path (scene-resident data), rebuilt

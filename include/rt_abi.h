@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 2
+#define RT_ABI_VERSION 3
 
 /* The reference's miss sentinel (base.py:12, shader.py:10). */
 #define RT_FARAWAY 1.0e39
@@ -97,7 +97,18 @@ typedef struct rt_env {
                                     NULL = test every sphere, like base.py:97 /
                                     shader.py:126.  Results are identical either way.     */
     int64_t accel_bytes;         /* size of that blob                                     */
+    const double* spheres_host;  /* optional: the caller's HOST copy of the sphere table the
+                                    call's spheres_dev holds (same layout, same values).  The
+                                    device entry points never read device memory on the host, so
+                                    without it every block derives the per-scene constants itself;
+                                    with it they are formed once, here, and scenes of at most
+                                    RT_SMALL_SCENE_SPHERES shapes travel as a kernel parameter
+                                    (no staging, sphere constants as instruction operands).
+                                    Same results either way.  NULL = not available.          */
+    const double* point_lights_host; /* optional: host copy of the point-light table, likewise */
 } rt_env;
+
+#define RT_SMALL_SCENE_SPHERES 4
 
 typedef enum rt_mode {
     RT_MODE_EXACT = 0, /* all-FP64, reference operation order, no FMA contraction        */
@@ -133,6 +144,9 @@ typedef enum rt_flags {
                                     and cam->width and the pointer multiples of 4 the warp
                                     packs a patch row into 32-bit words; byte stores
                                     otherwise.                                              */
+    RT_FLAG_GENERIC_KERNEL = 128, /* never use the kernel-parameter path of small scenes (see
+                                    rt_env.spheres_host): for tests and measurements that compare
+                                    the two paths                                             */
     RT_FLAG_IMAGE_ORDER = 2       /* rt_render_rows_dev / rt_render_strips_dev: rgb_dev and
                                     rgba8_dev are WHOLE frames (height x width) and every
                                     pixel is stored at row*width + col, whatever rows the

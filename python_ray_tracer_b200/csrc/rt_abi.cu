@@ -107,7 +107,49 @@ rt::SceneParams scene_params(const double* spheres_dev, int32_t n_spheres, const
     sp.dome_sum = sum;
     for (int i = 0; i < 3; ++i) sp.dome_color[i] = env->dome_color[i];
     sp.cutoff = env->mode == RT_MODE_FAST ? env->cutoff : 0.0;
+    // fast policy: per-launch constants formed here instead of per block or per hit
+    for (int i = 0; i < 3; ++i) sp.dome_rgb[i] = (float)(env->dome_color[i] * sum);
+    sp.cutoff_f = (float)sp.cutoff;
+    sp.chain_bound = -1.0f;
+    sp.host_bound = 0;
+    if (env->spheres_host != nullptr) {
+        const double* f = env->spheres_host;
+        const size_t n = (size_t)n_spheres;
+        double lmax = 0.0, gmax = 0.0;
+        for (size_t s = 0; s < n; ++s) {
+            lmax = std::fmax(lmax, rt::material_bound(f[RT_F_DIFFUSE_GAIN * n + s], f[RT_F_SPECULAR_GAIN * n + s],
+                                                      f[RT_F_SPECULAR_ROUGHNESS * n + s], f[RT_F_IRIDESCENCE_GAIN * n + s],
+                                                      f[RT_F_COLOR_R * n + s], f[RT_F_COLOR_G * n + s], f[RT_F_COLOR_B * n + s],
+                                                      f[RT_F_TEXTURE * n + s] != 0.0, sum, env->dome_color));
+            gmax = std::fmax(gmax, std::fabs(f[RT_F_SPECULAR_GAIN * n + s]));
+        }
+        sp.chain_bound = rt::chain_bound_of(sp.cutoff, lmax, gmax);
+        sp.host_bound = 1;
+    }
+    if (env->point_lights_host != nullptr)
+        for (int i = 0; i < 3; ++i) sp.light0[i] = env->point_lights_host[i];
     return sp;
+}
+
+// Scenes of at most kSmallMax spheres whose table the caller holds on the host too (rt_env.spheres_host,
+// point_lights_host): everything the fast policy's kernel reads of the scene, as one kernel parameter.
+bool small_table(const rt_env* env, int32_t n_spheres, const double* origin0, rt::SmallTable* table) {
+    if (env->mode != RT_MODE_FAST || env->spheres_host == nullptr || env->point_lights_host == nullptr) return false;
+    if (n_spheres > rt::kSmallMax || env->accel_dev != nullptr || (env->flags & RT_FLAG_GENERIC_KERNEL)) return false;
+    if ((env->flags & RT_FLAG_ALL_POINT_LIGHTS) && env->n_point_lights > 1) return false;
+    memset(table, 0, sizeof(*table));
+    const double* f = env->spheres_host;
+    const size_t n = (size_t)n_spheres;
+    for (size_t s = 0; s < n; ++s) {
+        const double cx = f[RT_F_CX * n + s], cy = f[RT_F_CY * n + s], cz = f[RT_F_CZ * n + s], r = f[RT_F_RADIUS * n + s];
+        table->geom[s] = {cx, cy, cz, r * r};
+        table->prim[s] = rt::make_sphere_primary(origin0, cx, cy, cz, r);
+        table->rec[s] = rt::make_shade_rec(cx, cy, cz, r, f[RT_F_DIFFUSE_GAIN * n + s], f[RT_F_SPECULAR_GAIN * n + s],
+                                           f[RT_F_SPECULAR_ROUGHNESS * n + s], f[RT_F_IRIDESCENCE_GAIN * n + s],
+                                           f[RT_F_COLOR_R * n + s], f[RT_F_COLOR_G * n + s], f[RT_F_COLOR_B * n + s],
+                                           f[RT_F_TEXTURE * n + s] != 0.0);
+    }
+    return true;
 }
 
 // The screen rectangle and linspace steps of base.py:130-139, evaluated in the same
@@ -135,6 +177,7 @@ rt::CameraParams camera_params(const rt_camera* cam, int32_t row0, int32_t row1)
 // is using it: the kernels put it back to zero themselves.
 constexpr int kMaxDevices = 64;
 constexpr unsigned int kRingSlots = 1024;
+constexpr unsigned int kRingStride = 8;  // a slot is two counters (rt_kernels.cuh: Tickets) in a 32-byte sector of its own
 struct CounterRing {
     unsigned int* base = nullptr;
     std::atomic<unsigned int> next{0};
@@ -155,15 +198,15 @@ cudaError_t ticket_counter(unsigned int** counter_out) {
         std::lock_guard<std::mutex> lock(g_ring_mutex);
         if (ring.base == nullptr) {
             unsigned int* p = nullptr;
-            if ((err = cudaMalloc(&p, sizeof(unsigned int) * kRingSlots)) != cudaSuccess) return err;
-            if ((err = cudaMemset(p, 0, sizeof(unsigned int) * kRingSlots)) != cudaSuccess) {
+            if ((err = cudaMalloc(&p, sizeof(unsigned int) * kRingSlots * kRingStride)) != cudaSuccess) return err;
+            if ((err = cudaMemset(p, 0, sizeof(unsigned int) * kRingSlots * kRingStride)) != cudaSuccess) {
                 cudaFree(p);
                 return err;
             }
             ring.base = p;
         }
     }
-    *counter_out = ring.base + (ring.next.fetch_add(1u) % kRingSlots);
+    *counter_out = ring.base + (size_t)(ring.next.fetch_add(1u) % kRingSlots) * kRingStride;
     return cudaSuccess;
 }
 
@@ -238,6 +281,11 @@ int render_camera(int device, const double* spheres_dev, int32_t n_spheres, cons
     const bool image_order = (env->flags & RT_FLAG_IMAGE_ORDER) != 0;
     const int64_t n = image_order ? (int64_t)cp.height * cp.width : (int64_t)cp.n_rows * cp.width;
     if (rgb_dev != nullptr && plane_stride < n) return fail(RT_ERR_BAD_ARG, "plane_stride %lld < %lld pixels", (long long)plane_stride, (long long)n);
+    // camera rays leave the eye: the kernels take "towards the camera" (shader.py:76) from the ray itself
+    for (int i = 0; i < 3; ++i)
+        if (env->eye[i] != cp.cam[i])
+            return fail(RT_ERR_BAD_ARG, "camera rays must start at env->eye (scene.camera.position, shader.py:76); "
+                        "for rays from elsewhere use rt_trace_rays_dev");
     DeviceScope scope(device);
     if (scope.status != RT_OK) return scope.status;
     // 3-byte pixels go out as packed words from the wide-store kernels when every patch row starts on a word boundary
@@ -248,8 +296,10 @@ int render_camera(int device, const double* spheres_dev, int32_t n_spheres, cons
     rt::OutputParams out = {rgb_dev, rgba8_dev, reinterpret_cast<unsigned long long*>(stats_dev), plane_stride,
                             rgb_dtype == RT_DTYPE_F64, image_order ? 1 : 0, bytes8,
                             (env->flags & RT_FLAG_WIDE_STORES) ? 1 : 0, (env->flags & RT_FLAG_EVEN_STORES) ? 1 : 0};
+    rt::SmallTable table;
+    const bool small = small_table(env, n_spheres, cp.cam, &table);
     cudaError_t err = launchers(env->mode).render_rows(stats_dev != nullptr, scene_params(spheres_dev, n_spheres, point_lights_dev, env),
-                                                      cp, out, static_cast<cudaStream_t>(stream));
+                                                      cp, out, small ? &table : nullptr, static_cast<cudaStream_t>(stream));
     if (err != cudaSuccess) return cuda_fail(err, "render_rows launch");
     return RT_OK;
 }

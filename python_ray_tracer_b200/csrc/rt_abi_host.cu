@@ -177,6 +177,9 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
     rt_env with_tree;
     if ((rc = attach_accel(*c, spheres_host, n_spheres, env, &with_tree)) != RT_OK) return rc;
     env = &with_tree;
+    // the tables are host memory here by definition: per-scene constants are formed on the host
+    with_tree.spheres_host = spheres_host;
+    with_tree.point_lights_host = point_lights_host;
     // the scratch buffers hold the band, chunk by chunk: a caller's whole-frame addressing flag
     // (meant for rt_render_rows_dev with its own frame buffer) must not reach the kernel
     with_tree.flags &= ~RT_FLAG_IMAGE_ORDER;
@@ -267,6 +270,9 @@ int rt_trace_rays_host(int device, const double* spheres_host, int32_t n_spheres
     rt_env with_tree;
     if ((rc = attach_accel(*c, spheres_host, n_spheres, env, &with_tree)) != RT_OK) return rc;
     env = &with_tree;
+    // the tables are host memory here by definition: per-scene constants are formed on the host
+    with_tree.spheres_host = spheres_host;
+    with_tree.point_lights_host = point_lights_host;
     const size_t plane = sizeof(double) * 3 * (size_t)n_rays;
     HOST_CUDA(reserve(c->rays, 2 * plane + 16));
     double* dirs_dev = static_cast<double*>(c->rays.ptr);

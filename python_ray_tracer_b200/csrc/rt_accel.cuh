@@ -18,6 +18,7 @@ struct AccelView {
     const SphereGeom* leaf_geom;
     const SphereGeom* geom;
     const SphereAux* aux;
+    const ShadeRec* rec;
     const int* large;
     int n_nodes, n_large;
     double local_bound, gain_bound;
@@ -32,6 +33,7 @@ __device__ __forceinline__ AccelView accel_view(const unsigned char* blob) {
     v.leaf_geom = reinterpret_cast<const SphereGeom*>(blob + h->off_leaf_geom);
     v.geom = reinterpret_cast<const SphereGeom*>(blob + h->off_geom);
     v.aux = reinterpret_cast<const SphereAux*>(blob + h->off_aux);
+    v.rec = reinterpret_cast<const ShadeRec*>(blob + h->off_rec);
     v.large = reinterpret_cast<const int*>(blob + h->off_large);
     v.n_nodes = h->n_nodes;
     v.n_large = h->n_large;
@@ -45,14 +47,6 @@ __device__ __forceinline__ SphereGeom ldg_geom(const SphereGeom* p) {
     const double2 a = __ldg(reinterpret_cast<const double2*>(p));
     const double2 b = __ldg(reinterpret_cast<const double2*>(p) + 1);
     return {a.x, a.y, b.x, b.y};
-}
-
-// distance along the ray to one sphere, kMiss on a miss: the policy's own sphere test
-template <int MODE>
-__device__ __forceinline__ double accel_sphere_t(Vec3 o, Vec3 d, const SphereGeom& g, double cc) {
-    if (MODE == kModeExact) return sphere_distance_exact(o, d, g, cc);
-    HalfB q = half_b(o, d, g);
-    return can_hit(q) ? near_root(q) : kMiss;
 }
 
 // ---- the slab test: FP32, conservative ------------------------------------------------------
@@ -133,9 +127,13 @@ __device__ __forceinline__ float slab_enter(const RaySlabs& r, const NodeView& n
 // the four loads are in flight at once); the one entered first is visited next, the other is
 // pushed with its entry distance only if the ray meets it, and dropped on the way back up if a
 // closer hit has been found meanwhile.
-template <int MODE>
-__device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 d, double& tmin, int& sid,
-                                              unsigned long long& evaluated) {
+// `sphere_t(geom, shape)`: the policy's own sphere test, kMiss on a miss.  Its distances may be a
+// multiple of the ray parameter the slabs measure (an unnormalised direction): limit_scale converts,
+// rounded up.
+template <class SphereT>
+__device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 d, float limit_scale, double& tmin, int& sid,
+                                              unsigned long long& evaluated, SphereT&& sphere_t) {
+    auto slab_limit = [&](double t) { return t < kMiss ? __fmul_ru(__double2float_ru(t), limit_scale) : INFINITY; };
     auto consider = [&](int s, double t) {
         if (t < tmin || (t == tmin && t != kMiss && s < sid)) {
             tmin = t;
@@ -144,7 +142,7 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
     };
     for (int i = 0; i < av.n_large; ++i) {
         const int s = __ldg(av.large + i);
-        consider(s, accel_sphere_t<MODE>(o, d, ldg_geom(av.geom + s), MODE == kModeExact ? __ldg(&av.aux[s].cc) : 0.0));
+        consider(s, sphere_t(ldg_geom(av.geom + s), s));
     }
     evaluated += (unsigned long long)av.n_large;
     if (av.n_nodes == 0) return;
@@ -152,7 +150,7 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
     float stack_t[kAccelStack];  // entry distance of a pushed box
     unsigned int stack_ref[kAccelStack];
     int top = 0;
-    float limit = __double2float_ru(tmin);
+    float limit = slab_limit(tmin);
     bool hit;
     const NodeView root = ldg_node(av.nodes);
     slab_enter(ray, root, limit, hit);
@@ -165,11 +163,10 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
             for (int k = 0; k < count; ++k) {
                 const int slot = first + k;
                 const int s = __ldg(av.order + slot);
-                consider(s, accel_sphere_t<MODE>(o, d, ldg_geom(av.leaf_geom + slot),
-                                                 MODE == kModeExact ? __ldg(&av.aux[s].cc) : 0.0));
+                consider(s, sphere_t(ldg_geom(av.leaf_geom + slot), s));
             }
             evaluated += (unsigned long long)count;
-            limit = __double2float_ru(tmin);
+            limit = slab_limit(tmin);
         } else {
             const NodeView a = ldg_node(av.nodes + first), b = ldg_node(av.nodes + first + 1);
             bool hit_a, hit_b;
@@ -204,19 +201,19 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
 
 // NumpyShader._calculate_shadow (shader.py:114-128): is any OTHER sphere hit closer than
 // `own` (the distance to the point's own sphere, kMiss if the shadow ray leaves it)?
-template <int MODE>
-__device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, Vec3 p, Vec3 l, double own,
-                                               unsigned long long& evaluated) {
+template <class SphereT>
+__device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, Vec3 p, Vec3 l, double own, float limit_scale,
+                                               unsigned long long& evaluated, SphereT&& sphere_t) {
     for (int i = 0; i < av.n_large; ++i) {
         const int s = __ldg(av.large + i);
         if (s == s_own) continue;
-        const double t = accel_sphere_t<MODE>(p, l, ldg_geom(av.geom + s), MODE == kModeExact ? __ldg(&av.aux[s].cc) : 0.0);
+        const double t = sphere_t(ldg_geom(av.geom + s), s);
         if (t < own) return true;
     }
     evaluated += (unsigned long long)av.n_large;
     if (av.n_nodes == 0) return false;
     const RaySlabs ray = ray_slabs(p, l, av.extent);
-    const float limit = __double2float_ru(own);
+    const float limit = own < kMiss ? __fmul_ru(__double2float_ru(own), limit_scale) : INFINITY;
     unsigned int stack[kAccelStack];
     int top = 0;
     bool hit;
@@ -232,8 +229,7 @@ __device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, V
                 const int slot = first + k;
                 const int s = __ldg(av.order + slot);
                 if (s == s_own) continue;
-                const double t = accel_sphere_t<MODE>(p, l, ldg_geom(av.leaf_geom + slot),
-                                                      MODE == kModeExact ? __ldg(&av.aux[s].cc) : 0.0);
+                const double t = sphere_t(ldg_geom(av.leaf_geom + slot), s);
                 if (t < own) return true;
             }
             evaluated += (unsigned long long)count;

@@ -13,6 +13,7 @@
 //   SphereGeom leaf_geom[n_in_tree]  {cx,cy,cz,r*r} in leaf-slot order (what traversal reads)
 //   SphereGeom geom[n_spheres]       the same records by shape index (what shading reads)
 //   SphereAux  aux[n_spheres]        {1/r, |C|^2} by shape index
+//   ShadeRec   rec[n_spheres]        what the fast policy's shading reads (rt_device.cuh), by shape index
 //   int32      large[n_large]        shapes kept out of the tree and tested for every ray
 //                                    (a ground sphere of radius 1e5 would swallow every box)
 #pragma once
@@ -21,7 +22,7 @@
 
 namespace rt {
 
-constexpr uint32_t kAccelMagic = 0x52544256u;  // "RTBV"
+constexpr uint32_t kAccelMagic = 0x32425452u;  // "RTB2" (second layout: + the fast policy's shading records)
 #ifndef RT_ACCEL_LEAF
 #define RT_ACCEL_LEAF 2  // measured: 2 beats 4 by 6 % at 1 025 shapes (fewer FP64 sphere tests per leaf visited)
 #endif
@@ -38,7 +39,7 @@ struct AccelHeader {
     int32_t n_in_tree;
     int32_t n_large;
     int32_t reserved;
-    int64_t off_nodes, off_order, off_leaf_geom, off_geom, off_aux, off_large;
+    int64_t off_nodes, off_order, off_leaf_geom, off_geom, off_aux, off_large, off_rec;
     int64_t bytes;
     double local_bound;  // sup over materials of |local colour| (material_bound(), rt_chain.cuh)
     double gain_bound;   // sup over materials of |specular_gain|

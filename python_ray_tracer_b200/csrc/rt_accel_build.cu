@@ -275,7 +275,8 @@ int64_t rt_accel_bytes(int32_t n_spheres) {
     if (n_spheres <= 0) return -1;
     const size_t n = (size_t)n_spheres;
     return (int64_t)(align16(sizeof(AccelHeader)) + align16(sizeof(AccelNode) * (2 * n + 1)) + align16(4 * n) +
-                     align16(32 * n) + align16(32 * n) + align16(16 * n) + align16(4 * rt::kAccelMaxLarge) + 64);
+                     align16(32 * n) + align16(32 * n) + align16(16 * n) + align16(sizeof(rt::ShadeRec) * n) +
+                     align16(4 * rt::kAccelMaxLarge) + 64);
 }
 
 int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_env* env, void* blob_out,
@@ -331,6 +332,8 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
     off += align16(32 * (size_t)n);
     h.off_aux = (int64_t)off;
     off += align16(16 * (size_t)n);
+    h.off_rec = (int64_t)off;
+    off += align16(sizeof(rt::ShadeRec) * (size_t)n);
     h.off_large = (int64_t)off;
     off += align16(4 * large.size());
     h.bytes = (int64_t)off;
@@ -370,6 +373,13 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
         aux[2 * (size_t)s] = 1.0 / r;                                 // shader.py:74
         aux[2 * (size_t)s + 1] = (cx * cx) + (cy * cy) + (cz * cz);  // shape.py:35
     }
+    rt::ShadeRec* rec = reinterpret_cast<rt::ShadeRec*>(base + h.off_rec);
+    auto field = [&](int f, int s) { return spheres_host[(size_t)f * n + s]; };
+    for (int s = 0; s < n; ++s)
+        rec[s] = rt::make_shade_rec(field(RT_F_CX, s), field(RT_F_CY, s), field(RT_F_CZ, s), field(RT_F_RADIUS, s),
+                                    field(RT_F_DIFFUSE_GAIN, s), field(RT_F_SPECULAR_GAIN, s), field(RT_F_SPECULAR_ROUGHNESS, s),
+                                    field(RT_F_IRIDESCENCE_GAIN, s), field(RT_F_COLOR_R, s), field(RT_F_COLOR_G, s),
+                                    field(RT_F_COLOR_B, s), field(RT_F_TEXTURE, s) != 0.0);
     if (!large.empty()) memcpy(base + h.off_large, large.data(), 4 * large.size());
     *bytes_out = h.bytes;
     return RT_OK;

@@ -55,6 +55,13 @@ struct SceneParams {
     double dome_sum;        // sum of dome_intensity (Fast)
     double dome_color[3];
     double cutoff;          // Fast: chain cutoff in linear units, 0 = off
+    // Fast policy, formed on the host (rt_abi.cu: scene_params):
+    float dome_rgb[3];      // dome_color * dome_sum
+    float cutoff_f;         // (float)cutoff
+    float chain_bound;      // sup |local colour| / (1 - sup w) over the materials when the caller gave the host
+                            // copy of the table (rt_env.spheres_host); < 0: no cut-off possible; see host_bound
+    int host_bound;         // 1: chain_bound is valid; 0: the staging loop computes it (no host copy of the table)
+    double light0[3];       // lights[0] when the host copy of the light table was given (small-scene kernels)
 };
 
 // Camera rows -> rays (base.py:123-141).  The linspace steps are divided on the host
@@ -112,6 +119,89 @@ struct __align__(16) SphereGeom {
 struct __align__(16) SphereAux {
     double inv_r;  // 1.0 / radius (shader.py:74)
     double cc;     // |C|^2 summed left to right (shape.py:35 abs(self.position))
+};
+
+// Fast policy: what shading one hit needs of its sphere (64 bytes, read as four 16-byte loads).
+// Formed once per scene -- on the host for the constant-bank kernels, by the staging loop otherwise --
+// so that nothing per-material is computed per hit: the texture colour arrives multiplied by
+// diffuse_gain, roughness as alpha^2 = roughness^4, the film weight as 0.1 * iridescence_gain
+// (shader.py:52), the bounce weight as 0.5 * specular_gain (shader.py:106).  Single precision
+// where the value only enters the FP32 shading tail.
+struct __align__(16) ShadeRec {
+    double cx, cy, cz, inv_r;
+    float kd_r, kd_g, kd_b, spec_gain;
+    float a2, film, half_gain;
+    unsigned int flags;
+};
+constexpr unsigned int kRecChecker = 1u;  // TextureChecker (shader.py:22-32)
+constexpr unsigned int kRecInward = 2u;   // negative radius: the normal points into the sphere
+
+// rays that start at the camera: O - C and |O - C|^2 - r^2 are per-sphere constants of the launch
+struct __align__(16) SpherePrimary {
+    double lx, ly, lz;  // origin0 - centre
+    double c;           // |origin0 - centre|^2 - r^2
+};
+
+__host__ __device__ inline ShadeRec make_shade_rec(double cx, double cy, double cz, double r, double diffuse_gain,
+                                                   double specular_gain, double roughness, double irid_gain, double cr,
+                                                   double cg, double cb, bool checker) {
+    ShadeRec m;
+    m.cx = cx, m.cy = cy, m.cz = cz;
+    m.inv_r = 1.0 / r;
+    m.kd_r = (float)(checker ? diffuse_gain : diffuse_gain * cr);
+    m.kd_g = (float)(checker ? diffuse_gain : diffuse_gain * cg);
+    m.kd_b = (float)(checker ? diffuse_gain : diffuse_gain * cb);
+    m.spec_gain = (float)specular_gain;
+    const double alpha = roughness * roughness;
+    m.a2 = (float)(alpha * alpha);
+    m.film = (float)(kFilmWeight * irid_gain);
+    m.half_gain = (float)(0.5 * specular_gain);
+    m.flags = (checker ? kRecChecker : 0u) | (r < 0.0 ? kRecInward : 0u);
+    return m;
+}
+__host__ __device__ inline SpherePrimary make_sphere_primary(const double* origin0, double cx, double cy, double cz, double r) {
+    const double lx = origin0[0] - cx, ly = origin0[1] - cy, lz = origin0[2] - cz;
+    return {lx, ly, lz, fma(lz, lz, fma(ly, ly, fma(lx, lx, -(r * r))))};
+}
+
+// Upper bound of |local colour| of one material (fast policy's chain cut-off).  local = ambient +
+// diffuse + dome + gain*(spec_base + gain*glint) + film, with F <= 1, G1(L) <= 1,
+// D <= a2/(pi*(min(1,a2^2)+eps)) and G1(V)/(4 NdotV + eps) <= 1/(2*(sqrt(min(a2,1))+eps)).
+__host__ __device__ inline double material_bound(double diffuse_gain, double specular_gain, double roughness, double irid_gain,
+                                                 double cr, double cg, double cb, bool checker, double dome_sum,
+                                                 const double* dome_color) {
+    double tex = checker ? 1.0 : fmax(fabs(cr), fmax(fabs(cg), fabs(cb)));
+    double dome = fabs(dome_sum) * fmax(fabs(dome_color[0]), fmax(fabs(dome_color[1]), fabs(dome_color[2])));
+    double alpha = roughness * roughness;
+    double a2 = alpha * alpha;
+    double dmax = a2 / (kPi * (fmin(1.0, a2 * a2) + kEps));
+    double gv = 1.0 / (2.0 * (sqrt(fmin(a2, 1.0)) + kEps));
+    double g = fabs(specular_gain);
+    double spec = g * (dmax * gv + g);
+    double film = 1.4 * kFilmWeight * fabs(irid_gain);
+    return kAmbient + fabs(diffuse_gain) * tex + dome + spec + film;
+}
+
+// sup |local| / (1 - sup w) of the chain cut-off (rt_fast.cuh), or -1 when it cannot be used
+__host__ __device__ inline float chain_bound_of(double cutoff, double local_max, double gain_max) {
+    if (!(cutoff > 0.0)) return -1.0f;
+    const double wmax = 0.5 * gain_max;
+    // remaining <= W * lmax * sum_j wmax^j ; only usable when the series converges
+    if (wmax < 1.0 && local_max < 1e300) return (float)(local_max / (1.0 - wmax)) * 1.000001f;
+    return -1.0f;
+}
+
+#ifndef RT_SMALL_MAX
+#define RT_SMALL_MAX 4
+#endif
+// Scenes of at most kSmallMax spheres whose table the caller also holds on the host: the whole table
+// travels as a kernel parameter (constant bank), the loops over it are unrolled at compile time and
+// the sphere constants are instruction operands -- no staging loop, no shared-memory sphere loads.
+constexpr int kSmallMax = RT_SMALL_MAX;
+struct SmallTable {
+    SphereGeom geom[kSmallMax];
+    SpherePrimary prim[kSmallMax];
+    ShadeRec rec[kSmallMax];
 };
 
 struct Vec3 {

@@ -13,6 +13,9 @@ namespace rt {
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 5  // resident 128-thread blocks per SM the register allocator must allow
 #endif
+#ifndef RT_SMALL_MIN_BLOCKS
+#define RT_SMALL_MIN_BLOCKS 5  // the same for the constant-bank kernels of small scenes
+#endif
 #ifndef RT_DYNAMIC_PCT
 #define RT_DYNAMIC_PCT 30     // long launches of cheap items: share of the items left to the ticket counter
 #endif
@@ -21,6 +24,12 @@ namespace rt {
 #endif
 #ifndef RT_COSTLY_ITEM_SPHERES
 #define RT_COSTLY_ITEM_SPHERES 8   // scenes with at least this many spheres are ticketed entirely
+#endif
+#ifndef RT_CHUNK4_ROUNDS
+#define RT_CHUNK4_ROUNDS 4   // a draw takes 4 tickets while more than this many per warp are left ...
+#endif
+#ifndef RT_CHUNK2_ROUNDS
+#define RT_CHUNK2_ROUNDS 2   // ... 2 while more than this many are left, then 1 (0 0: always single tickets)
 #endif
 
 #ifndef RT_PATCH_W
@@ -40,74 +49,82 @@ constexpr int kBlockThreads = 128;
 constexpr int kBigBlockThreads = 640;
 constexpr size_t kSmemPerSm = 227 * 1024;
 
-__host__ __device__ inline size_t staged_bytes(int n_spheres, int n_lights = 1) {
-    return (sizeof(SphereGeom) + sizeof(SpherePrimary) + sizeof(SphereAux) + sizeof(SphereMaterial)) * (size_t)n_spheres +
-           sizeof(double) * 3 * (size_t)n_lights;
-}
-
 // Work distribution of the persistent kernels.  A work item is one 8x4 patch (or 32 rays).
 // The first static_rounds * n_warps items are dealt round-robin (warp w takes items w,
-// w + n_warps, ...: no atomics); the rest are drawn one at a time from a device counter
-// (lane 0, one atomicAdd per ticket), so the launch ends balanced at the granularity of a
-// single patch.  Every warp keeps its next ticket in flight while it works and draws
-// exactly one ticket >= n_tickets before it leaves, so the draw that returns
-// n_tickets + n_warps - 1 is the last of the launch and puts the counter back to zero for
-// the next launch that uses it.
+// w + n_warps, ...: no atomics); the rest are tickets drawn from a device counter by lane 0, so the
+// launch ends balanced at the granularity of a single patch.  Every warp keeps its next draw in
+// flight while it works.
 //
 // How much is ticketed, and in which order, is chosen per launch from measurements on B200
 // (profiles/r01/schedule_sweep.txt).  Patch times of the README frame run from 1 us (sky)
 // to 28 us (15-bounce chains where the spheres meet the ground): a static deal of
-// everything leaves a 15 % tail at 1080p, while ticketing everything costs ~1 G
-// same-address atomics/s on an 8K frame (+9 %).  So: short launches and launches of costly
+// everything leaves a 15 % tail at 1080p.  So: short launches and launches of costly
 // items (many spheres) are ticketed entirely, after one static round that hides the burst
 // of first draws, and taken from the bottom of the frame upwards -- the long chains sit low
 // in the frame and the rows that come last are its top, where the reference's fixed camera
 // (image plane z = 0, +y up, base.py:130-141) sees the least, so the tail is made of short
 // patches; long launches of cheap items deal the first 70 % statically, top-down.  These
 // are heuristics about time only, never about results.
+//
+// Draws on ONE address are served at about one per nanosecond by the L2 slice that owns it: a
+// 1080p frame of trivial patches took 68 us in round 1 (64 800 single-ticket draws), which is the
+// whole budget of a frame now.  So a draw takes 4 consecutive tickets while the launch is young, 2
+// later and 1 at the end (chunk_hi / chunk_mid: tickets left at which the size drops); with the
+// bottom-up order the single tickets are the cheap sky patches, so the launch still ends level.
 struct Tickets {
-    unsigned int* counter;
+    unsigned int* counter;       // [0] tickets drawn so far, [1] warps that have left (both zero between launches)
     unsigned int n_tickets;      // items handed out dynamically
     unsigned int n_warps;        // gridDim.x * (block threads / 32)
     unsigned int static_rounds;  // items [0, static_rounds * n_warps) are dealt statically
     unsigned int n_items;
     unsigned int reversed;       // 1: take items from the last one backwards; 2: alternately from both ends (wide-store kernels)
+    unsigned int chunk_hi, chunk_mid;
 };
-// A draw is split in two: issue_ticket() starts the atomic, take_ticket() broadcasts its result
-// after the item.  The atomic is atom.inc with the launch's last draw as its bound (every warp
-// ends on one draw past the tickets, n_tickets + n_warps draws in all): the counter re-arms
-// itself for the next launch, and -- unlike atom.add under a lane == 0 predicate -- ptxas does
-// not wrap it in its warp-aggregation sequence (vote, popc, shuffle of the result).
-// What this does NOT achieve is hiding the round trip (~0.8 us): at 96 registers the result is
-// spilled on the next instruction, and the spill store waits for it.  Measured consequences
-// (profiles/r01/schedule_sweep.txt): a 1080p frame of trivial items takes 68 us (22 draws per
-// warp), handing out 8/4/2/1 items per draw lowers that floor to 51 us but costs the README
-// frame 6 us in balance (its costly patches cluster), so single tickets stay.
-__device__ __forceinline__ unsigned int issue_ticket(const Tickets& tk, int lane) {
+__device__ __forceinline__ unsigned int chunk_size(const Tickets& tk, unsigned int drawn_so_far) {
+    const unsigned int left = tk.n_tickets > drawn_so_far ? tk.n_tickets - drawn_so_far : 0u;
+    return left > tk.chunk_hi ? 4u : (left > tk.chunk_mid ? 2u : 1u);
+}
+// A draw is split in two: issue_draw() starts the atomic, take_draw() broadcasts its result when
+// the warp has run out of items.
+__device__ __forceinline__ unsigned int issue_draw(const Tickets& tk, int lane, unsigned int count) {
     unsigned int t = 0;
-    if (lane == 0)
-        asm volatile("atom.global.inc.u32 %0, [%1], %2;" : "=r"(t) : "l"(tk.counter), "r"(tk.n_tickets + tk.n_warps - 1u));
+    if (lane == 0) asm volatile("atom.global.add.u32 %0, [%1], %2;" : "=r"(t) : "l"(tk.counter), "r"(count));
     return t;
 }
-__device__ __forceinline__ unsigned int take_ticket(const Tickets& tk, unsigned int t, int lane) {
-    return __shfl_sync(0xffffffffu, t, 0);
-}
+__device__ __forceinline__ unsigned int take_draw(unsigned int t) { return __shfl_sync(0xffffffffu, t, 0); }
 
-// The item loop of a warp: the static rounds, then tickets, the next one kept in flight under
-// the item.  (Drawing only when the ticket is needed -- no draw live across the item body -- was
-// measured for the big blocks, whose items take >= 100 us: 17.99 against 18.07 ms on c3, not kept.)
+// The item loop of a warp: the static rounds, then chunks of tickets, the next draw kept in flight
+// under the items of the current one.  One copy of the item body (it is most of the kernel's code,
+// and the instruction cache is cold at every launch of the bench: L2 is flushed between frames).
+// The last warp to leave puts the counters back to zero for the next launch that uses them.
 template <typename Item>
 __device__ __forceinline__ void run_items(const Tickets& tk, const int lane, const unsigned int warp_id, Item&& item) {
-    unsigned int drawn = issue_ticket(tk, lane);  // in flight during the static rounds
-#pragma unroll 1
-    for (unsigned int r = 0; r < tk.static_rounds; ++r) item(r * tk.n_warps + warp_id);
+    unsigned int size = chunk_size(tk, 0u);
+    unsigned int drawn = issue_draw(tk, lane, size);  // in flight during the static rounds
     const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
-    unsigned int next = take_ticket(tk, drawn, lane);
+    unsigned int round = 0, pos = 0, end = 0;
 #pragma unroll 1
-    while (next < tk.n_tickets) {
-        drawn = issue_ticket(tk, lane);  // in flight during this item
-        item(first_dynamic + next);
-        next = take_ticket(tk, drawn, lane);
+    for (;;) {
+        unsigned int idx;
+        if (round < tk.static_rounds) {
+            idx = round * tk.n_warps + warp_id;
+            ++round;
+        } else {
+            if (pos == end) {
+                pos = take_draw(drawn);
+                if (pos >= tk.n_tickets) break;
+                end = pos + size < tk.n_tickets ? pos + size : tk.n_tickets;
+                size = chunk_size(tk, end);
+                drawn = issue_draw(tk, lane, size);
+            }
+            idx = first_dynamic + pos++;
+        }
+        item(idx);
+    }
+    if (lane == 0) {
+        unsigned int left;
+        asm volatile("atom.global.inc.u32 %0, [%1], %2;" : "=r"(left) : "l"(tk.counter + 1), "r"(tk.n_warps - 1u));
+        if (left == tk.n_warps - 1u) atomicExch(tk.counter, 0u);  // every other warp has made its last draw
     }
 }
 
@@ -155,15 +172,29 @@ __device__ __forceinline__ unsigned int quantize_channel(double v) {
     if (hi >= 0x3ff00000) return 255u;   // v >= 1
     return (unsigned int)(255.0 * v);
 }
+// The fast policy's pixels are FP32: the product rounded towards zero truncates to the same byte as
+// the exact product 255 * v (which FP64 holds exactly: 8 x 24 bits), so the fused 8-bit image equals
+// rt_quantize_dev of the stored planes, bit for bit.
+__device__ __forceinline__ unsigned int quantize_channel(float v) {
+    const int bits = __float_as_int(v);
+    if (bits < 0) return 0u;
+    if (bits >= 0x3f800000) return 255u;
+    return (unsigned int)__fmul_rz(255.0f, v);
+}
+
+template <typename T>
+struct Rgb {
+    T x, y, z;
+};
 
 // 3-byte pixels of one patch row, packed into 32-bit words by the warp (Bytes8::kRgb8Words):
 // lane px of a row segment of PW pixels stores word px of its 3*PW/4 words, taking the bytes of
 // pixels 4*px/3 and 4*px/3 + 1 from their lanes.  The segment starts at a multiple of four
 // pixels and the frame width is one too, so every word is aligned and no word straddles two
 // rows or two patches.  Called by all 32 lanes; `valid` = this lane owns a pixel of the frame.
-template <int PW>
+template <int PW, typename T>
 __device__ __forceinline__ void store_rgb8_words(const OutputParams& out, bool valid, long long p, int px, int cols_left,
-                                                 Vec3 c) {
+                                                 Rgb<T> c) {
     unsigned int q = 0u;
     if (valid) q = quantize_channel(c.x) | (quantize_channel(c.y) << 8) | (quantize_channel(c.z) << 16);
     const int lane = threadIdx.x & 31;
@@ -178,13 +209,14 @@ __device__ __forceinline__ void store_rgb8_words(const OutputParams& out, bool v
     }
 }
 
-__device__ __forceinline__ void store_pixel(const OutputParams& out, long long p, Vec3 c) {
+template <typename T>
+__device__ __forceinline__ void store_pixel(const OutputParams& out, long long p, Rgb<T> c) {
     if (out.rgb != nullptr) {
         if (out.rgb_is_f64) {
             double* f = static_cast<double*>(out.rgb);
-            f[p] = c.x;
-            f[out.plane_stride + p] = c.y;
-            f[2 * out.plane_stride + p] = c.z;
+            f[p] = (double)c.x;
+            f[out.plane_stride + p] = (double)c.y;
+            f[2 * out.plane_stride + p] = (double)c.z;
         } else {
             float* f = static_cast<float*>(out.rgb);
             f[p] = (float)c.x;
@@ -205,77 +237,33 @@ __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p
     }
 }
 
-// Camera rows of one band or interleaved shard (CameraParams): ray generation + trace + stores, one thread per pixel of a
-// patch.  Persistent: the grid is sized to the resident block slots of the GPU.
-template <int MODE, bool STATS, int BLOCK, bool ACCEL, int PW>
-__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_ACCEL_MIN_BLOCKS : RT_MIN_BLOCKS) : 1)
-    render_rows_kernel(SceneParams sp, CameraParams cp, OutputParams out, Tickets tk) {
-    constexpr int kWarpTileW = PW, kWarpTileH = 32 / PW;
-    extern __shared__ __align__(16) unsigned char smem[];
-    AccelView av = {};
-    if (ACCEL) av = accel_view(sp.accel);
-    const Staged st = ACCEL ? stage_lights_only<MODE>(sp, smem, av) : stage_scene<MODE>(sp, smem, cp.cam);
+// ---- the two tracers the kernels are written over ----------------------------------------------------
+// camera(col, row) / ray(o, d) -> colour of one pixel / ray, counters in k.
+struct ExactTracer {
+    using Pixel = Rgb<double>;
+    const SceneParams& sp;
+    Staged st;
+    AccelView av;
+    template <bool STATS, bool TREE>
+    __device__ __forceinline__ Pixel ray(Vec3 o, Vec3 d, Counters& k) const {
+        const Vec3 c = trace_chain_exact<STATS, TREE>(sp, st, av, o, d, k);
+        return {c.x, c.y, c.z};
+    }
+};
 
+// Camera rows of one band or interleaved shard (CameraParams): ray generation + trace + stores, one
+// thread per pixel of a patch.  Persistent: the grid is sized to the resident block slots of the GPU.
+// `pixel(col, row, k)` is the tracer of the instantiation.
+template <bool STATS, int BLOCK, int PW, typename PixelFn>
+__device__ __forceinline__ void render_rows_body(const CameraParams& cp, const OutputParams& out, const Tickets& tk, PixelFn&& pixel) {
+    constexpr int kTileW = PW, kTileH = 32 / PW;
     const int lane = threadIdx.x & 31;
-    const int px = lane & (kWarpTileW - 1), py = lane / kWarpTileW;
-    const unsigned int tiles_x = (unsigned int)(cp.width + kWarpTileW - 1) / kWarpTileW;
+    const int px = lane & (kTileW - 1), py = lane / kTileW;
+    const unsigned int tiles_x = (unsigned int)(cp.width + kTileW - 1) / kTileW;
     const unsigned int tiles_x_recip = tiles_x > 1u ? (unsigned int)(0x100000000ull / tiles_x) : 0xffffffffu;
     const unsigned int warp_id = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
-    const Vec3 eye = {cp.cam[0], cp.cam[1], cp.cam[2]};
     Counters k = {0, 0, 0, 0};
 
-    auto render_patch = [&](unsigned int item) {
-#ifdef RT_TIMING_DEBUG
-        unsigned long long t_item0 = 0;
-        if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_item0));
-#endif
-        // item / tiles_x by a reciprocal formed once per thread: floor(2^32 / d) underestimates
-        // the quotient of a 31-bit item by at most one
-        unsigned int ty = __umulhi(item, tiles_x_recip);
-        unsigned int tx = item - ty * tiles_x;
-        if (tx >= tiles_x) {
-            tx -= tiles_x;
-            ty += 1u;
-        }
-        const int local_row = (int)ty * kWarpTileH + py;
-        const int col = (int)tx * kWarpTileW + px;
-        const bool valid = col < cp.width && local_row < cp.n_rows;
-        if constexpr (PW == kWideTileW) {
-            // the wide-store kernels can pack 3-byte pixels across the warp: all lanes reach the store
-            long long p = 0;
-            Vec3 c = {0.0, 0.0, 0.0};
-            if (valid) {
-                const int row = image_row(cp, local_row);
-                Vec3 d = primary_direction<MODE>(cp, col, row);
-                c = trace_chain<MODE, STATS, !ACCEL, ACCEL>(sp, st, av, eye, d, k);
-                p = (long long)(out.image_order ? row : local_row) * cp.width + col;
-                store_pixel(out, p, c);
-            }
-            if (out.bytes8 == kRgb8Words && out.rgba8 != nullptr) store_rgb8_words<PW>(out, valid, p, px, cp.width - col + px, c);
-        } else if (valid) {
-            const int row = image_row(cp, local_row);
-            Vec3 d = primary_direction<MODE>(cp, col, row);
-            Vec3 c = trace_chain<MODE, STATS, !ACCEL, ACCEL>(sp, st, av, eye, d, k);
-            store_pixel(out, (long long)(out.image_order ? row : local_row) * cp.width + col, c);
-        }
-#ifdef RT_TIMING_DEBUG
-        if (STATS && out.stats != nullptr) {
-            __syncwarp();
-            unsigned long long t_item1;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_item1));
-            if (lane == 0) {
-                out.stats[8 + 2 * 148 * 32 + 2 * item] = t_item0;
-                out.stats[8 + 2 * 148 * 32 + 2 * item + 1] = t_item1;
-            }
-        }
-#endif
-    };
-
-#ifdef RT_TIMING_DEBUG
-    // experiment only (tools/warp_timeline.py): per-warp start/end stamps behind the counters
-    unsigned long long t_start = 0;
-    if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
-#endif
     auto render_item = [&](unsigned int idx) {
         unsigned int item = tk.reversed ? tk.n_items - 1u - idx : idx;
         if constexpr (PW == kWideTileW) {
@@ -289,45 +277,133 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_AC
                 else item = r == 2u ? group : tk.n_items - 1u - (2u * group + r);
             }
         }
-        render_patch(item);
+        // item / tiles_x by a reciprocal formed once per thread: floor(2^32 / d) underestimates
+        // the quotient of a 31-bit item by at most one
+        unsigned int ty = __umulhi(item, tiles_x_recip);
+        unsigned int tx = item - ty * tiles_x;
+        if (tx >= tiles_x) {
+            tx -= tiles_x;
+            ty += 1u;
+        }
+        const int local_row = (int)ty * kTileH + py;
+        const int col = (int)tx * kTileW + px;
+        const bool valid = col < cp.width && local_row < cp.n_rows;
+        if constexpr (PW == kWideTileW) {
+            // the wide-store kernels can pack 3-byte pixels across the warp: all lanes reach the store
+            long long p = 0;
+            decltype(pixel(0, 0, k)) c = {0, 0, 0};
+            if (valid) {
+                const int row = image_row(cp, local_row);
+                c = pixel(col, row, k);
+                p = (long long)(out.image_order ? row : local_row) * cp.width + col;
+                store_pixel(out, p, c);
+            }
+            if (out.bytes8 == kRgb8Words && out.rgba8 != nullptr) store_rgb8_words<PW>(out, valid, p, px, cp.width - col + px, c);
+        } else if (valid) {
+            const int row = image_row(cp, local_row);
+            const auto c = pixel(col, row, k);
+            store_pixel(out, (long long)(out.image_order ? row : local_row) * cp.width + col, c);
+        }
     };
     run_items(tk, lane, warp_id, render_item);
-#ifdef RT_TIMING_DEBUG
-    if (STATS && out.stats != nullptr && lane == 0) {
-        unsigned long long t_end;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
-        out.stats[8 + 2 * warp_id] = t_start;
-        out.stats[8 + 2 * warp_id + 1] = t_end;
-    }
-#endif
     flush_counters<STATS>(k, out.stats);
 }
 
-// Explicit ray batch, one thread per ray, same work distribution (an item = 32 rays).
-template <int MODE, bool STATS, int BLOCK, bool ACCEL>
-__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (ACCEL ? RT_ACCEL_MIN_BLOCKS : RT_MIN_BLOCKS) : 1)
-    trace_rays_kernel(SceneParams sp, RayBatch rb, OutputParams out, Tickets tk) {
+// camera point of a pixel on the plane z = 0 minus the eye: the UNNORMALISED primary direction
+__device__ __forceinline__ Vec3 primary_offset(const CameraParams& cp, int col, int row) {
+    const double x = linspace_at(cp.x_start, cp.x_stop, cp.x_step, cp.width, col);
+    const double y = linspace_at(cp.y_start, cp.y_stop, cp.y_step, cp.height, row);
+    return {x - cp.cam[0], y - cp.cam[1], 0.0 - cp.cam[2]};
+}
+
+template <class Scene, bool STATS>
+__device__ __forceinline__ Rgb<float> fast_camera_pixel(const Scene& sc, const SceneParams& sp, const CameraParams& cp, int col, int row,
+                                                        Counters& k) {
+    const Vec3 q = primary_offset(cp, col, row);
+    Rgb<float> c;
+    trace_chain_fast<Scene, STATS, true>(sc, sp, {cp.cam[0], cp.cam[1], cp.cam[2]}, q, fdot(q, q), c.x, c.y, c.z, k);
+    return c;
+}
+
+// KIND: 0 = sphere table staged in shared memory, 1 = BVH blob
+template <int MODE, bool STATS, int BLOCK, int KIND, int PW>
+__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (KIND == 1 ? RT_ACCEL_MIN_BLOCKS : RT_MIN_BLOCKS) : 1)
+    render_rows_kernel(const __grid_constant__ SceneParams sp, const __grid_constant__ CameraParams cp,
+                       const __grid_constant__ OutputParams out, const __grid_constant__ Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
-    AccelView av = {};
-    if (ACCEL) av = accel_view(sp.accel);
-    const Staged st = ACCEL ? stage_lights_only<MODE>(sp, smem, av) : stage_scene<MODE>(sp, smem, sp.eye);
+    if constexpr (MODE == kModeExact) {
+        const ExactTracer tr = {sp, stage_exact(sp, smem), KIND == 1 ? accel_view(sp.accel) : AccelView{}};
+        const Vec3 eye = {cp.cam[0], cp.cam[1], cp.cam[2]};
+        render_rows_body<STATS, BLOCK, PW>(cp, out, tk, [&](int col, int row, Counters& k) {
+            return tr.template ray<STATS, KIND == 1>(eye, primary_direction<kModeExact>(cp, col, row), k);
+        });
+    } else if constexpr (KIND == 1) {
+        const TreeScene sc = stage_tree(sp, smem);
+        render_rows_body<STATS, BLOCK, PW>(cp, out, tk, [&](int col, int row, Counters& k) {
+            return fast_camera_pixel<TreeScene, STATS>(sc, sp, cp, col, row, k);
+        });
+    } else {
+        const StagedScene sc = stage_fast(sp, smem, cp.cam);
+        render_rows_body<STATS, BLOCK, PW>(cp, out, tk, [&](int col, int row, Counters& k) {
+            return fast_camera_pixel<StagedScene, STATS>(sc, sp, cp, col, row, k);
+        });
+    }
+}
+
+// Scenes of N <= kSmallMax spheres, fast policy: the table is a kernel parameter.
+template <bool STATS, int N, int PW>
+__global__ void __launch_bounds__(kBlockThreads, RT_SMALL_MIN_BLOCKS)
+    render_rows_small_kernel(const __grid_constant__ SceneParams sp, const __grid_constant__ CameraParams cp,
+                             const __grid_constant__ OutputParams out, const __grid_constant__ Tickets tk,
+                             const __grid_constant__ SmallTable table) {
+    __shared__ __align__(16) unsigned char smem[N * sizeof(ShadeRec)];
+    const SmallScene<N> sc = stage_small<N>(sp, table, smem);
+    render_rows_body<STATS, kBlockThreads, PW>(cp, out, tk, [&](int col, int row, Counters& k) {
+        return fast_camera_pixel<SmallScene<N>, STATS>(sc, sp, cp, col, row, k);
+    });
+}
+
+// Explicit ray batch, one thread per ray, same work distribution (an item = 32 rays).
+template <bool STATS, int BLOCK, typename RayFn>
+__device__ __forceinline__ void trace_rays_body(const RayBatch& rb, const OutputParams& out, const Tickets& tk, RayFn&& ray) {
     const int lane = threadIdx.x & 31;
     const unsigned int warp_id = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
     Counters k = {0, 0, 0, 0};
-
     auto trace_item = [&](unsigned int item) {
         const long long i = (long long)item * 32 + lane;
         if (i < rb.n) {
             Vec3 o = {rb.origin0[0], rb.origin0[1], rb.origin0[2]};
             if (rb.origins != nullptr) o = {rb.origins[i], rb.origins[rb.n + i], rb.origins[2 * rb.n + i]};
-            Vec3 d = {rb.directions[i], rb.directions[rb.n + i], rb.directions[2 * rb.n + i]};
-            Vec3 c = trace_chain<MODE, STATS, false, ACCEL>(sp, st, av, o, d, k);
-            store_pixel(out, i, c);
+            const Vec3 d = {rb.directions[i], rb.directions[rb.n + i], rb.directions[2 * rb.n + i]};
+            store_pixel(out, i, ray(o, d, k));
         }
     };
-
     run_items(tk, lane, warp_id, trace_item);
     flush_counters<STATS>(k, out.stats);
+}
+
+template <class Scene, bool STATS>
+__device__ __forceinline__ Rgb<float> fast_ray(const Scene& sc, const SceneParams& sp, Vec3 o, Vec3 d, Counters& k) {
+    Rgb<float> c;
+    trace_chain_fast<Scene, STATS, false>(sc, sp, o, d, 1.0, c.x, c.y, c.z, k);
+    return c;
+}
+
+template <int MODE, bool STATS, int BLOCK, int KIND>
+__global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (KIND == 1 ? RT_ACCEL_MIN_BLOCKS : RT_MIN_BLOCKS) : 1)
+    trace_rays_kernel(const __grid_constant__ SceneParams sp, const __grid_constant__ RayBatch rb,
+                      const __grid_constant__ OutputParams out, const __grid_constant__ Tickets tk) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    if constexpr (MODE == kModeExact) {
+        const ExactTracer tr = {sp, stage_exact(sp, smem), KIND == 1 ? accel_view(sp.accel) : AccelView{}};
+        trace_rays_body<STATS, BLOCK>(rb, out, tk, [&](Vec3 o, Vec3 d, Counters& k) { return tr.template ray<STATS, KIND == 1>(o, d, k); });
+    } else if constexpr (KIND == 1) {
+        const TreeScene sc = stage_tree(sp, smem);
+        trace_rays_body<STATS, BLOCK>(rb, out, tk, [&](Vec3 o, Vec3 d, Counters& k) { return fast_ray<TreeScene, STATS>(sc, sp, o, d, k); });
+    } else {
+        const StagedScene sc = stage_fast(sp, smem, sp.eye);
+        trace_rays_body<STATS, BLOCK>(rb, out, tk, [&](Vec3 o, Vec3 d, Counters& k) { return fast_ray<StagedScene, STATS>(sc, sp, o, d, k); });
+    }
 }
 
 // NumpySphere.intersect (shape.py:28-51) for a ray batch against one sphere.

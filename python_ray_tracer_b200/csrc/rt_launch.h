@@ -8,8 +8,9 @@
 namespace rt {
 
 struct Launchers {
+    // `small`: host-built table of a scene of <= kSmallMax spheres (fast policy), or nullptr
     cudaError_t (*render_rows)(bool stats, const SceneParams&, const CameraParams&, const OutputParams&,
-                               cudaStream_t);
+                               const SmallTable* small, cudaStream_t);
     cudaError_t (*trace_rays)(bool stats, const SceneParams&, const RayBatch&, const OutputParams&,
                               cudaStream_t);
     cudaError_t (*sphere_distance)(const RayBatch&, const double* centre, double radius, double* out,

@@ -43,18 +43,9 @@ cudaError_t persistent_grid(Kernel kernel, int block_threads, size_t smem, unsig
     return cudaSuccess;
 }
 
-template <typename Kernel, typename Work>
-cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParams& sp, const Work& work,
-                              const OutputParams& out, unsigned long long n_items64, cudaStream_t stream,
-                              bool camera = false) {
-    if (n_items64 > 0x7ffffff0ull) return cudaErrorInvalidValue;  // 31-bit items (reciprocal division in the kernels)
-    const unsigned int n_items = (unsigned int)n_items64;
-    const size_t smem = sp.accel != nullptr ? sizeof(double) * 3 * (size_t)sp.n_lights_used + 16
-                                            : staged_bytes(sp.n_spheres, sp.n_lights_used);
-    unsigned int grid = 0;
-    cudaError_t err = persistent_grid(kernel, block_threads, smem, n_items, &grid);
-    if (err != cudaSuccess) return err;
-    Tickets tk;
+inline cudaError_t make_tickets(Tickets& tk, const SceneParams& sp, const OutputParams& out, unsigned int n_items, unsigned int grid,
+                                int block_threads, bool camera) {
+    cudaError_t err;
     if ((err = ticket_counter(&tk.counter)) != cudaSuccess) return err;
     tk.n_warps = grid * ((unsigned int)block_threads / 32u);
     tk.n_items = n_items;
@@ -68,35 +59,84 @@ cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParam
         tk.static_rounds = rounds - (unsigned int)((unsigned long long)rounds * RT_DYNAMIC_PCT / 100ull);
     }
     tk.n_tickets = n_items - tk.static_rounds * tk.n_warps;
+    // big blocks (items of >= 100 us) and scenes of costly items keep single tickets
+    const bool chunks = block_threads == kBlockThreads && sp.n_spheres < RT_COSTLY_ITEM_SPHERES;
+    tk.chunk_hi = chunks && RT_CHUNK4_ROUNDS > 0 ? RT_CHUNK4_ROUNDS * tk.n_warps : 0xffffffffu;
+    tk.chunk_mid = chunks && RT_CHUNK2_ROUNDS > 0 ? RT_CHUNK2_ROUNDS * tk.n_warps : 0xffffffffu;
+    return cudaSuccess;
+}
+
+template <typename Kernel, typename Work>
+cudaError_t launch_persistent(Kernel kernel, int block_threads, const SceneParams& sp, const Work& work,
+                              const OutputParams& out, unsigned long long n_items64, cudaStream_t stream,
+                              bool camera = false) {
+    if (n_items64 > 0x7ffffff0ull) return cudaErrorInvalidValue;  // 31-bit items (reciprocal division in the kernels)
+    const unsigned int n_items = (unsigned int)n_items64;
+    const size_t smem = sp.accel != nullptr ? sizeof(double) * 3 * (size_t)sp.n_lights_used + 16
+                                            : staged_bytes(sp.n_spheres, sp.n_lights_used);
+    unsigned int grid = 0;
+    cudaError_t err = persistent_grid(kernel, block_threads, smem, n_items, &grid);
+    if (err != cudaSuccess) return err;
+    Tickets tk;
+    if ((err = make_tickets(tk, sp, out, n_items, grid, block_threads, camera)) != cudaSuccess) return err;
     kernel<<<grid, block_threads, smem, stream>>>(sp, work, out, tk);
     return cudaGetLastError();
 }
 
+template <typename Kernel>
+cudaError_t launch_small(Kernel kernel, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
+                         const SmallTable& table, unsigned long long n_items64, cudaStream_t stream) {
+    if (n_items64 > 0x7ffffff0ull) return cudaErrorInvalidValue;
+    const unsigned int n_items = (unsigned int)n_items64;
+    unsigned int grid = 0;
+    cudaError_t err = persistent_grid(kernel, kBlockThreads, 0, n_items, &grid);
+    if (err != cudaSuccess) return err;
+    Tickets tk;
+    if ((err = make_tickets(tk, sp, out, n_items, grid, kBlockThreads, true)) != cudaSuccess) return err;
+    kernel<<<grid, kBlockThreads, 0, stream>>>(sp, cp, out, tk, table);
+    return cudaGetLastError();
+}
+
+template <int PW, int N>
+cudaError_t render_rows_small(bool stats, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
+                              const SmallTable& table, unsigned long long n, cudaStream_t stream) {
+    if constexpr (kMode == kModeFast) {
+        if (sp.n_spheres == N) {
+            if (stats) return launch_small(render_rows_small_kernel<true, N, PW>, sp, cp, out, table, n, stream);
+            return launch_small(render_rows_small_kernel<false, N, PW>, sp, cp, out, table, n, stream);
+        }
+        if constexpr (N > 1) return render_rows_small<PW, N - 1>(stats, sp, cp, out, table, n, stream);
+    }
+    return cudaErrorInvalidValue;
+}
+
 template <int PW>
 cudaError_t render_rows_patch(bool stats, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
-                              cudaStream_t stream) {
+                              const SmallTable* small, cudaStream_t stream) {
     const int rows = cp.n_rows;
     constexpr int kPatchH = 32 / PW;
     const unsigned long long tiles_x = (unsigned long long)(cp.width + PW - 1) / PW;
     const unsigned long long tiles_y = (unsigned long long)(rows + kPatchH - 1) / kPatchH;
     const unsigned long long n = tiles_x * tiles_y;
     if (sp.accel != nullptr) {
-        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, true, PW>, kBlockThreads, sp, cp, out, n, stream, true);
-        return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, true, PW>, kBlockThreads, sp, cp, out, n, stream, true);
+        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, 1, PW>, kBlockThreads, sp, cp, out, n, stream, true);
+        return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, 1, PW>, kBlockThreads, sp, cp, out, n, stream, true);
     }
+    if (kMode == kModeFast && small != nullptr && sp.n_spheres <= kSmallMax && sp.n_lights_used == 1)
+        return render_rows_small<PW, kSmallMax>(stats, sp, cp, out, *small, n, stream);
     if (big_blocks(sp.n_spheres)) {
-        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads, false, PW>, kBigBlockThreads, sp, cp, out, n, stream, true);
-        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads, false, PW>, kBigBlockThreads, sp, cp, out, n, stream, true);
+        if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBigBlockThreads, 0, PW>, kBigBlockThreads, sp, cp, out, n, stream, true);
+        return launch_persistent(render_rows_kernel<kMode, false, kBigBlockThreads, 0, PW>, kBigBlockThreads, sp, cp, out, n, stream, true);
     }
-    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, false, PW>, kBlockThreads, sp, cp, out, n, stream, true);
-    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, false, PW>, kBlockThreads, sp, cp, out, n, stream, true);
+    if (stats) return launch_persistent(render_rows_kernel<kMode, true, kBlockThreads, 0, PW>, kBlockThreads, sp, cp, out, n, stream, true);
+    return launch_persistent(render_rows_kernel<kMode, false, kBlockThreads, 0, PW>, kBlockThreads, sp, cp, out, n, stream, true);
 }
 
 cudaError_t render_rows(bool stats, const SceneParams& sp, const CameraParams& cp, const OutputParams& out,
-                        cudaStream_t stream) {
+                        const SmallTable* small, cudaStream_t stream) {
     if (cp.n_rows <= 0 || cp.width <= 0) return cudaSuccess;
-    if (out.wide_patches) return render_rows_patch<kWideTileW>(stats, sp, cp, out, stream);
-    return render_rows_patch<kWarpTileW>(stats, sp, cp, out, stream);
+    if (out.wide_patches) return render_rows_patch<kWideTileW>(stats, sp, cp, out, small, stream);
+    return render_rows_patch<kWarpTileW>(stats, sp, cp, out, small, stream);
 }
 
 cudaError_t trace_rays(bool stats, const SceneParams& sp, const RayBatch& rb, const OutputParams& out,
@@ -104,15 +144,15 @@ cudaError_t trace_rays(bool stats, const SceneParams& sp, const RayBatch& rb, co
     if (rb.n <= 0) return cudaSuccess;
     const unsigned long long n_items = ((unsigned long long)rb.n + 31ull) / 32ull;
     if (sp.accel != nullptr) {
-        if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBlockThreads, true>, kBlockThreads, sp, rb, out, n_items, stream);
-        return launch_persistent(trace_rays_kernel<kMode, false, kBlockThreads, true>, kBlockThreads, sp, rb, out, n_items, stream);
+        if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBlockThreads, 1>, kBlockThreads, sp, rb, out, n_items, stream);
+        return launch_persistent(trace_rays_kernel<kMode, false, kBlockThreads, 1>, kBlockThreads, sp, rb, out, n_items, stream);
     }
     if (big_blocks(sp.n_spheres)) {
-        if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBigBlockThreads, false>, kBigBlockThreads, sp, rb, out, n_items, stream);
-        return launch_persistent(trace_rays_kernel<kMode, false, kBigBlockThreads, false>, kBigBlockThreads, sp, rb, out, n_items, stream);
+        if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBigBlockThreads, 0>, kBigBlockThreads, sp, rb, out, n_items, stream);
+        return launch_persistent(trace_rays_kernel<kMode, false, kBigBlockThreads, 0>, kBigBlockThreads, sp, rb, out, n_items, stream);
     }
-    if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBlockThreads, false>, kBlockThreads, sp, rb, out, n_items, stream);
-    return launch_persistent(trace_rays_kernel<kMode, false, kBlockThreads, false>, kBlockThreads, sp, rb, out, n_items, stream);
+    if (stats) return launch_persistent(trace_rays_kernel<kMode, true, kBlockThreads, 0>, kBlockThreads, sp, rb, out, n_items, stream);
+    return launch_persistent(trace_rays_kernel<kMode, false, kBlockThreads, 0>, kBlockThreads, sp, rb, out, n_items, stream);
 }
 
 cudaError_t sphere_distance(const RayBatch& rb, const double* c, double radius, double* out,

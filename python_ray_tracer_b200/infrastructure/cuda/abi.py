@@ -12,7 +12,7 @@ import os
 from pathlib import Path
 from typing import Optional, Sequence
 
-RT_ABI_VERSION = 2
+RT_ABI_VERSION = 3
 RT_FARAWAY = 1.0e39
 RT_MAX_DOME_LIGHTS = 8
 RT_STATS_WORDS = 4
@@ -28,6 +28,8 @@ RT_FLAG_ACCEL_FAST_BUILD = 8
 RT_FLAG_WIDE_STORES = 16
 RT_FLAG_RGB8 = 32
 RT_FLAG_EVEN_STORES = 64
+RT_FLAG_GENERIC_KERNEL = 128
+RT_SMALL_SCENE_SPHERES = 4
 RT_ACCEL_AUTO_SPHERES = 32
 RT_IPC_HANDLE_BYTES = 64
 RT_DTYPE_F32 = 0
@@ -57,6 +59,8 @@ class RtEnv(C.Structure):
         ("cutoff", C.c_double),
         ("accel_dev", C.c_void_p),
         ("accel_bytes", C.c_int64),
+        ("spheres_host", C.c_void_p),
+        ("point_lights_host", C.c_void_p),
     ]
 
 
@@ -77,7 +81,12 @@ def make_env(
     mode: int = RT_MODE_EXACT,
     flags: int = RT_FLAG_NONE,
     cutoff: float = 0.0,
+    spheres_host=None,
+    point_lights_host=None,
 ) -> RtEnv:
+    """``spheres_host`` / ``point_lights_host``: the caller's C-contiguous float64 NumPy copies of the
+    tables the call's device pointers hold (``rt_env.spheres_host``); the caller keeps them alive
+    for the duration of the call."""
     env = RtEnv()
     env.eye[:] = [float(v) for v in eye]
     env.n_point_lights = int(n_point_lights)
@@ -91,6 +100,10 @@ def make_env(
     env.mode = int(mode)
     env.flags = int(flags)
     env.cutoff = float(cutoff)
+    if spheres_host is not None:
+        env.spheres_host = spheres_host.ctypes.data
+    if point_lights_host is not None:
+        env.point_lights_host = point_lights_host.ctypes.data
     return env
 
 

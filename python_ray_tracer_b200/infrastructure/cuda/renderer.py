@@ -209,6 +209,8 @@ class CudaRenderer(Renderer):
             mode=_PRECISIONS[self.precision],
             flags=(abi.RT_FLAG_ALL_POINT_LIGHTS if self.all_point_lights else abi.RT_FLAG_NONE) | extra_flags,
             cutoff=self.cutoff if self.precision == "fast" else 0.0,
+            spheres_host=flat.spheres,
+            point_lights_host=flat.point_lights,
         )
 
     def flatten(self, scene: Scene3D) -> FlatScene:

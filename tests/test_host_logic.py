@@ -173,7 +173,7 @@ def test_abi_library_exports_every_declared_symbol():
         assert hasattr(lib, name), name
     assert lib.rt_abi_version() == abi.RT_ABI_VERSION
     # struct layouts the header promises
-    assert ctypes.sizeof(abi.RtCamera) == 32 and ctypes.sizeof(abi.RtEnv) == 160
+    assert ctypes.sizeof(abi.RtCamera) == 32 and ctypes.sizeof(abi.RtEnv) == 176
 
 
 def test_ctypes_structs_match_the_header_as_compiled(tmp_path):
@@ -183,14 +183,14 @@ def test_ctypes_structs_match_the_header_as_compiled(tmp_path):
     src.write_text(
         '#include <stdio.h>\n#include <stddef.h>\n#include "rt_abi.h"\n'
         'int main(void){printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(rt_env), sizeof(rt_camera), '
-        'offsetof(rt_env, dome_intensity), offsetof(rt_env, max_depth), offsetof(rt_env, cutoff), '
+        'offsetof(rt_env, dome_intensity), offsetof(rt_env, max_depth), offsetof(rt_env, spheres_host), '
         'offsetof(rt_camera, width));return 0;}\n'
     )
     exe = tmp_path / "sizes"
     subprocess.run(["/usr/bin/gcc", "-I", str(ROOT / "include"), str(src), "-o", str(exe)], check=True)
     got = [int(v) for v in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     want = [ctypes.sizeof(abi.RtEnv), ctypes.sizeof(abi.RtCamera), abi.RtEnv.dome_intensity.offset,
-            abi.RtEnv.max_depth.offset, abi.RtEnv.cutoff.offset, abi.RtCamera.width.offset]
+            abi.RtEnv.max_depth.offset, abi.RtEnv.spheres_host.offset, abi.RtCamera.width.offset]
     assert got == want
 
 
@@ -284,10 +284,13 @@ def _parse_accel(blob: bytes):
     import struct
 
     magic, n, n_nodes, n_tree, n_large, _ = struct.unpack_from("<Iiiiii", blob, 0)
-    offs = struct.unpack_from("<7q", blob, 24)
-    local_bound, gain_bound = struct.unpack_from("<2d", blob, 24 + 56)
-    (extent,) = struct.unpack_from("<f", blob, 24 + 56 + 16)
-    off_nodes, off_order, off_leaf, off_geom, off_aux, off_large, total = offs
+    offs = struct.unpack_from("<8q", blob, 24)
+    local_bound, gain_bound = struct.unpack_from("<2d", blob, 24 + 64)
+    (extent,) = struct.unpack_from("<f", blob, 24 + 64 + 16)
+    off_nodes, off_order, off_leaf, off_geom, off_aux, off_large, off_rec, total = offs
+    rec = np.frombuffer(blob, dtype=np.dtype([("c", "<f8", 3), ("inv_r", "<f8"), ("kd", "<f4", 3), ("spec_gain", "<f4"),
+                                              ("a2", "<f4"), ("film", "<f4"), ("half_gain", "<f4"), ("flags", "<u4")]),
+                        count=n, offset=off_rec)
     nodes = np.frombuffer(blob, dtype=np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("ref", "<u4"), ("axis", "<i4")]),
                           count=n_nodes, offset=off_nodes)
     order = np.frombuffer(blob, dtype="<i4", count=n_tree, offset=off_order)
@@ -295,7 +298,7 @@ def _parse_accel(blob: bytes):
     geom = np.frombuffer(blob, dtype="<f8", count=4 * n, offset=off_geom).reshape(-1, 4)
     aux = np.frombuffer(blob, dtype="<f8", count=2 * n, offset=off_aux).reshape(-1, 2)
     large = np.frombuffer(blob, dtype="<i4", count=n_large, offset=off_large)
-    return dict(magic=magic, n=n, nodes=nodes, order=order, leaf_geom=leaf_geom, geom=geom, aux=aux, large=large,
+    return dict(magic=magic, n=n, nodes=nodes, order=order, leaf_geom=leaf_geom, geom=geom, aux=aux, large=large, rec=rec,
                 total=total, local_bound=local_bound, gain_bound=gain_bound, extent=extent)
 
 
@@ -318,7 +321,7 @@ def test_accel_blob_is_a_valid_tree(n_spheres, fast_build):
     assert lib.rt_accel_build_host(flat.spheres.ctypes.data, n, ctypes.byref(env), buf.ctypes.data, cap, ctypes.byref(used)) == 0
     assert lib.rt_accel_build_host(flat.spheres.ctypes.data, n, ctypes.byref(env), buf.ctypes.data, 64, ctypes.byref(used)) == -1
     a = _parse_accel(buf[: used.value].tobytes())
-    assert a["magic"] == 0x52544256 and a["n"] == n and a["total"] == used.value <= cap
+    assert a["magic"] == 0x32425452 and a["n"] == n and a["total"] == used.value <= cap
     assert sorted(a["order"].tolist() + a["large"].tolist()) == list(range(n))
     if n > 2:
         assert (n - 1) in a["large"].tolist()  # the radius-99999 ground stays out of the tree
@@ -326,6 +329,13 @@ def test_accel_blob_is_a_valid_tree(n_spheres, fast_build):
     assert np.array_equal(a["geom"][:, :3], c) and np.array_equal(a["geom"][:, 3], flat.spheres[3] ** 2)
     assert np.array_equal(a["leaf_geom"], a["geom"][a["order"]]) and np.array_equal(a["aux"][:, 0], 1.0 / flat.spheres[3])
     assert a["gain_bound"] == np.abs(flat.spheres[5]).max() and a["local_bound"] > 0
+    # the fast policy's shading records (rt_device.cuh: ShadeRec)
+    rec, f = a["rec"], flat.spheres
+    checker = f[11] != 0
+    assert np.array_equal(rec["c"], c) and np.array_equal(rec["inv_r"], 1.0 / f[3])
+    assert np.array_equal(rec["kd"], np.where(checker[:, None], f[4][:, None], (f[4] * f[8:11]).T).astype(np.float32))
+    assert np.array_equal(rec["a2"], ((f[6] * f[6]) ** 2).astype(np.float32)) and np.array_equal(rec["flags"] & 1, checker.astype(np.uint32))
+    assert np.array_equal(rec["half_gain"], (0.5 * f[5]).astype(np.float32)) and np.array_equal(rec["film"], (0.1 * f[7]).astype(np.float32))
 
     depths = []
 

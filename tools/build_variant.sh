@@ -20,4 +20,4 @@ ${CXX:-g++} -O3 -std=c++17 -fPIC -Wall -c "$src/rt_png_host.cpp" -o "$out/rt_png
 pids+=($!)
 for p in "${pids[@]}"; do wait "$p"; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "$out/librt_b200.so" "$out"/*.o
-$NVCC $FLAGS "$@" -Xptxas -v -c "$src/trace_fast.cu" -o /dev/null 2>&1 | grep -A2 "render_rows_kernelILi1ELb0" | grep -E "Used|spill" | sed "s/^/[$name] /"
+$NVCC $FLAGS "$@" -Xptxas -v -c "$src/trace_fast.cu" -o /dev/null 2>&1 | grep -A2 "render_rows_small_kernelILb0ELi3ELi8" | grep -E "Used|spill" | sed "s/^/[$name] /"
