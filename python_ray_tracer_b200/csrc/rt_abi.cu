@@ -177,7 +177,7 @@ rt::CameraParams camera_params(const rt_camera* cam, int32_t row0, int32_t row1)
 // is using it: the kernels put it back to zero themselves.
 constexpr int kMaxDevices = 64;
 constexpr unsigned int kRingSlots = 1024;
-constexpr unsigned int kRingStride = 8;  // a slot is two counters (rt_kernels.cuh: Tickets) in a 32-byte sector of its own
+constexpr unsigned int kRingStride = 8;  // every counter in a 32-byte sector of its own
 struct CounterRing {
     unsigned int* base = nullptr;
     std::atomic<unsigned int> next{0};

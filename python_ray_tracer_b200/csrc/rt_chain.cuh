@@ -106,14 +106,18 @@ __device__ __forceinline__ TreeScene stage_tree(const SceneParams& sp, unsigned 
 
 template <int N>
 __device__ __forceinline__ SmallScene<N> stage_small(const SceneParams& sp, const SmallTable& table, unsigned char* smem) {
-    // the records shading indexes by the sphere that was hit: a shared-memory copy (16 words per record)
+    // what is indexed by a sphere number only known at run time (the sphere that was hit, the others of
+    // its shadow test): a shared-memory copy, N * (16 + 8) words
     unsigned int* dst = reinterpret_cast<unsigned int*>(smem);
-    const unsigned int* src = reinterpret_cast<const unsigned int*>(table.rec);
-    for (int i = threadIdx.x; i < N * (int)(sizeof(ShadeRec) / 4); i += blockDim.x) dst[i] = src[i];
+    const unsigned int* rec = reinterpret_cast<const unsigned int*>(table.rec);
+    const unsigned int* geom = reinterpret_cast<const unsigned int*>(table.geom);
+    for (int i = threadIdx.x; i < N * 16; i += blockDim.x) dst[i] = rec[i];
+    for (int i = threadIdx.x; i < N * 8; i += blockDim.x) dst[N * 16 + i] = geom[i];
     __syncthreads();
     SmallScene<N> sc;
     sc.t = &table;
     sc.recs = (unsigned int)__cvta_generic_to_shared(smem);
+    sc.geoms = sc.recs + N * 64u;
     sc.light0 = {sp.light0[0], sp.light0[1], sp.light0[2]};
     sc.bound = sp.chain_bound;
     return sc;

@@ -96,6 +96,7 @@ template <int N>
 struct SmallScene {
     const SmallTable* t;  // the kernel parameter: compile-time indices become constant-bank operands
     unsigned int recs;    // shared-memory copy of t->rec, indexed by the sphere that was hit
+    unsigned int geoms;   // and of t->geom, indexed by "the other spheres" of the shadow test
     Vec3 light0;
     float bound;
 
@@ -104,33 +105,43 @@ struct SmallScene {
     __device__ __forceinline__ float chain_bound() const { return bound; }
     __device__ __forceinline__ ShadeRec rec(int s) const { return lds_rec(recs + (unsigned int)s * 64u); }
 
+    // all N tests first (independent FP64 chains interleave), then the roots of those that can be hit
     __device__ __forceinline__ void nearest_primary(Vec3, Vec3 q, double a, double& tmin, int& sid, unsigned long long& tests) const {
         tests += N;
+        HalfB h[N];
 #pragma unroll
-        for (int s = 0; s < N; ++s) {
-            const HalfB h = half_b_primary(q, a, t->prim[s]);
-            if (can_hit(h)) consider(near_root(h), s, tmin, sid);
-        }
+        for (int s = 0; s < N; ++s) h[s] = half_b_primary(q, a, t->prim[s]);
+#pragma unroll
+        for (int s = 0; s < N; ++s)
+            if (can_hit(h[s])) consider(near_root(h[s]), s, tmin, sid);
     }
     __device__ __forceinline__ void nearest(Vec3 o, Vec3 d, double& tmin, int& sid, unsigned long long& tests) const {
         tests += N;
+        HalfB h[N];
 #pragma unroll
-        for (int s = 0; s < N; ++s) {
-            const HalfB h = half_b(o, d, t->geom[s]);
-            if (can_hit(h)) consider(near_root(h), s, tmin, sid);
-        }
+        for (int s = 0; s < N; ++s) h[s] = half_b(o, d, t->geom[s]);
+#pragma unroll
+        for (int s = 0; s < N; ++s)
+            if (can_hit(h[s])) consider(near_root(h[s]), s, tmin, sid);
     }
-    // is any sphere but `own` met by the ray p + u*lv, u > 0?  (no roots needed)
+    // is any sphere but `own` met by the ray p + u*lv, u > 0?  (no roots needed)  The N - 1 others are
+    // own + 1, own + 2, ... (mod N), read from the shared-memory copy: straight-line, nothing wasted on `own`.
     __device__ __forceinline__ bool others_hit(Vec3 p, Vec3 lv, double ll, int own, unsigned long long& tests) const {
         tests += N;
         bool any = false;
+        int s = own;
 #pragma unroll
-        for (int s = 0; s < N; ++s)
-            if (s != own) any = any || can_hit(half_b_scaled(p, lv, ll, t->geom[s]));
+        for (int j = 1; j < N; ++j) {
+            s = s + 1 == N ? 0 : s + 1;
+            SphereGeom g;
+            lds_f64x2(geoms + (unsigned int)s * 32u, g.cx, g.cy);
+            lds_f64x2(geoms + (unsigned int)s * 32u + 16u, g.cz, g.rr);
+            any |= can_hit(half_b_scaled(p, lv, ll, g));
+        }
         return any;
     }
     // the whole of shader.py:126-128: lit iff no other sphere is nearer than the point's own
-    __device__ __noinline__ bool lit_slow(Vec3 p, Vec3 lv, double ll, int own, unsigned long long&) const {
+    __device__ __forceinline__ bool lit_slow(Vec3 p, Vec3 lv, double ll, int own, unsigned long long&) const {
         double mine = kMiss, other = kMiss;
 #pragma unroll
         for (int s = 0; s < N; ++s) {
@@ -205,7 +216,7 @@ struct StagedScene {
         if (s < n && s != own) any = can_hit(half_b_scaled(p, lv, ll, g(s)));
         return any;
     }
-    __device__ __noinline__ bool lit_slow(Vec3 p, Vec3 lv, double ll, int own, unsigned long long&) const {
+    __device__ __forceinline__ bool lit_slow(Vec3 p, Vec3 lv, double ll, int own, unsigned long long&) const {
         const HalfB ho = half_b_scaled(p, lv, ll, g(own));
         const double mine = can_hit(ho) ? near_root(ho) : kMiss;
         for (int s = 0; s < n; ++s) {
@@ -256,7 +267,7 @@ struct TreeScene {
             return can_hit(half_b_scaled(p, lv, ll, g)) ? 0.0 : kMiss;
         });
     }
-    __device__ __noinline__ bool lit_slow(Vec3 p, Vec3 lv, double ll, int own, unsigned long long& tests) const {
+    __device__ __forceinline__ bool lit_slow(Vec3 p, Vec3 lv, double ll, int own, unsigned long long& tests) const {
         const HalfB ho = half_b_scaled(p, lv, ll, ldg_geom(av.geom + own));
         const double mine = can_hit(ho) ? near_root(ho) : kMiss;
         tests += 1;

@@ -68,27 +68,29 @@ constexpr size_t kSmemPerSm = 227 * 1024;
 //
 // Draws on ONE address are served at about one per nanosecond by the L2 slice that owns it: a
 // 1080p frame of trivial patches took 68 us in round 1 (64 800 single-ticket draws), which is the
-// whole budget of a frame now.  So a draw takes 4 consecutive tickets while the launch is young, 2
-// later and 1 at the end (chunk_hi / chunk_mid: tickets left at which the size drops); with the
-// bottom-up order the single tickets are the cheap sky patches, so the launch still ends level.
+// whole budget of a frame now.  So a draw may take several consecutive tickets while the launch is
+// young and single ones at the end (RT_CHUNK4_ROUNDS / RT_CHUNK2_ROUNDS); with the bottom-up order
+// the single tickets are the cheap sky patches, so the launch still ends level.
 struct Tickets {
-    unsigned int* counter;       // [0] tickets drawn so far, [1] warps that have left (both zero between launches)
+    unsigned int* counter;       // draws so far; zero between launches (the last draw of a launch wraps it)
     unsigned int n_tickets;      // items handed out dynamically
     unsigned int n_warps;        // gridDim.x * (block threads / 32)
     unsigned int static_rounds;  // items [0, static_rounds * n_warps) are dealt statically
     unsigned int n_items;
     unsigned int reversed;       // 1: take items from the last one backwards; 2: alternately from both ends (wide-store kernels)
-    unsigned int chunk_hi, chunk_mid;
+    // draw k takes tickets [4k, 4k+4) for k < n4, then pairs for the next n2 draws, then single tickets
+    unsigned int n4, n2, cover4, cover2, n_draws;
 };
-__device__ __forceinline__ unsigned int chunk_size(const Tickets& tk, unsigned int drawn_so_far) {
-    const unsigned int left = tk.n_tickets > drawn_so_far ? tk.n_tickets - drawn_so_far : 0u;
-    return left > tk.chunk_hi ? 4u : (left > tk.chunk_mid ? 2u : 1u);
-}
 // A draw is split in two: issue_draw() starts the atomic, take_draw() broadcasts its result when
-// the warp has run out of items.
-__device__ __forceinline__ unsigned int issue_draw(const Tickets& tk, int lane, unsigned int count) {
+// the warp has run out of items.  The atomic is atom.inc with the launch's last draw as its bound
+// (every warp ends on one draw past the last chunk, n_draws + n_warps draws in all): the counter
+// re-arms itself for the next launch, and -- unlike atom.add under a lane == 0 predicate -- ptxas
+// does not wrap it in its warp-aggregation sequence (vote, prefix shuffles, a second atomic).  Which
+// tickets a draw takes is a function of its index, so chunks need no atom.add.
+__device__ __forceinline__ unsigned int issue_draw(const Tickets& tk, int lane) {
     unsigned int t = 0;
-    if (lane == 0) asm volatile("atom.global.add.u32 %0, [%1], %2;" : "=r"(t) : "l"(tk.counter), "r"(count));
+    if (lane == 0)
+        asm volatile("atom.global.inc.u32 %0, [%1], %2;" : "=r"(t) : "l"(tk.counter), "r"(tk.n_draws + tk.n_warps - 1u));
     return t;
 }
 __device__ __forceinline__ unsigned int take_draw(unsigned int t) { return __shfl_sync(0xffffffffu, t, 0); }
@@ -96,11 +98,9 @@ __device__ __forceinline__ unsigned int take_draw(unsigned int t) { return __shf
 // The item loop of a warp: the static rounds, then chunks of tickets, the next draw kept in flight
 // under the items of the current one.  One copy of the item body (it is most of the kernel's code,
 // and the instruction cache is cold at every launch of the bench: L2 is flushed between frames).
-// The last warp to leave puts the counters back to zero for the next launch that uses them.
 template <typename Item>
 __device__ __forceinline__ void run_items(const Tickets& tk, const int lane, const unsigned int warp_id, Item&& item) {
-    unsigned int size = chunk_size(tk, 0u);
-    unsigned int drawn = issue_draw(tk, lane, size);  // in flight during the static rounds
+    unsigned int drawn = issue_draw(tk, lane);  // in flight during the static rounds
     const unsigned int first_dynamic = tk.static_rounds * tk.n_warps;
     unsigned int round = 0, pos = 0, end = 0;
 #pragma unroll 1
@@ -111,20 +111,23 @@ __device__ __forceinline__ void run_items(const Tickets& tk, const int lane, con
             ++round;
         } else {
             if (pos == end) {
-                pos = take_draw(drawn);
-                if (pos >= tk.n_tickets) break;
-                end = pos + size < tk.n_tickets ? pos + size : tk.n_tickets;
-                size = chunk_size(tk, end);
-                drawn = issue_draw(tk, lane, size);
+                const unsigned int k = take_draw(drawn);
+                if (k >= tk.n_draws) break;
+                if (k < tk.n4) {
+                    pos = 4u * k;
+                    end = pos + 4u < tk.cover4 ? pos + 4u : tk.cover4;
+                } else if (k < tk.n4 + tk.n2) {
+                    pos = tk.cover4 + 2u * (k - tk.n4);
+                    end = pos + 2u < tk.cover4 + tk.cover2 ? pos + 2u : tk.cover4 + tk.cover2;
+                } else {
+                    pos = tk.cover4 + tk.cover2 + (k - tk.n4 - tk.n2);
+                    end = pos + 1u;
+                }
+                drawn = issue_draw(tk, lane);
             }
             idx = first_dynamic + pos++;
         }
         item(idx);
-    }
-    if (lane == 0) {
-        unsigned int left;
-        asm volatile("atom.global.inc.u32 %0, [%1], %2;" : "=r"(left) : "l"(tk.counter + 1), "r"(tk.n_warps - 1u));
-        if (left == tk.n_warps - 1u) atomicExch(tk.counter, 0u);  // every other warp has made its last draw
     }
 }
 
@@ -264,8 +267,17 @@ __device__ __forceinline__ void render_rows_body(const CameraParams& cp, const O
     const unsigned int warp_id = blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5);
     Counters k = {0, 0, 0, 0};
 
+#ifdef RT_TIMING_DEBUG
+    // experiment only (tools/warp_timeline.py): per-warp and per-item start/end stamps behind the counters
+    unsigned long long t_start = 0;
+    if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+#endif
     auto render_item = [&](unsigned int idx) {
         unsigned int item = tk.reversed ? tk.n_items - 1u - idx : idx;
+#ifdef RT_TIMING_DEBUG
+        unsigned long long t_item0 = 0;
+        if (STATS) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_item0));
+#endif
         if constexpr (PW == kWideTileW) {
             // frames that several GPUs write (RT_FLAG_EVEN_STORES): two patches from the bottom, then one
             // from the top, so that cheap rows (many stores per microsecond) and costly ones mix over the
@@ -304,8 +316,27 @@ __device__ __forceinline__ void render_rows_body(const CameraParams& cp, const O
             const auto c = pixel(col, row, k);
             store_pixel(out, (long long)(out.image_order ? row : local_row) * cp.width + col, c);
         }
+#ifdef RT_TIMING_DEBUG
+        if (STATS && out.stats != nullptr) {
+            __syncwarp();
+            unsigned long long t_item1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_item1));
+            if (lane == 0) {
+                out.stats[8 + 2 * 148 * 32 + 2 * item] = t_item0;
+                out.stats[8 + 2 * 148 * 32 + 2 * item + 1] = t_item1;
+            }
+        }
+#endif
     };
     run_items(tk, lane, warp_id, render_item);
+#ifdef RT_TIMING_DEBUG
+    if (STATS && out.stats != nullptr && lane == 0) {
+        unsigned long long t_end;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+        out.stats[8 + 2 * warp_id] = t_start;
+        out.stats[8 + 2 * warp_id + 1] = t_end;
+    }
+#endif
     flush_counters<STATS>(k, out.stats);
 }
 
@@ -356,7 +387,7 @@ __global__ void __launch_bounds__(kBlockThreads, RT_SMALL_MIN_BLOCKS)
     render_rows_small_kernel(const __grid_constant__ SceneParams sp, const __grid_constant__ CameraParams cp,
                              const __grid_constant__ OutputParams out, const __grid_constant__ Tickets tk,
                              const __grid_constant__ SmallTable table) {
-    __shared__ __align__(16) unsigned char smem[N * sizeof(ShadeRec)];
+    __shared__ __align__(16) unsigned char smem[N * (sizeof(ShadeRec) + sizeof(SphereGeom))];
     const SmallScene<N> sc = stage_small<N>(sp, table, smem);
     render_rows_body<STATS, kBlockThreads, PW>(cp, out, tk, [&](int col, int row, Counters& k) {
         return fast_camera_pixel<SmallScene<N>, STATS>(sc, sp, cp, col, row, k);

@@ -61,8 +61,15 @@ inline cudaError_t make_tickets(Tickets& tk, const SceneParams& sp, const Output
     tk.n_tickets = n_items - tk.static_rounds * tk.n_warps;
     // big blocks (items of >= 100 us) and scenes of costly items keep single tickets
     const bool chunks = block_threads == kBlockThreads && sp.n_spheres < RT_COSTLY_ITEM_SPHERES;
-    tk.chunk_hi = chunks && RT_CHUNK4_ROUNDS > 0 ? RT_CHUNK4_ROUNDS * tk.n_warps : 0xffffffffu;
-    tk.chunk_mid = chunks && RT_CHUNK2_ROUNDS > 0 ? RT_CHUNK2_ROUNDS * tk.n_warps : 0xffffffffu;
+    const unsigned int T = tk.n_tickets;
+    const unsigned int hi = chunks && RT_CHUNK4_ROUNDS > 0 ? RT_CHUNK4_ROUNDS * tk.n_warps : 0xffffffffu;
+    const unsigned int mid = chunks && RT_CHUNK2_ROUNDS > 0 ? RT_CHUNK2_ROUNDS * tk.n_warps : 0xffffffffu;
+    tk.n4 = T > hi ? (T - hi + 3u) / 4u : 0u;
+    tk.cover4 = 4u * tk.n4 < T ? 4u * tk.n4 : T;
+    const unsigned int rest = T - tk.cover4;
+    tk.n2 = rest > mid ? (rest - mid + 1u) / 2u : 0u;
+    tk.cover2 = 2u * tk.n2 < rest ? 2u * tk.n2 : rest;
+    tk.n_draws = tk.n4 + tk.n2 + (rest - tk.cover2);
     return cudaSuccess;
 }
 

@@ -151,7 +151,7 @@ def test_exact_and_fast_agree_at_1080p(rt):
     a8 = (255 * np.clip(a, 0, 1)).astype(np.uint8).T
     b8 = (255 * np.clip(b, 0, 1)).astype(np.uint8).T
     assert_png_parity(b8, a8, "fast vs exact 1080p")
-    assert rep["max_abs"] < 1e-6
+    assert rep["max_abs"] < 1e-5  # the fast policy shades in single precision (values up to ~1.7)
 
 
 def test_c3_1024_spheres_4k_band(rt, c_oracle):

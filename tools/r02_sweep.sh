@@ -8,14 +8,17 @@ cd "$root"
 case "${1:-}" in
 build)
   rm -rf build/variants
-  tools/build_variant.sh base
-  tools/build_variant.sh mb6 -DRT_SMALL_MIN_BLOCKS=6                      # 80 registers, 6 blocks per SM
-  tools/build_variant.sh mb4 -DRT_SMALL_MIN_BLOCKS=4                      # 128 registers, 4 blocks per SM
-  tools/build_variant.sh single -DRT_CHUNK4_ROUNDS=0 -DRT_CHUNK2_ROUNDS=0  # one ticket per draw, as in round 1
-  tools/build_variant.sh chunk2 -DRT_CHUNK4_ROUNDS=0 -DRT_CHUNK2_ROUNDS=2  # at most two tickets per draw
-  tools/build_variant.sh chunk84 -DRT_CHUNK4_ROUNDS=8 -DRT_CHUNK2_ROUNDS=4 # chunks end earlier
-  tools/build_variant.sh spec32 -DRT_SPEC_F32_A2=0.03f                    # rough materials: |H|^2 and N.H in FP32
-  tools/build_variant.sh nosmall -DRT_SMALL_MAX=1                         # README scene through the staged-table kernel
+  make -C python_ray_tracer_b200/csrc >/dev/null
+  (tools/build_variant.sh base) &
+  (tools/build_variant.sh mb6 -DRT_SMALL_MIN_BLOCKS=6) &                       # 80 registers, 6 blocks per SM
+  (tools/build_variant.sh single -DRT_CHUNK4_ROUNDS=0 -DRT_CHUNK2_ROUNDS=0) &  # one ticket per draw, as in round 1
+  (tools/build_variant.sh chunk2 -DRT_CHUNK4_ROUNDS=0 -DRT_CHUNK2_ROUNDS=2) &  # pairs, single tickets for the last 2 rounds
+  wait
+  (tools/build_variant.sh chunk2b -DRT_CHUNK4_ROUNDS=0 -DRT_CHUNK2_ROUNDS=6) & # pairs end earlier
+  (tools/build_variant.sh chunk42 -DRT_CHUNK4_ROUNDS=12 -DRT_CHUNK2_ROUNDS=4) & # fours only at the very start
+  (tools/build_variant.sh mb6c2 -DRT_SMALL_MIN_BLOCKS=6 -DRT_CHUNK4_ROUNDS=0 -DRT_CHUNK2_ROUNDS=2) &
+  (tools/build_variant.sh timing -DRT_TIMING_DEBUG -DRT_CHUNK4_ROUNDS=0 -DRT_CHUNK2_ROUNDS=2) &
+  wait
   ;;
 run)
   for wl in c2 c1 c4; do

@@ -17,7 +17,8 @@ dev = torch.device("cuda", 0)
 stream = torch.cuda.current_stream(0)
 w, h = 1920, 1080
 flat = flatten_scene(scenes.readme_scene(w, h), DefaultMaterial(**scenes.README_GAINS))
-env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, mode=abi.RT_MODE_FAST, cutoff=1e-7)
+env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, mode=abi.RT_MODE_FAST, cutoff=1e-7,
+                   spheres_host=flat.spheres, point_lights_host=flat.point_lights)
 cam = abi.make_camera(flat.eye, w, h)
 sph, lig = torch.from_numpy(flat.spheres).to(dev), torch.from_numpy(flat.point_lights).to(dev)
 n = w * h
