@@ -25,11 +25,14 @@ namespace rt {
 #ifndef RT_COSTLY_ITEM_SPHERES
 #define RT_COSTLY_ITEM_SPHERES 8   // scenes with at least this many spheres are ticketed entirely
 #endif
+// Tickets per draw (profiles/r02/ticket_chunks.txt): fours lose (four neighbouring patches where the
+// spheres meet the ground outlast the frame), pairs while more than 6 rounds are left win 6 % at 1080p
+// and cost nothing on short launches, which stay on single tickets.
 #ifndef RT_CHUNK4_ROUNDS
-#define RT_CHUNK4_ROUNDS 4   // a draw takes 4 tickets while more than this many per warp are left ...
+#define RT_CHUNK4_ROUNDS 0   // a draw takes 4 tickets while more than this many per warp are left (0: never) ...
 #endif
 #ifndef RT_CHUNK2_ROUNDS
-#define RT_CHUNK2_ROUNDS 2   // ... 2 while more than this many are left, then 1 (0 0: always single tickets)
+#define RT_CHUNK2_ROUNDS 6   // ... 2 while more than this many are left, then 1 (0 0: always single tickets)
 #endif
 
 #ifndef RT_PATCH_W
