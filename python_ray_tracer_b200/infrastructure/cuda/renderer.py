@@ -80,21 +80,34 @@ class CameraRays(NumpyVector3D):
 
 
 class DeviceColor(NumpyRGBColor):
-    """Colour result living on the GPU: planar linear RGB ``[3, n]`` (+ optional RGBA8).
+    """Colour result living on the GPU: planar linear RGB ``[3, n]`` and/or the 8-bit image.
 
     ``x``/``y``/``z`` are NumPy views of one device-to-host copy, made on first access,
     so the object reads like the reference's ``NumpyRGBColor`` of flat arrays
-    (``base.py:119-121``).
+    (``base.py:119-121``).  When ``raytrace_scene`` was handed the renderer's own
+    ``CameraRays`` it renders only the 8-bit image ``save_image`` needs
+    (``rgba8``, here ``[n, 3]``) and keeps a recipe for the linear planes: they are rendered
+    if and when somebody reads them (``render_image_pipeline`` never does,
+    ``application.py:43-52``).
     """
 
-    __slots__ = ("planes", "rgba8", "stats", "device", "_host")
+    __slots__ = ("_planes", "rgba8", "stats", "device", "_host", "_render_planes")
 
-    def __init__(self, planes, rgba8=None, stats=None, device: int = 0) -> None:
-        self.planes = planes  # torch tensor [3, n] float32/float64 on the device
-        self.rgba8 = rgba8  # torch tensor [n, 4] uint8 on the device, or None
+    def __init__(self, planes, rgba8=None, stats=None, device: int = 0, render_planes=None) -> None:
+        self._planes = planes  # torch tensor [3, n] float32/float64 on the device, or None (lazy)
+        self.rgba8 = rgba8  # torch tensor [n, 4] or [n, 3] uint8 on the device, or None
         self.stats = stats  # torch tensor [4] int64 on the device, or None
         self.device = device
         self._host = None
+        self._render_planes = render_planes
+
+    @property
+    def planes(self):
+        if self._planes is None:
+            if self._render_planes is None:
+                raise RuntimeError("this colour holds no linear planes")
+            self._planes = self._render_planes()
+        return self._planes
 
     def numpy(self) -> np.ndarray:
         if self._host is None:
@@ -113,6 +126,26 @@ class DeviceColor(NumpyRGBColor):
         return {"rays_traced": traced, "hits_shaded": hits, "generations": deepest, "sphere_tests": tests}
 
 
+class _Nvtx:
+    """NVTX range around one stage (upload, kernel, download, encode): shows up in Nsight timelines."""
+
+    def __init__(self, name: str) -> None:
+        self.name = name
+
+    def __enter__(self):
+        try:
+            _torch().cuda.nvtx.range_push(self.name)
+            self.on = True
+        except Exception:  # no CUDA runtime: describing scenes must still work
+            self.on = False
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            _torch().cuda.nvtx.range_pop()
+        return False
+
+
 class CudaRenderer(Renderer):
     """``Renderer`` port on one B200 (``cuda:device``).
 
@@ -129,9 +162,11 @@ class CudaRenderer(Renderer):
     ``all_point_lights``  extension (``main.py:45`` TODO): shade with every point light.
     ``output_dtype``  ``"float64"`` (default, the reference's dtype) or ``"float32"``.
     ``collect_stats``  count rays / hits / generations / sphere tests per launch.
-    ``png_compress_level``  zlib level of ``save_image``'s PNG (6 = Pillow's default, what the
-                   reference writes); ``None`` = the library's own deflate (``rt_png_deflate_rows``,
-                   ~6x faster than level 6 at about the same size).  Decoded pixels do not depend on it.
+    ``png_compress_level``  ``None`` (default) = the library's own deflate (``rt_png_deflate_rows``, row
+                   bands on ``png_threads`` threads); an integer = that zlib level (6 = Pillow's
+                   default, byte-for-byte the kind of file the reference writes, ~30x slower).
+                   Decoded pixels do not depend on it.
+    ``png_threads``  threads ``save_image`` deflates with (default: up to 8 of the host's cores).
     ``accel``      ``"auto"`` (default): scenes of at least ``ACCEL_MIN_SPHERES`` shapes get a
                    bounding-volume tree (``rt_accel_build_host``) so rays skip sphere tests
                    that provably miss; ``True`` / ``False`` force it on or off.  Results do
@@ -155,7 +190,8 @@ class CudaRenderer(Renderer):
         output_dtype: str = "float64",
         collect_stats: bool = False,
         device: int = 0,
-        png_compress_level: Optional[int] = 6,
+        png_compress_level: Optional[int] = None,
+        png_threads: Optional[int] = None,
         accel: Any = "auto",
     ) -> None:
         if precision not in _PRECISIONS:
@@ -181,6 +217,19 @@ class CudaRenderer(Renderer):
         self.collect_stats = bool(collect_stats)
         self.device = int(device)
         self.png_compress_level = None if png_compress_level is None else int(png_compress_level)
+        if png_threads is None:
+            import os
+
+            try:
+                png_threads = len(os.sched_getaffinity(0))
+            except AttributeError:
+                png_threads = os.cpu_count() or 1
+            png_threads = min(8, png_threads)
+        self.png_threads = max(1, int(png_threads))
+        self._png_pool = None
+        self._rgb8_dev = None     # reused across frames: the 8-bit image on the device ...
+        self._rgb8_pinned = None  # ... and its pinned landing zone on the host
+        self.last_timing: Dict[str, float] = {}
         if accel not in ("auto", True, False):
             raise ValueError("accel must be 'auto', True or False")
         self.accel = accel
@@ -220,7 +269,9 @@ class CudaRenderer(Renderer):
         """Device copies of the sphere SoA and the point-light table (cached by content)."""
         torch = _require_cuda(self.device)
         key = flat.key()
-        if key != self._scene_key or self._scene_dev is None:
+        if key == self._scene_key and self._scene_dev is not None:
+            return self._scene_dev
+        with _Nvtx("rt: scene upload"):
             dev = torch.device("cuda", self.device)
             spheres = torch.from_numpy(flat.spheres).to(dev, non_blocking=False)
             lights = torch.from_numpy(flat.point_lights).to(dev, non_blocking=False)
@@ -278,7 +329,7 @@ class CudaRenderer(Renderer):
         return CameraRays(self, camera, row0, row1)
 
     def render_rows(self, flat: FlatScene, camera: Camera, row0: int, row1: int, *, planes=None,
-                    rgba8=None, want_rgba8: bool = False, flags: int = 0) -> DeviceColor:
+                    rgba8=None, want_rgba8: bool = False, flags: int = 0, no_planes: bool = False) -> DeviceColor:
         """Launch the camera-ray kernel for rows ``[row0, row1)`` into (optionally
         caller-supplied) device buffers.  ``flags``: launch options of ``include/rt_abi.h``
         (``RT_FLAG_WIDE_STORES``: 32x1 patches; ``RT_FLAG_RGB8``: the 8-bit image has 3 bytes per
@@ -289,7 +340,7 @@ class CudaRenderer(Renderer):
         dev = torch.device("cuda", self.device)
         spheres, lights = self.upload_scene(flat)
         n = (row1 - row0) * int(camera.width)
-        if planes is None:
+        if planes is None and not no_planes:
             planes = torch.empty((3, n), dtype=self._torch_dtype(), device=dev)
         if rgba8 is None and want_rgba8:
             rgba8 = torch.empty((n, 3 if flags & abi.RT_FLAG_RGB8 else 4), dtype=torch.uint8, device=dev)
@@ -299,7 +350,8 @@ class CudaRenderer(Renderer):
         abi.check(
             lib.rt_render_rows_dev(
                 self.device, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env), C.byref(cam),
-                row0, row1, planes.data_ptr(), self._abi_dtype(), planes.stride(0),
+                row0, row1, None if planes is None else planes.data_ptr(), self._abi_dtype(),
+                max(n, 1) if planes is None else planes.stride(0),
                 None if rgba8 is None else rgba8.data_ptr(), None if stats is None else stats.data_ptr(),
                 self._stream(),
             ),
@@ -380,14 +432,32 @@ class CudaRenderer(Renderer):
 
     def raytrace_scene(self, ray_origin: Any, normalized_ray_direction: Any, scene: Scene3D) -> DeviceColor:
         """Colour of every ray (``base.py:91-121`` with every ``NumpyShader.create`` it
-        triggers, ``shader.py:63-112``)."""
+        triggers, ``shader.py:63-112``).
+
+        Handed the renderer's own ``CameraRays`` (what ``render_image_pipeline`` does,
+        ``application.py:48-50``) it launches the camera kernel for the 8-bit image only -- into a
+        device buffer reused across frames -- and renders the linear planes the first time
+        ``.x/.y/.z`` is read; explicit arrays go through ``trace_rays``."""
         flat = self.flatten(scene)
         rays = normalized_ray_direction
         if isinstance(rays, CameraRays):
             origin = as_float_triple(ray_origin, "ray origin")
-            if origin == as_float_triple(rays.camera.position, "camera position"):
-                return self.render_rows(flat, rays.camera, rays.row0, rays.row1, want_rgba8=True)
+            # the camera kernel takes "towards the camera" (shader.py:76) from the ray itself: camera rays
+            # that do not start at scene.camera.position are traced as explicit rays
+            if origin == as_float_triple(rays.camera.position, "camera position") == tuple(flat.eye):
+                return self._render_camera_lazy(flat, rays)
         return self.trace_rays(flat, ray_origin, rays)
+
+    def _render_camera_lazy(self, flat: FlatScene, rays: "CameraRays") -> DeviceColor:
+        torch = _require_cuda(self.device)
+        camera, row0, row1 = rays.camera, rays.row0, rays.row1
+        n = (row1 - row0) * int(camera.width)
+        if self._rgb8_dev is None or self._rgb8_dev.shape[0] != n:
+            self._rgb8_dev = torch.empty((n, 3), dtype=torch.uint8, device=torch.device("cuda", self.device))
+        with _Nvtx("rt: trace kernel (8-bit image)"):
+            color = self.render_rows(flat, camera, row0, row1, rgba8=self._rgb8_dev, flags=abi.RT_FLAG_RGB8, no_planes=True)
+        color._render_planes = lambda: self.render_rows(flat, camera, row0, row1).planes
+        return color
 
     def trace_rays(self, flat: FlatScene, ray_origin: Any, directions: Any) -> DeviceColor:
         """Explicit ray batch: ``directions`` has flat ``x, y, z`` arrays; ``ray_origin`` is
@@ -445,15 +515,42 @@ class CudaRenderer(Renderer):
 
     def save_image(self, color: Any, camera: Camera, output_path: Path) -> None:
         """Quantise and write the PNG (``base.py:143-151``).  A frame in which no ray hit
-        anything is written black (the reference raises on it)."""
+        anything is written black (the reference raises on it).
+
+        The 8-bit image comes from the trace kernel's fused quantisation when ``color`` carries it,
+        through ``rt_quantize_dev`` otherwise; it lands in a pinned buffer reused across frames and is
+        deflated in row bands on ``png_threads`` threads.  ``last_timing`` holds the stage times (ms)."""
+        import time
+
+        torch = _require_cuda(self.device)
         width, height = int(camera.width), int(camera.height)
-        if isinstance(color, DeviceColor) and color.rgba8 is not None:
-            rgb8 = color.rgba8[:, :3].contiguous().cpu().numpy()
-        else:
-            rgb8 = self.quantize(color, 3).cpu().numpy()
-        if rgb8.shape[0] != width * height:
-            raise ValueError(f"colour has {rgb8.shape[0]} pixels, camera is {width}x{height}")
-        write_png(Path(output_path), rgb8.reshape(height, width, 3), self.png_compress_level)
+        t0 = time.perf_counter()
+        with _Nvtx("rt: 8-bit image to host"):
+            if isinstance(color, DeviceColor) and color.rgba8 is not None:
+                dev8 = color.rgba8
+            else:
+                dev8 = self.quantize(color, 3)
+            if dev8.shape[0] != width * height:
+                raise ValueError(f"colour has {dev8.shape[0]} pixels, camera is {width}x{height}")
+            channels = int(dev8.shape[1])
+            if self._rgb8_pinned is None or tuple(self._rgb8_pinned.shape) != (width * height, channels):
+                self._rgb8_pinned = torch.empty((width * height, channels), dtype=torch.uint8).pin_memory()
+            self._rgb8_pinned.copy_(dev8, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()  # the kernel and the copy
+        t1 = time.perf_counter()
+        with _Nvtx("rt: PNG encode + write"):
+            if self._png_pool is None and self.png_threads > 1:
+                from concurrent.futures import ThreadPoolExecutor
+
+                self._png_pool = ThreadPoolExecutor(self.png_threads)
+            pixels = self._rgb8_pinned.numpy().reshape(height, width, channels)
+            if channels == 4 and self.png_compress_level is not None:
+                pixels = pixels[:, :, :3]
+            write_png(Path(output_path), pixels, self.png_compress_level, self.png_threads, self._png_pool)
+        t2 = time.perf_counter()
+        self.last_timing = {"kernel_and_d2h_ms": (t1 - t0) * 1e3, "png_ms": (t2 - t1) * 1e3,
+                            "encoder": "rt_png_deflate_rows x%d threads" % self.png_threads if self.png_compress_level is None
+                            else "zlib level %d x%d threads" % (self.png_compress_level, self.png_threads)}
 
 
 def sphere_distance(sphere: Any, ray_origin: Any, normalized_ray_direction: Any, *, device: int = 0,

@@ -58,15 +58,39 @@ class FlatScene:
     def n_spheres(self) -> int:
         return int(self.spheres.shape[1])
 
-    def key(self) -> bytes:
-        """Content key used to skip re-uploading an unchanged scene."""
-        return b"|".join(
-            (
-                self.spheres.tobytes(),
-                self.point_lights.tobytes(),
-                np.asarray(self.eye + self.dome_color + tuple(self.dome_intensity)).tobytes(),
-            )
+    def key(self) -> tuple:
+        """Content key used to skip re-uploading an unchanged scene: a 64-bit multilinear
+        fingerprint of the tables (one vectorised pass, no copy of the table) plus the small
+        values themselves."""
+        cached = self.__dict__.get("_key")
+        if cached is None:
+            cached = self.__dict__["_key"] = self._make_key()
+        return cached
+
+    def _make_key(self) -> tuple:
+        return (
+            self.spheres.shape,
+            _fingerprint(self.spheres),
+            self.point_lights.shape,
+            _fingerprint(self.point_lights),
+            tuple(self.eye),
+            tuple(self.dome_color),
+            tuple(self.dome_intensity),
         )
+
+
+_WEIGHTS: Dict[int, np.ndarray] = {}
+
+
+def _fingerprint(table: np.ndarray) -> int:
+    """sum_i bits_i * w_i mod 2^64 with fixed odd random w_i: changes with any single entry and,
+    with probability 1 - 2^-63, with any set of entries."""
+    bits = np.ascontiguousarray(table, dtype=np.float64).reshape(-1).view(np.uint64)
+    w = _WEIGHTS.get(bits.size)
+    if w is None:
+        w = _WEIGHTS[bits.size] = np.random.default_rng(0x5EED).integers(0, 2**63, bits.size, dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+    with np.errstate(over="ignore"):
+        return int((bits * w).sum(dtype=np.uint64))
 
 
 def _is_shader(obj: Any) -> bool:

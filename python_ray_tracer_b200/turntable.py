@@ -40,14 +40,28 @@ def frame_path(out_dir: Path, frame: int) -> Path:
 
 def encode_frame(rgba: np.ndarray, width: int, height: int, compress_level: Optional[int] = None, bands: int = 2,
                  pool=None) -> bytes:
-    """PNG bytes of one frame as it comes off the GPU (``[n, 4]`` RGBA8, row-major).
+    """PNG bytes of one frame as it comes off the GPU (``[n, 3]`` RGB8 or ``[n, 4]`` RGBA8, row-major).
     ``compress_level=None``: the library's own deflate (``rt_png_deflate_rows``, about four times
     faster than zlib level 1 on rendered frames and smaller; alpha dropped inside the encoder);
     an integer: zlib at that level.  Decoded pixels are the same either way."""
+    channels = rgba.shape[-1]
     if compress_level is None:
-        return encode_png_fast(rgba.reshape(height, width, 4), bands, pool)
-    rgb8 = np.ascontiguousarray(rgba[:, :3]).reshape(height, width, 3)
+        return encode_png_fast(rgba.reshape(height, width, channels), bands, pool)
+    rgb8 = np.ascontiguousarray(rgba.reshape(-1, channels)[:, :3]).reshape(height, width, 3)
     return encode_png_parallel(rgb8, compress_level, bands, pool)
+
+
+def frames_to_render(out_dir: Path, n_frames: int, rank: int = 0, world: int = 1, resume: bool = True) -> list:
+    """This rank's frames that still have to be rendered.  A frame is done when its final name
+    exists: frames are written to ``frame_NNNN.png.tmp`` and renamed, so a run that was killed
+    mid-write (or whose encoder raised) leaves no truncated ``frame_NNNN.png`` behind for the next
+    resume to count as done.  Stale ``.tmp`` files of this rank's frames are removed."""
+    mine = list(frames_of_rank(n_frames, world, rank))
+    for k in mine:
+        stale = frame_path(out_dir, k).with_suffix(".png.tmp")
+        if stale.exists():
+            stale.unlink()
+    return [k for k in mine if not (resume and frame_path(out_dir, k).exists())]
 
 
 def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: int, out_dir: Path, *,
@@ -64,7 +78,7 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
     out_dir = Path(out_dir)
     out_dir.mkdir(parents=True, exist_ok=True)
     device = renderer.device
-    todo = [k for k in frames_of_rank(n_frames, world, rank) if not (resume and frame_path(out_dir, k).exists())]
+    todo = frames_to_render(out_dir, n_frames, rank, world, resume)
     threads = encoder_threads or max(1, min(len(os.sched_getaffinity(0)), (os.cpu_count() or 2) // max(1, world)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 2) // max(1, world))
     stats = {"frames": 0, "skipped": len(list(frames_of_rank(n_frames, world, rank))) - len(todo),
              "wall_s": 0.0, "gpu_s": 0.0, "encode_s": 0.0, "encoder_threads": threads}
@@ -77,13 +91,15 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
     width, height = int(first.width), int(first.height)
     n = width * height
     dev = torch.device("cuda", device)
-    # two frames in flight: device RGBA8 + linear planes (the kernel's other output) and pinned host copies
+    # two frames in flight: the device 8-bit image (3 bytes per pixel, what save_image hands to its
+    # encoder, base.py:143-151; no linear planes are written) and its pinned host copy
+    from .infrastructure.cuda import abi
+
     slots = []
     for _ in range(2):
         slots.append({
-            "planes": torch.empty((3, n), dtype=renderer._torch_dtype(), device=dev),
-            "rgba8": torch.empty((n, 4), dtype=torch.uint8, device=dev),
-            "host": torch.empty((n, 4), dtype=torch.uint8).pin_memory(),
+            "rgba8": torch.empty((n, 3), dtype=torch.uint8, device=dev),
+            "host": torch.empty((n, 3), dtype=torch.uint8).pin_memory(),
             "rendered": torch.cuda.Event(enable_timing=True), "started": torch.cuda.Event(enable_timing=True),
             "copied": torch.cuda.Event(), "frame": None, "pending": None,
         })
@@ -91,7 +107,10 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
     def encode_and_write(frame: int, rgba: np.ndarray) -> float:
         t0 = time.perf_counter()
         data = encode_frame(rgba, width, height, compress_level, bands_per_frame, band_pool)  # off the main thread
-        frame_path(out_dir, frame).write_bytes(data)
+        final = frame_path(out_dir, frame)
+        partial = final.with_suffix(".png.tmp")
+        partial.write_bytes(data)
+        os.replace(partial, final)  # atomic within the directory
         return time.perf_counter() - t0
 
     def retire(slot) -> None:
@@ -116,7 +135,7 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
             scene = scene_of_frame(frame)
             flat = renderer.flatten(scene)
             slot["started"].record(render_stream)
-            renderer.render_rows(flat, scene.camera, 0, height, planes=slot["planes"], rgba8=slot["rgba8"])
+            renderer.render_rows(flat, scene.camera, 0, height, rgba8=slot["rgba8"], flags=abi.RT_FLAG_RGB8, no_planes=True)
             slot["rendered"].record(render_stream)
             copy_stream.wait_event(slot["rendered"])
             with torch.cuda.stream(copy_stream):
@@ -125,9 +144,15 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
             slot["frame"] = frame
         for slot in slots:
             retire(slot)
-        for f in futures:
-            stats["encode_s"] += f.result()
-            stats["frames"] += 1
+        failed = None
+        for f in futures:  # every frame that can be written is written before an encoder error surfaces
+            try:
+                stats["encode_s"] += f.result()
+                stats["frames"] += 1
+            except Exception as exc:  # noqa: BLE001 -- re-raised below
+                failed = failed or exc
+        if failed is not None:
+            raise failed
     stats["wall_s"] = time.perf_counter() - wall0
     return stats
 

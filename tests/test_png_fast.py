@@ -170,5 +170,20 @@ def test_write_png_with_the_library_deflate(tmp_path):
     assert np.array_equal(png.read_png(tmp_path / "zlib.png"), img)
     from python_ray_tracer_b200.infrastructure import CudaRenderer
 
-    assert CudaRenderer(png_compress_level=None).png_compress_level is None
-    assert CudaRenderer().png_compress_level == 6
+    assert CudaRenderer().png_compress_level is None  # the library's deflate is save_image's default
+    assert CudaRenderer(png_compress_level=6).png_compress_level == 6
+
+
+def test_turntable_resume_ignores_partial_frames(tmp_path):
+    """Resume counts a frame as done only under its final name: a leftover ``.png.tmp`` (a run killed
+    mid-write) is deleted and its frame rendered again; finished frames are skipped."""
+    from python_ray_tracer_b200 import turntable
+
+    turntable.frame_path(tmp_path, 0).write_bytes(b"done")
+    turntable.frame_path(tmp_path, 2).with_suffix(".png.tmp").write_bytes(b"\x89PNG truncated")
+    turntable.frame_path(tmp_path, 3).write_bytes(b"done")
+    turntable.frame_path(tmp_path, 3).with_suffix(".png.tmp").write_bytes(b"stale")
+    assert turntable.frames_to_render(tmp_path, 5) == [1, 2, 4]
+    assert not list(tmp_path.glob("*.tmp"))
+    assert turntable.frames_to_render(tmp_path, 5, resume=False) == [0, 1, 2, 3, 4]
+    assert turntable.frames_to_render(tmp_path, 5, rank=1, world=2) == [1]
