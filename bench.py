@@ -2,20 +2,26 @@
 """Benchmark of the hot path: ``NumpyRenderer.raytrace_scene`` replaced by the sm_100a trace kernel.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
-                    [--workload c2|c3|c4|c5] [--precision fast|exact]
+                    [--workload c2|c1|c3|c4|c5] [--precision fast|exact]
 
 A step is one frame of the workload through the hot path (camera rays -> nearest hit ->
 shadow ray -> shading -> bounce chain -> framebuffer stores).  The default workload is
 BASELINE.json's ``configs[1]`` (README scene, 1920x1080, all effects); with N > 1 every rank
-renders its own frame of the turntable (``configs[4]``: frame-sharded, no data-path
-collective, weak scaling).  ``--workload c4`` is the 8K row-band configuration with an NCCL
-gather of the bands to rank 0.  One JSON line is printed by rank 0.
+renders its own such frame per step (frame-sharded, no data-path collective, weak scaling).
+One JSON line is printed by rank 0.  Besides the contract's keys it carries
+
+  ``c4``        BASELINE configs[3]: ONE 7680x4320 frame over the N ranks (interleaved 16-row strips, the
+                kernels store the 8-bit frame into rank 0's framebuffer over NVLink peer memory), with
+                the same frame on rank 0 alone timed beside it and the two frames compared;
+  ``pipeline``  ``render_image_pipeline(scene, path, CudaRenderer())`` at 1080p, PNG written, on rank 0;
+  ``c3``        BASELINE configs[2] (1 025 shapes, 4K, depth 8) through the sphere tree, rank 0, N = 1.
 
 Metric: Mrays/s = primary rays (= pixels) per second / 1e6; ``ms_per_step`` is ms/frame.
 ``value`` is device time with the scene resident in HBM (CUDA events on the launch stream,
-L2 flushed between steps, max over ranks); ``e2e`` is the same frame through the host-buffer
-C-ABI entry point (``rt_render_frame_host``): scene upload, kernel, linear RGB + 8-bit image
-copied back into pinned host memory, every step.
+L2 flushed between steps, max over ranks).  ``e2e`` is the same frame through the host-buffer
+C-ABI entry point ``rt_render_frame_host``: scene upload, kernel, and the 8-bit image
+``save_image`` consumes (base.py:143-151) copied into pinned host memory, every step; the figure
+with the linear float planes copied back instead is reported beside it.
 """
 
 from __future__ import annotations
@@ -25,6 +31,7 @@ import ctypes as C
 import json
 import os
 import sys
+import tempfile
 import threading
 import time
 from pathlib import Path
@@ -46,34 +53,49 @@ README_DEFAULT = DefaultMaterial(**scenes.README_GAINS)
 FLOP_PER_SPHERE_TEST = 24.0   # one ray/sphere quadratic
 FLOP_PER_HIT = 280.0          # NumpyShader.create without its S shadow tests
 BYTES_PER_PIXEL = 12.0 + 4.0  # planar f32 RGB + RGBA8, each written once
-# dram__bytes_read.sum + dram__bytes_write.sum per launch, one `ncu --set full` capture per workload
-# (profiles/r01/*_details.txt); None where no capture was taken
-NCU_DRAM_BYTES_PER_LAUNCH = {"c2": 639488}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from this round's
+# `ncu --set full` captures: profiles/r02/ncu_traffic.json names the capture each figure comes from
+TRAFFIC_FILE = ROOT / "profiles" / "r02" / "ncu_traffic.json"
+
+
+def scene_of(name: str, rank: int = 0, step: int = 0, world: int = 1):
+    """(Scene3D, width, height, max_depth) of one step on one rank."""
+    if name == "c2":
+        return scenes.readme_scene(1920, 1080), 1920, 1080, 0
+    if name == "c5":
+        return scenes.turntable_scene((step * world + rank) % 256, 256, 1920, 1080), 1920, 1080, 0
+    if name == "c3":
+        return scenes.random_spheres_scene(3840, 2160), 3840, 2160, 8
+    if name == "c4":
+        return scenes.readme_scene(7680, 4320), 7680, 4320, 0
+    if name == "c1":
+        return scenes.readme_scene(960, 540), 960, 540, 0
+    raise SystemExit(f"unknown workload {name}")
+
+
+LABELS = {
+    "c1": "README scene 960x540 (configs[0])",
+    "c2": "README scene 1920x1080, all effects (configs[1])",
+    "c3": "1024 random spheres + checkered ground, 4 PointLights (reference semantics: light 0 shades), depth 8, 3840x2160 (configs[2])",
+    "c4": "README scene 7680x4320, one frame row-band sharded over the ranks, assembled on rank 0 (configs[3])",
+    "c5": "256-frame turntable of the README scene at 1080p, frame-sharded (configs[4])",
+}
 
 
 def workload(name: str, rank: int, step: int, world: int):
     """(label, flat scene, width, height, max_depth) of one step on one rank."""
-    if name == "c2":
-        # N > 1: a batch of N frames of configs[1] per step, one per rank (frame-sharded, nothing
-        # exchanged): per-GPU work is exactly the N = 1 work, which is what weak scaling compares.
-        # (Turntable frames differ in cost by +-20 %; that batch is workload c5.)
-        label = "README scene 1920x1080, all effects (configs[1])"
-        if world > 1:
-            label += "; batch of %d such frames per step, one per rank" % world
-        return label, flatten_scene(scenes.readme_scene(1920, 1080), README_DEFAULT), 1920, 1080, 0
-    if name == "c5":
-        frame = (step * world + rank) % 256
-        return ("256-frame turntable of the README scene at 1080p, frame-sharded (configs[4])",
-                flatten_scene(scenes.turntable_scene(frame, 256, 1920, 1080), README_DEFAULT), 1920, 1080, 0)
-    if name == "c3":
-        return ("1024 random spheres + checkered ground, 4 PointLights (reference semantics: light 0 shades), depth 8, 3840x2160 (configs[2])",
-                flatten_scene(scenes.random_spheres_scene(3840, 2160), README_DEFAULT), 3840, 2160, 8)
-    if name == "c4":
-        return ("README scene 7680x4320, row-band sharded with gather to rank 0 (configs[3])",
-                flatten_scene(scenes.readme_scene(7680, 4320), README_DEFAULT), 7680, 4320, 0)
-    if name == "c1":
-        return "README scene 960x540 (configs[0])", flatten_scene(scenes.readme_scene(960, 540), README_DEFAULT), 960, 540, 0
-    raise SystemExit(f"unknown workload {name}")
+    scene, width, height, max_depth = scene_of(name, rank, step, world)
+    return LABELS[name], flatten_scene(scene, README_DEFAULT), width, height, max_depth
+
+
+def config_of(name: str, world: int) -> dict:
+    """The configuration BOTH arms measure (the reference arm prints the same object)."""
+    _, width, height, max_depth = scene_of(name)
+    flat = workload(name, 0, 0, 1)[1]
+    return {"workload": LABELS[name], "width": width, "height": height, "spheres": flat.n_spheres,
+            "max_depth": max_depth or None,
+            "frames_per_step": 1 if name == "c4" else world,
+            "sharding": ("one frame over %d rank(s)" % world) if name == "c4" else ("one frame per rank per step, %d rank(s)" % world)}
 
 
 class ClockSampler(threading.Thread):
@@ -81,7 +103,7 @@ class ClockSampler(threading.Thread):
 
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index: int, period: float = 0.002) -> None:
+    def __init__(self, index: int, period: float = 0.001) -> None:
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
@@ -116,11 +138,17 @@ class ClockSampler(threading.Thread):
             self.sample()
             self._stop_event.wait(self.period)
 
-    def finish(self) -> dict:
+    def mark(self) -> int:
+        return len(self.samples)
+
+    def summary(self, first: int = 0, last=None) -> dict:
+        window = self.samples[first:last]
+        return {"sm_mhz": int(np.median(window)) if window else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(window)}
+
+    def finish(self) -> None:
         self._stop_event.set()
         self.join(timeout=2.0)
-        med = int(np.median(self.samples)) if self.samples else None
-        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
 def measured_peaks() -> dict:
@@ -131,16 +159,27 @@ def measured_peaks() -> dict:
     return {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def ncu_traffic(name: str):
+    if TRAFFIC_FILE.exists():
+        entry = json.loads(TRAFFIC_FILE.read_text()).get(name)
+        if entry:
+            return entry.get("dram_bytes_per_launch"), entry.get("capture")
+    return None, None
+
+
 # --------------------------------------------------------------------------------------
 # CPU legs (the only places bench.py executes oracle/ code: as the timed baseline)
 # --------------------------------------------------------------------------------------
 def _rows_job(args):
-    flat, width, height, rows, max_depth = args
+    flat, width, height, rows, max_depth, repeats = args
     from oracle import numpy_port
 
     pixels = (rows[:, None] * width + np.arange(width)[None, :]).reshape(-1)
-    rgb, counters = numpy_port.render(flat, width, height, pixels=pixels, max_depth=max_depth)
-    return float(rgb.sum()), counters[0]
+    total = 0.0
+    for _ in range(repeats):
+        rgb, counters = numpy_port.render(flat, width, height, pixels=pixels, max_depth=max_depth)
+        total += float(rgb.sum())
+    return total, counters[0]
 
 
 def sample_rows(height: int, rows_wanted: int) -> np.ndarray:
@@ -183,36 +222,47 @@ def cpu_single_core(flat, width, height, max_depth, budget_s: float = 20.0) -> d
 def run_reference_arm(args) -> None:
     """``--impl reference``: the reference's CPU algorithm (NumPy port; the reference tree
     itself does not exist on the GPU box) on every host core: the frame is cut into row
-    bands (bit-identical to the full frame) and rendered by a process pool."""
+    bands (bit-identical to the full frame) and rendered by a process pool.  A step is the
+    whole frame rendered ``repeats`` times, sized so that a step takes about 2.5 s (the
+    single-frame steps of round 1 took 0.12 s and their rate moved by +-15 % from run to run)
+    and the whole run a few minutes."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import multiprocessing as mp
 
-    label, flat, width, height, max_depth = workload(args.workload, 0, 0, max(1, args.gpus))
+    world = max(1, args.gpus)
+    label, flat, width, height, max_depth = workload(args.workload, 0, 0, world)
     cores = host_cores()
-    # bounded sample: evenly spaced rows sized for ~2 s per step per core at ~0.4 Mpx/s/core
+    # rows: the whole frame when the scene is small enough, evenly spaced rows otherwise
     target_px = int(min(width * height, 0.4e6 * 2.0 * cores / max(1.0, flat.n_spheres / 3.0) ** 2))
     rows = sample_rows(height, max(cores, min(height, target_px // width)))
-    jobs = [(flat, width, height, rows[j::cores], max_depth) for j in range(cores) if len(rows[j::cores])]
     n = width * len(rows)
-    times = []
+    total_steps = args.warmup + args.steps
+    step_budget = min(3.0, max(0.5, 150.0 / max(1, total_steps)))
     with mp.get_context("fork").Pool(cores) as pool:
-        for step in range(args.warmup + args.steps):
+        jobs = [(flat, width, height, rows[j::cores], max_depth, 1) for j in range(cores) if len(rows[j::cores])]
+        t0 = time.perf_counter()
+        pool.map(_rows_job, jobs, chunksize=1)  # calibration (untimed): one pass over the sample
+        once = time.perf_counter() - t0
+        repeats = max(1, int(round(step_budget / max(once, 1e-3))))
+        jobs = [j[:5] + (repeats,) for j in jobs]
+        times = []
+        for step in range(total_steps):
             t0 = time.perf_counter()
             pool.map(_rows_job, jobs, chunksize=1)
             dt = time.perf_counter() - t0
             if step >= args.warmup:
                 times.append(dt)
     sec = float(np.mean(times))
-    value = n / sec / 1e6
-    sample = (f"{len(rows)} evenly spaced rows of {width}x{height} ({n} pixels) per step, interleaved over {len(jobs)} processes; "
+    value = n * repeats / sec / 1e6
+    sample = (f"{repeats} x {len(rows)} evenly spaced rows of {width}x{height} ({n} pixels) per step, interleaved over {len(jobs)} processes; "
               "oracle/numpy_port.py = the reference's whole-array NumPy algorithm on the flattened scene")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "ms_per_frame_extrapolated": width * height / (value * 1e6) * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": label, "width": width, "height": height, "spheres": flat.n_spheres},
+        "config": config_of(args.workload, world),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -222,256 +272,420 @@ def run_reference_arm(args) -> None:
 # --------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------
-def run_b200_arm(args) -> None:
-    import torch
-    import torch.distributed as dist
+class Gpu:
+    """What every part of the GPU arm needs: the library, this rank's device and stream."""
 
-    from python_ray_tracer_b200.infrastructure.cuda import abi, affinity, sharding
+    def __init__(self, args) -> None:
+        import torch
+        import torch.distributed as dist
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    bound = affinity.bind_to_device(local) if world > 1 else None  # pinned buffers next to this rank's GPU
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    lib = abi.load()
-    stream = torch.cuda.current_stream(local)
-    sptr = int(stream.cuda_stream)
-    mode = abi.RT_MODE_FAST if args.precision == "fast" else abi.RT_MODE_EXACT
-    banded = args.workload == "c4"  # one frame over all ranks (N = 1 included: same output format)
+        from python_ray_tracer_b200.infrastructure.cuda import abi, affinity, sharding
 
+        self.torch, self.dist, self.abi, self.sharding = torch, dist, abi, sharding
+        self.args = args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.bound = affinity.bind_to_device(self.local) if self.world > 1 else None  # pinned buffers next to this rank's GPU
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.lib = abi.load()
+        self.stream = torch.cuda.current_stream(self.local)
+        self.sptr = int(self.stream.cuda_stream)
+        self.mode = abi.RT_MODE_FAST if args.precision == "fast" else abi.RT_MODE_EXACT
+        self.flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=self.dev)  # > 126 MB L2
+        self.launches = 0  # kernels of librt_b200.so launched inside timed regions
+
+    def barrier(self) -> None:
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.local)
+
+    def max_over_ranks(self, value: float) -> float:
+        t = self.torch.tensor([float(value)], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def gather_floats(self, value: float) -> list:
+        t = self.torch.tensor([float(value)], dtype=self.torch.float64, device=self.dev)
+        if self.world == 1:
+            return [float(value)]
+        out = [self.torch.zeros_like(t) for _ in range(self.world)]
+        self.dist.all_gather(out, t)
+        return [float(v.item()) for v in out]
+
+    def env_of(self, flat, max_depth, flags=0):
+        abi = self.abi
+        return abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, max_depth=max_depth,
+                            mode=self.mode, cutoff=self.args.cutoff if self.mode == abi.RT_MODE_FAST else 0.0, flags=flags,
+                            spheres_host=flat.spheres, point_lights_host=flat.point_lights)
+
+    def tree_of(self, flat, env):
+        """rt_accel_build_host + upload; names the blob in env.  Returns the device tensor (keep it alive)."""
+        abi, lib = self.abi, self.lib
+        capacity = int(lib.rt_accel_bytes(flat.n_spheres))
+        blob = np.empty(capacity, dtype=np.uint8)
+        used = C.c_int64(0)
+        abi.check(lib.rt_accel_build_host(flat.spheres.ctypes.data, flat.n_spheres, C.byref(env), blob.ctypes.data,
+                                          capacity, C.byref(used)), "rt_accel_build_host")
+        dev_blob = self.torch.from_numpy(blob[: used.value]).to(self.dev)
+        env.accel_dev, env.accel_bytes = dev_blob.data_ptr(), dev_blob.numel()
+        return dev_blob
+
+    def timed_steps(self, launch, steps: int, warmup: int, together: bool = False) -> np.ndarray:
+        """``warmup`` untimed launches, then ``steps`` launches each between its own CUDA event pair
+        with the L2 flushed before it; per-step ms of THIS rank.  ``together``: all ranks start each
+        step after a barrier (one frame over all ranks)."""
+        torch = self.torch
+        for s in range(warmup):
+            launch(s)
+        self.barrier()
+        events = []
+        for s in range(warmup, warmup + steps):
+            self.flush.fill_(s & 0xFF)  # evict the previous frame's lines from L2 (not timed)
+            if together and self.world > 1:
+                # a rank still flushing would compete with the others' peer stores into rank 0
+                self.dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(self.stream)
+            launch(s)
+            self.launches += 1
+            e1.record(self.stream)
+            events.append((e0, e1))
+        self.barrier()
+        return np.array([a.elapsed_time(b) for a, b in events])
+
+
+def device_frames(g: Gpu, name: str, use_tree: bool):
+    """Scene tables of every step resident in HBM, and launch(step, stats) for workload ``name``
+    (one frame per rank per step; rows_dev entry point, planar f32 + RGBA8 outputs)."""
+    torch, abi, lib, args = g.torch, g.abi, g.lib, g.args
     total = args.warmup + args.steps
-    frames = [workload(args.workload, rank, s, world) for s in range(total)]
-    label, _, width, height, max_depth = frames[0]
-    # one frame over all ranks: interleaved strips (sharding.StripShard) for the device path,
-    # contiguous bands for the host-buffer path
-    shard = sharding.StripShard(height, world, rank) if banded else None
-    row0, row1 = sharding.band_rows(height, world, rank) if banded else (0, height)
-    n = shard.n_rows * width if banded else (row1 - row0) * width
-    cam = abi.make_camera(frames[0][1].eye, width, height)
-
-    # scene tables of every step resident in HBM before the timed region
-    tables = []
-    for _, flat, _, _, _ in frames:
-        env = abi.make_env(flat.eye, len(flat.point_lights), flat.dome_intensity, flat.dome_color, max_depth=max_depth,
-                           mode=mode, cutoff=args.cutoff if mode == abi.RT_MODE_FAST else 0.0,
-                           spheres_host=flat.spheres, point_lights_host=flat.point_lights)
-        tables.append((torch.from_numpy(flat.spheres).to(dev), torch.from_numpy(flat.point_lights).to(dev), env, flat))
-    # sphere tree (rt_accel_build_host) for scenes past the measured break-even; built and
-    # uploaded before the timed region for the device path (scene-resident data), rebuilt
-    # inside the timed region by the host entry point of the e2e path
-    use_tree = args.accel == "on" or (args.accel == "auto" and frames[0][1].n_spheres >= abi.RT_ACCEL_AUTO_SPHERES)
-    blobs = {}
-    if use_tree:
-        for _, _, env, flat in tables:
-            key = flat.key()
-            if key not in blobs:
-                capacity = int(lib.rt_accel_bytes(flat.n_spheres))
-                blob = np.empty(capacity, dtype=np.uint8)
-                used = C.c_int64(0)
-                abi.check(lib.rt_accel_build_host(flat.spheres.ctypes.data, flat.n_spheres, C.byref(env), blob.ctypes.data,
-                                                  capacity, C.byref(used)), "rt_accel_build_host")
-                blobs[key] = torch.from_numpy(blob[: used.value]).to(dev)
-            env.accel_dev, env.accel_bytes = blobs[key].data_ptr(), blobs[key].numel()
-    planes = torch.empty((3, n), dtype=torch.float32, device=dev)
-    rgba8 = torch.empty((n, 4), dtype=torch.uint8, device=dev)
-    stats = torch.zeros(4, dtype=torch.int64, device=dev)
-    flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    peer = None
-    peer_layout = None
-    if banded and args.exchange == "peer":
-        # rank 0 owns the whole-frame 8-bit buffer; the other ranks map it and their kernels
-        # store into it over NVLink while they render (no gather, no permutation).  Up to four
-        # writers rank 0's port keeps up with 32-byte row segments of 8x4 patches; from eight on
-        # the frame goes out as 96-byte rows of 32x1 patches of 3-byte pixels, the patches taken
-        # from both ends of the shard (profiles/r01/c4_store_layouts.txt).
-        peer_layout = args.peer_layout if args.peer_layout != "auto" else ("rgb8-wide" if world >= 8 else "rgba8")
-        env_flags = abi.RT_FLAG_IMAGE_ORDER
-        if peer_layout == "rgb8-wide":
-            env_flags |= abi.RT_FLAG_WIDE_STORES | abi.RT_FLAG_RGB8 | abi.RT_FLAG_EVEN_STORES
-        peer = sharding.PeerFrame(height, width, rank, world, local, dst=0, channels=3 if peer_layout == "rgb8-wide" else 4)
-        for i, (sph, lig, env, flat_) in enumerate(tables):
-            env.flags |= env_flags
+    distinct = total if name == "c5" else 1
+    tables, keep = [], []
+    for s in range(distinct):
+        _, flat, width, height, max_depth = workload(name, g.rank, s, g.world)
+        env = g.env_of(flat, max_depth)
+        if use_tree:
+            keep.append(g.tree_of(flat, env))
+        tables.append((torch.from_numpy(flat.spheres).to(g.dev), torch.from_numpy(flat.point_lights).to(g.dev), env, flat))
+    n = width * height
+    cam = abi.make_camera(tables[0][3].eye, width, height)
+    planes = torch.empty((3, n), dtype=torch.float32, device=g.dev)
+    rgba8 = torch.empty((n, 4), dtype=torch.uint8, device=g.dev)
+    stats = torch.zeros(4, dtype=torch.int64, device=g.dev)
 
     def launch(step: int, with_stats: bool = False) -> None:
-        spheres, lights, env, flat = tables[step]
-        if peer is not None:
-            # the exchange step is inside the kernel: stores go to rank 0's framebuffer
-            abi.check(lib.rt_render_strips_dev(local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
-                                               C.byref(cam), shard.strip_rows, rank, world, None, abi.RT_DTYPE_F32, 0,
-                                               peer.ptr, stats.data_ptr() if with_stats else None, sptr),
-                      "rt_render_strips_dev")
-        elif banded:
-            abi.check(lib.rt_render_strips_dev(local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
-                                               C.byref(cam), shard.strip_rows, rank, world, planes.data_ptr(),
-                                               abi.RT_DTYPE_F32, n, rgba8.data_ptr(),
-                                               stats.data_ptr() if with_stats else None, sptr), "rt_render_strips_dev")
-            # the one exchange step of the path: 8-bit shards -> rank 0, permuted to image order
-            sharding.gather_frame(rgba8.view(shard.n_rows, width, 4), shard, dst=0)
-        else:
-            abi.check(lib.rt_render_rows_dev(local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
-                                             C.byref(cam), row0, row1, planes.data_ptr(), abi.RT_DTYPE_F32, n,
-                                             rgba8.data_ptr(), stats.data_ptr() if with_stats else None, sptr),
-                      "rt_render_rows_dev")
+        spheres, lights, env, flat = tables[step % distinct]
+        abi.check(lib.rt_render_rows_dev(g.local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
+                                         C.byref(cam), 0, height, planes.data_ptr(), abi.RT_DTYPE_F32, n,
+                                         rgba8.data_ptr(), stats.data_ptr() if with_stats else None, g.sptr),
+                  "rt_render_rows_dev")
 
-    def barrier() -> None:
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(local)
+    def counters() -> dict:
+        stats.zero_()
+        launch(total - 1, with_stats=True)
+        torch.cuda.synchronize(g.local)
+        traced, hits, deepest, tests = (int(v) for v in stats.cpu().tolist())
+        return {"rays_traced": traced, "hits_shaded": hits, "generations": deepest, "sphere_tests": tests}
 
-    for s in range(args.warmup):
-        launch(s)
-    barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
-    events = []
-    wall0 = time.perf_counter()
-    for s in range(args.warmup, total):
-        flush.fill_(s & 0xFF)  # evict the previous frame's lines from L2 (not timed)
-        if banded and world > 1:
-            # one frame over all ranks: start it together, after every rank's flush (a rank
-            # still flushing would compete with the others' peer stores into rank 0)
-            dist.barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        launch(s)
-        e1.record(stream)
-        events.append((e0, e1))
-    sampler.sample()
-    barrier()
-    wall = time.perf_counter() - wall0
-    clocks = sampler.finish()
-    step_ms = np.array([a.elapsed_time(b) for a, b in events])
-    mean_ms = torch.tensor([float(step_ms.mean())], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(mean_ms, op=dist.ReduceOp.MAX)
-    ms_per_step = float(mean_ms.item())
-    pixels_per_step = width * height if banded else width * height * world
-    value = pixels_per_step / (ms_per_step * 1e-3) / 1e6
+    return launch, counters, tables, cam, width, height, (planes, rgba8, keep)
 
-    # ---- work counters of one step (untimed) for the arithmetic roofline
-    stats.zero_()
-    launch(total - 1, with_stats=True)
-    torch.cuda.synchronize(local)
-    traced, hits, deepest, tests = (int(v) for v in stats.cpu().tolist())
-    flop = tests * FLOP_PER_SPHERE_TEST + hits * FLOP_PER_HIT
 
-    # ---- end to end through the host-buffer C-ABI entry point, pinned host outputs.
-    # The step's result is what raytrace_scene returns: the linear RGB planes.  A second
-    # pass also brings back the 8-bit image save_image would write (reported beside it).
-    if peer is not None:
-        torch.cuda.synchronize(local)
-        peer.close()
-        peer = None
-        for _, _, env, _ in tables:
-            env.flags &= ~(abi.RT_FLAG_IMAGE_ORDER | abi.RT_FLAG_WIDE_STORES | abi.RT_FLAG_RGB8 | abi.RT_FLAG_EVEN_STORES)
-    for _, _, env, _ in tables:  # the host entry point builds its own tree (or none: --accel off)
-        env.accel_dev, env.accel_bytes = None, 0
-        if not use_tree:
-            env.flags |= abi.RT_FLAG_NO_ACCEL
-    n_host = (row1 - row0) * width  # host path: this rank's contiguous band
-    rgb_host = torch.empty((3, n_host), dtype=torch.float32).pin_memory()
-    rgb8_host = torch.empty((n_host, 3), dtype=torch.uint8).pin_memory()
+def host_path(g: Gpu, tables, cam, width, height, use_tree: bool) -> dict:
+    """End to end through rt_render_frame_host with pinned host outputs, every step: scene upload (and the
+    tree build for large scenes), kernel, copy to the host, one value read on the host."""
+    torch, abi, lib, args = g.torch, g.abi, g.lib, g.args
+    n = width * height
+    rgb_host = torch.empty((3, n), dtype=torch.float32).pin_memory()
+    rgb8_host = torch.empty((n, 3), dtype=torch.uint8).pin_memory()
+    total = args.warmup + args.steps
+    envs = []
+    for _, _, env, flat in tables:  # the host entry point builds its own tree (or none: --accel off)
+        e = g.env_of(flat, env.max_depth, 0 if use_tree else abi.RT_FLAG_NO_ACCEL)
+        envs.append(e)
 
-    def e2e_pass(with_rgb8: bool, with_planes: bool = True) -> float:
+    def one_pass(with_rgb8: bool, with_planes: bool) -> float:
         times = []
         for s in range(total):
-            _, _, env, flat = tables[s]
+            env, flat = envs[s % len(envs)], tables[s % len(tables)][3]
             t0 = time.perf_counter()
-            abi.check(lib.rt_render_frame_host(local, flat.spheres.ctypes.data, flat.n_spheres, flat.point_lights.ctypes.data,
-                                               C.byref(env), C.byref(cam), row0, row1,
+            abi.check(lib.rt_render_frame_host(g.local, flat.spheres.ctypes.data, flat.n_spheres, flat.point_lights.ctypes.data,
+                                               C.byref(env), C.byref(cam), 0, height,
                                                rgb_host.data_ptr() if with_planes else None, abi.RT_DTYPE_F32,
                                                rgb8_host.data_ptr() if with_rgb8 else None, None), "rt_render_frame_host")
             # the result is read on the host inside the timed region
-            _ = (float(rgb_host[0, n_host // 2]) + float(rgb_host[2, n_host - 1])) if with_planes else int(rgb8_host[n_host // 2, 1])
+            _ = (float(rgb_host[0, n // 2]) + float(rgb_host[2, n - 1])) if with_planes else int(rgb8_host[n // 2, 1])
             if s >= args.warmup:
                 times.append(time.perf_counter() - t0)
-        ms = torch.tensor([float(np.mean(times)) * 1e3], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
+        return g.max_over_ranks(float(np.mean(times)) * 1e3)
 
-    e2e_ms_value = e2e_pass(False)
-    e2e_rgb8_ms = e2e_pass(True)
-    e2e_rgb8_only_ms = e2e_pass(True, with_planes=False)
-    e2e_value = pixels_per_step / (e2e_ms_value * 1e-3) / 1e6
+    rgb8_ms = one_pass(True, False)
+    planes_ms = one_pass(False, True)
+    both_ms = one_pass(True, True)
     flat = tables[-1][3]
-    h2d = flat.spheres.nbytes + flat.point_lights.nbytes
-    d2h = rgb_host.numel() * 4
+    px = width * height * g.world
+    rate = lambda ms: px / (ms * 1e-3) / 1e6  # noqa: E731
+    return {
+        "value": rate(rgb8_ms), "unit": UNIT, "ms_per_step": rgb8_ms,
+        "h2d_bytes_per_step": int(flat.spheres.nbytes + flat.point_lights.nbytes),
+        "d2h_bytes_per_step": int(rgb8_host.numel()),
+        "d2h_gb_per_s_per_gpu": rgb8_host.numel() / (rgb8_ms * 1e-3) / 1e9,
+        "host_cpus_bound": len(g.bound) if g.bound else None,
+        "api": "rt_render_frame_host(rgb8_host): scene upload + kernel (8-bit image quantised by the trace kernel, no linear "
+               "planes written) + D2H of the RGB8 image save_image consumes (base.py:143-151) into pinned host memory, row "
+               "chunks pipelined (kernel of chunk i+1 under the copy of chunk i)",
+        # what raytrace_scene returns to a caller that reads .x/.y/.z: the linear planes
+        "linear_planes_f32": {"ms_per_step": planes_ms, "value": rate(planes_ms), "d2h_bytes_per_step": int(rgb_host.numel() * 4),
+                              "d2h_gb_per_s_per_gpu": rgb_host.numel() * 4 / (planes_ms * 1e-3) / 1e9},
+        "planes_and_rgb8": {"ms_per_step": both_ms, "value": rate(both_ms),
+                            "d2h_bytes_per_step": int(rgb_host.numel() * 4 + rgb8_host.numel())},
+    }
 
+
+def pipeline_object(g: Gpu, frames: int = 8) -> dict:
+    """``render_image_pipeline(scene, path, CudaRenderer())`` at 1080p with the PNG written: the
+    reference's only timed entry point (main.py:55-57, application.py:43-52)."""
+    from python_ray_tracer_b200 import render_image_pipeline
+    from python_ray_tracer_b200.infrastructure import CudaRenderer
+
+    scene = scenes.readme_scene(1920, 1080)
+    out = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        for label, kw in (("library_deflate", {}), ("zlib6_like_pillow", {"png_compress_level": 6, "png_threads": 1})):
+            renderer = CudaRenderer(**scenes.README_GAINS, device=g.local, **kw)
+            n = frames if label == "library_deflate" else 2
+            walls, trace_d2h, png = [], [], []
+            for i in range(n + 1):
+                path = Path(tmp) / f"{label}_{i}.png"
+                t0 = time.perf_counter()
+                render_image_pipeline(scene, path, renderer)
+                dt = time.perf_counter() - t0
+                if i:  # the first call creates buffers, the pinned landing zone and the encoder pool
+                    walls.append(dt * 1e3)
+                    trace_d2h.append(renderer.last_timing["kernel_and_d2h_ms"])
+                    png.append(renderer.last_timing["png_ms"])
+            size = path.stat().st_size
+            out[label] = {"ms_per_frame": float(np.mean(walls)), "flatten_launch_kernel_d2h_ms": float(np.mean(walls) - np.mean(png)),
+                          "kernel_and_d2h_ms": float(np.mean(trace_d2h)), "png_ms": float(np.mean(png)),
+                          "encoder": renderer.last_timing["encoder"], "png_bytes": int(size), "frames": n}
+    lib_d = out["library_deflate"]
+    return {"api": "render_image_pipeline(readme_scene(1920, 1080), path, CudaRenderer(**README gains)): get_ray_directions -> "
+                   "raytrace_scene (8-bit image only, linear planes lazy) -> save_image (pinned D2H + PNG to a tmpfs file)",
+            "ms_per_frame": lib_d["ms_per_frame"], "png_ms": lib_d["png_ms"], "d2h_ms": None,
+            "kernel_ms": None, "without_png_ms": lib_d["flatten_launch_kernel_d2h_ms"], "encoder": lib_d["encoder"],
+            "variants": out}
+
+
+def c4_object(g: Gpu, steps: int, warmup: int) -> dict:
+    """BASELINE configs[3]: one 7680x4320 README frame over all ranks, assembled on rank 0."""
+    torch, abi, lib, sharding, args = g.torch, g.abi, g.lib, g.sharding, g.args
+    _, flat, width, height, max_depth = workload("c4", 0, 0, g.world)
+    world, rank = g.world, g.rank
+    layout = args.peer_layout if args.peer_layout != "auto" else ("rgb8-wide" if world >= 8 else "rgba8")
+    channels = 3 if layout == "rgb8-wide" else 4
+    flags = abi.RT_FLAG_IMAGE_ORDER | ((abi.RT_FLAG_WIDE_STORES | abi.RT_FLAG_RGB8 | abi.RT_FLAG_EVEN_STORES) if layout == "rgb8-wide" else 0)
+    env = g.env_of(flat, max_depth, flags)
+    cam = abi.make_camera(flat.eye, width, height)
+    spheres, lights = torch.from_numpy(flat.spheres).to(g.dev), torch.from_numpy(flat.point_lights).to(g.dev)
+    shard = sharding.StripShard(height, world, rank)
+    peer = sharding.PeerFrame(height, width, rank, world, g.local, dst=0, channels=channels)
+
+    def launch_shard(_step=0) -> None:
+        # the exchange step is inside the kernel: stores go to rank 0's framebuffer
+        abi.check(lib.rt_render_strips_dev(g.local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
+                                           C.byref(cam), shard.strip_rows, rank, world, None, abi.RT_DTYPE_F32, 0,
+                                           peer.ptr, None, g.sptr), "rt_render_strips_dev")
+
+    # ---- the single-GPU frame (rank 0 alone, its fastest 8-bit layout: RGBA8, 8x4 patches) and the comparison
+    solo_ms, matches = None, None
+    solo_env = g.env_of(flat, max_depth, abi.RT_FLAG_IMAGE_ORDER)
+    solo = torch.empty((height, width, 4), dtype=torch.uint8, device=g.dev) if rank == 0 else None
+
+    def launch_solo(_step=0) -> None:
+        abi.check(lib.rt_render_strips_dev(g.local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(solo_env),
+                                           C.byref(cam), shard.strip_rows, 0, 1, None, abi.RT_DTYPE_F32, 0,
+                                           solo.data_ptr(), None, g.sptr), "rt_render_strips_dev")
+
+    if rank == 0:
+        launch_solo()
+    launch_shard()
+    frame = peer.complete()
+    if rank == 0:
+        matches = bool(torch.equal(frame[:, :, :3], solo[:, :, :3]))
+    # every rank times its shard; then rank 0 times the whole frame alone while the others wait
+    shard_ms = g.timed_steps(launch_shard, steps, warmup, together=True)
+    mine = float(shard_ms.mean())
+    per_rank = g.gather_floats(mine)
+    ms_per_step = max(per_rank)
+    if rank == 0:
+        was = g.world
+        g.world = 1  # no barriers: the other ranks are parked at the barrier below
+        solo_ms = float(g.timed_steps(launch_solo, steps, warmup).mean())
+        g.world = was
+    g.barrier()
+
+    # ---- end to end: all ranks render, rank 0 copies the assembled frame to pinned host memory
+    host = torch.empty((height, width, channels), dtype=torch.uint8).pin_memory() if rank == 0 else None
+    e2e = []
+    for s in range(warmup + steps):
+        g.barrier()
+        t0 = time.perf_counter()
+        launch_shard()
+        frame = peer.complete()  # stream sync on every rank + barrier
+        if rank == 0:
+            host.copy_(frame, non_blocking=True)
+            torch.cuda.current_stream(g.local).synchronize()
+            _ = int(host[height // 2, width // 2, 1])
+        if s >= warmup:
+            e2e.append((time.perf_counter() - t0) * 1e3)
+    e2e_ms = float(np.mean(e2e))
+    peer.close()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        return {}
+    px = width * height
+    return {
+        "workload": LABELS["c4"], "n_gpus": world, "ms_per_step": ms_per_step, "value": px / (ms_per_step * 1e-3) / 1e6, "unit": UNIT,
+        "scaling": "strong", "exchange": {"kind": "peer stores over NVLink into rank 0's framebuffer (CUDA IPC), no gather",
+                                          "layout": "RGB8, 32x1 patches, patches from both ends" if layout == "rgb8-wide" else "RGBA8, 8x4 patches",
+                                          "strip_rows": shard.strip_rows},
+        "per_rank_ms": per_rank, "own_n1_ms": solo_ms,
+        "own_n1_note": "the same frame on rank 0 alone in the same run (RGBA8, 8x4 patches: its fastest 8-bit layout)",
+        "efficiency_vs_own_n1": solo_ms / (world * ms_per_step),
+        "frame_matches_single_gpu": matches,
+        "e2e": {"ms_per_step": e2e_ms, "value": px / (e2e_ms * 1e-3) / 1e6,
+                "what": "launch on every rank -> stream sync + barrier -> D2H of the assembled frame on rank 0 into pinned host memory -> one pixel read",
+                "d2h_bytes_per_step": px * channels},
+        "steps": steps, "warmup": warmup,
+    }
+
+
+def c3_object(g: Gpu, steps: int, warmup: int) -> dict:
+    """BASELINE configs[2] through the sphere tree on one GPU."""
+    saved = (g.args.steps, g.args.warmup)
+    g.args.steps, g.args.warmup = steps, warmup
+    try:
+        launch, counters, tables, cam, width, height, keep = device_frames(g, "c3", use_tree=True)
+        ms = float(g.timed_steps(launch, steps, warmup).mean())
+        k = counters()
+    finally:
+        g.args.steps, g.args.warmup = saved
+    return {"workload": LABELS["c3"], "ms_per_step": ms, "value": width * height / (ms * 1e-3) / 1e6, "unit": UNIT,
+            "accel": "sphere BVH (rt_accel_build_host), built before the timed region", "counters": k, "steps": steps, "warmup": warmup}
+
+
+def run_b200_arm(args) -> None:
+    g = Gpu(args)
+    torch, abi, lib = g.torch, g.abi, g.lib
+    name = args.workload
+    if name == "c4":
+        obj = c4_object(g, args.steps, args.warmup)
+        if g.rank == 0:
+            obj["config"] = config_of("c4", g.world)
+            obj["metric"], obj["warmup"], obj["higher_is_better"], obj["dtype"], obj["data"] = METRIC, args.warmup, True, "f64", "synthetic"
+            obj["gpu_launches"] = g.launches
+            print(json.dumps(obj))
+        if g.world > 1:
+            g.dist.destroy_process_group()
+        return
+
+    label, flat0, width, height, max_depth = workload(name, g.rank, 0, g.world)
+    use_tree = args.accel == "on" or (args.accel == "auto" and flat0.n_spheres >= abi.RT_ACCEL_AUTO_SPHERES)
+    launch, counters, tables, cam, width, height, keep = device_frames(g, name, use_tree)
+    n = width * height
+
+    sampler = ClockSampler(g.local)
+    sampler.start()
+    wall0 = time.perf_counter()
+    step_ms = g.timed_steps(launch, args.steps, args.warmup)
+    wall = time.perf_counter() - wall0
+    timed_mark = sampler.mark()
+    # the ALU peaks of this GPU, measured in the same clock-sampled window (rank 0's denominators)
+    fp64, fp32 = C.c_double(0.0), C.c_double(0.0)
+    abi.check(lib.rt_measure_fma_peak(g.local, abi.RT_DTYPE_F64, C.byref(fp64)), "rt_measure_fma_peak f64")
+    abi.check(lib.rt_measure_fma_peak(g.local, abi.RT_DTYPE_F32, C.byref(fp32)), "rt_measure_fma_peak f32")
+    sampler.finish()
+    clocks = sampler.summary(0, timed_mark)
+    peak_clocks = sampler.summary(timed_mark)
+    main_launches = g.launches
+
+    ms_per_step = g.max_over_ranks(float(step_ms.mean()))
+    pixels_per_step = n * g.world
+    value = pixels_per_step / (ms_per_step * 1e-3) / 1e6
+    k = counters()
+    flop = k["sphere_tests"] * FLOP_PER_SPHERE_TEST + k["hits_shaded"] * FLOP_PER_HIT
+
+    e2e = host_path(g, tables, cam, width, height, use_tree)
+    c4 = c4_object(g, args.c4_steps, 3) if (args.c4 and name == "c2") else None
+    extra = {}
+    if g.rank == 0 and name == "c2":
+        extra["pipeline"] = pipeline_object(g)
+        if g.world == 1 and args.c3:
+            extra["c3"] = c3_object(g, 20, 3)
+    if g.world > 1:
+        g.barrier()
+    if g.rank != 0:
+        if g.world > 1:
+            g.dist.destroy_process_group()
         return
 
     # ---- rooflines of the trace kernel (rank 0's launch)
     kernel_ms = float(step_ms.mean())
     peaks = measured_peaks()
-    bytes_per_pixel = (3.0 if peer_layout == "rgb8-wide" else 4.0) if (banded and args.exchange == "peer") else BYTES_PER_PIXEL
-    achieved_gbs = bytes_per_pixel * n / (kernel_ms * 1e-3) / 1e9
-    fp64 = C.c_double(0.0)
-    fp32 = C.c_double(0.0)
-    abi.check(lib.rt_measure_fma_peak(local, abi.RT_DTYPE_F64, C.byref(fp64)), "rt_measure_fma_peak f64")
-    abi.check(lib.rt_measure_fma_peak(local, abi.RT_DTYPE_F32, C.byref(fp32)), "rt_measure_fma_peak f32")
+    achieved_gbs = BYTES_PER_PIXEL * n / (kernel_ms * 1e-3) / 1e9
     achieved_tflops = flop / (kernel_ms * 1e-3) / 1e12
-
+    traffic, capture = ncu_traffic(name)
     cpu = None
-    if world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_single_core(frames[0][1], width, height, max_depth)
-
+    if g.world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_single_core(flat0, width, height, max_depth)
+    small = (args.precision == "fast" and flat0.n_spheres <= abi.RT_SMALL_SCENE_SPHERES and not use_tree)
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if banded else "weak",
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": g.world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": label, "width": width, "height": height, "spheres": frames[0][1].n_spheres,
-                   "max_depth": max_depth or None, "precision": args.precision, "cutoff": args.cutoff,
-                   "accel": ("sphere BVH (rt_accel_build_host): built before the timed region for `value`, inside it for `e2e`"
-                             if use_tree else "none: every ray tests every sphere"),
-                   "output": (("whole-frame %s on rank 0 (fused quantisation), no linear planes" % ("RGB8, 32x1 patches" if peer_layout == "rgb8-wide" else "RGBA8, 8x4 patches")) if banded and args.exchange == "peer" else "planar f32 linear RGB + RGBA8 (fused quantisation)"),
-                   "parallelism": (("interleaved 16-row strips x%d, kernels store the 8-bit frame into rank 0's framebuffer over NVLink peer memory (no gather)" % world)
-                                   if args.exchange == "peer" else ("interleaved 16-row strips x%d + NCCL gather of RGBA8 to rank 0 + row permutation" % world)) if banded else ("frame-sharded x%d, no collective" % world),
-                   "l2": "512 MiB buffer written between timed steps (L2 flush); each step timed by its own CUDA event pair"},
-        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_value, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "d2h_gb_per_s_per_gpu": d2h / (e2e_ms_value * 1e-3) / 1e9,
-                "host_cpus_bound": len(bound) if bound else None,
-                "api": "rt_render_frame_host: scene upload + kernel + D2H of the f32 linear planes into pinned host memory, row chunks pipelined (kernel of chunk i+1 under the copy of chunk i, small first chunk, one strided copy per chunk)",
-                "with_rgb8": {"ms_per_step": e2e_rgb8_ms, "value": pixels_per_step / (e2e_rgb8_ms * 1e-3) / 1e6,
-                              "d2h_bytes_per_step": d2h + rgb8_host.numel()},
-                # what render_image_pipeline needs on the host: only the 8-bit image save_image writes
-                "rgb8_only": {"ms_per_step": e2e_rgb8_only_ms, "value": pixels_per_step / (e2e_rgb8_only_ms * 1e-3) / 1e6,
-                              "d2h_bytes_per_step": rgb8_host.numel()}},
-        "gpu_launches": args.steps,
+        "config": config_of(name, g.world),
+        "arm": {"precision": args.precision, "cutoff": args.cutoff,
+                "arithmetic": "FP64 geometry (rays, roots, hit points, shadow decisions, GGX inputs), FP32 shading tail",
+                "accel": ("sphere BVH (rt_accel_build_host): built before the timed region for `value`, inside it for `e2e`"
+                          if use_tree else "none: every ray tests every sphere"),
+                "kernel": "render_rows_small_kernel (sphere table as a kernel parameter)" if small else "render_rows_kernel",
+                "output": "planar f32 linear RGB + RGBA8 (fused quantisation), 16 B per pixel",
+                "parallelism": "frame-sharded x%d, no collective" % g.world,
+                "l2": "512 MiB buffer written between timed steps (L2 flush); each step timed by its own CUDA event pair"},
+        "e2e": e2e,
+        "gpu_launches": main_launches,
         # The binding roofline of this path is the FP64 pipe (no contraction, 16 B written per
         # pixel): algorithmic flops / kernel time against the FP64 FMA rate measured on this GPU
         # in this run.  The HBM reading (MEASURED_PEAKS.json denominator) is kept beside it.
         "roofline": {"bound": "fp64-alu", "achieved": achieved_tflops, "peak": fp64.value / 1e12, "unit": "TFLOP/s",
                      "frac": achieved_tflops / (fp64.value / 1e12) if fp64.value else None,
-                     "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload),
-                     "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one launch under ncu --set full "
-                                     "(profiles/): the frame stays in the 126 MB L2 while the kernel runs, so DRAM sees "
-                                     "almost nothing of the 33 MB the launch writes",
-                     "peak_source": "rt_measure_fma_peak (register-resident FP64 FMA chains), same GPU, same run; "
+                     "traffic": traffic, "traffic_capture": capture,
+                     "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel under ncu --set full: "
+                                     "the frame stays in the 126 MB L2 while the kernel runs, so DRAM sees almost nothing of the "
+                                     "33 MB the launch writes",
+                     "peak_source": "rt_measure_fma_peak (register-resident FP64 FMA chains), same GPU, same run, inside the clock sampler's window; "
                                     "MEASURED_PEAKS.json holds no ALU peak",
-                     "fp32_peak": fp32.value / 1e12, "kernel": "render_rows_kernel", "kernel_ms": kernel_ms,
-                     "algorithmic_flop_per_step": flop,
-                     "counters": {"rays_traced": traced, "hits_shaded": hits, "generations": deepest, "sphere_tests": tests}},
+                     "peak_clocks": peak_clocks, "fp32_peak": fp32.value / 1e12, "kernel_ms": kernel_ms,
+                     "algorithmic_flop_per_step": flop, "counters": k},
         "roofline_hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved_gbs / peaks["hbm_gbs"], "peak_source": peaks["source"],
-                         "algorithmic_bytes_per_step": bytes_per_pixel * n},
-        "roofline_alu": {"frac": achieved_tflops / (fp64.value / 1e12) if fp64.value else None,
-                         "note": "same as roofline (kept for the sweep scripts)"},
+                         "algorithmic_bytes_per_step": BYTES_PER_PIXEL * n},
         "clocks": clocks,
         "wall_s_timed_region": wall,
     }
+    if c4:
+        line["c4"] = c4
+    line.update(extra)
     if cpu is not None:
         line["cpu_baseline"] = cpu
     print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    if g.world > 1:
+        g.dist.destroy_process_group()
 
 
 def main() -> None:
@@ -487,10 +701,10 @@ def main() -> None:
     parser.add_argument("--accel", choices=["auto", "on", "off"], default="auto",
                         help="sphere BVH: auto = scenes of RT_ACCEL_AUTO_SPHERES shapes or more")
     parser.add_argument("--peer-layout", choices=["auto", "rgba8", "rgb8-wide"], default="auto",
-                        help="c4 with --exchange peer: how the frame is stored into rank 0's buffer (auto: rgb8-wide from 8 ranks on)")
-    parser.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
-                        help="c4 with N > 1: kernels store into rank 0's framebuffer over NVLink (peer) or "
-                             "render locally and gather with NCCL (nccl)")
+                        help="c4: how the frame is stored into rank 0's buffer (auto: rgb8-wide from 8 ranks on)")
+    parser.add_argument("--no-c4", dest="c4", action="store_false", help="skip the c4 object of the default run")
+    parser.add_argument("--no-c3", dest="c3", action="store_false", help="skip the c3 object of the default N = 1 run")
+    parser.add_argument("--c4-steps", type=int, default=30)
     args = parser.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3  # timing rule: at least 3 warm-up steps

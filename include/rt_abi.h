@@ -175,6 +175,13 @@ int rt_abi_version(void);
 const char* rt_last_error(void);
 int rt_device_count(int* count_out);
 int rt_release_cache(void);
+/* What a kernel of an earlier launch on `device` reported, if anything: device entry points only
+ * enqueue work, so a launch that finds it cannot render what it was given (an rt_env.accel_dev that
+ * is not a blob for its sphere table; a tree deeper than the traversal stack) sets a sticky word
+ * instead.  Returns RT_OK, or RT_ERR_UNSUPPORTED with the reason in rt_last_error(), and clears
+ * it.  Every device entry point makes the same check first, so such a launch never goes unnoticed;
+ * call this after synchronising to learn about the launch just finished. */
+int rt_device_status(int device);
 
 /*
  * rt_measure_fma_peak -- achieved FLOP/s (2 per FMA) of a register-resident chain of

@@ -94,6 +94,9 @@ rt::SceneParams scene_params(const double* spheres_dev, int32_t n_spheres, const
     sp.spheres = spheres_dev;
     sp.lights = lights_dev;
     sp.accel = static_cast<const unsigned char*>(env->accel_dev);
+    sp.accel_bytes = env->accel_bytes;
+    sp.error_word = nullptr;
+    if (sp.accel != nullptr) rt::device_error_word(&sp.error_word);  // current device = the call's (DeviceScope)
     sp.n_spheres = n_spheres;
     sp.n_lights_used = (env->flags & RT_FLAG_ALL_POINT_LIGHTS) ? env->n_point_lights : 1;
     sp.n_dome = env->n_dome_lights;
@@ -131,12 +134,17 @@ rt::SceneParams scene_params(const double* spheres_dev, int32_t n_spheres, const
     return sp;
 }
 
-// Scenes of at most kSmallMax spheres whose table the caller holds on the host too (rt_env.spheres_host,
-// point_lights_host): everything the fast policy's kernel reads of the scene, as one kernel parameter.
-bool small_table(const rt_env* env, int32_t n_spheres, const double* origin0, rt::SmallTable* table) {
+bool small_scene(const rt_env* env, int32_t n_spheres) {
     if (env->mode != RT_MODE_FAST || env->spheres_host == nullptr || env->point_lights_host == nullptr) return false;
     if (n_spheres > rt::kSmallMax || env->accel_dev != nullptr || (env->flags & RT_FLAG_GENERIC_KERNEL)) return false;
     if ((env->flags & RT_FLAG_ALL_POINT_LIGHTS) && env->n_point_lights > 1) return false;
+    return true;
+}
+
+// Scenes of at most kSmallMax spheres whose table the caller holds on the host too (rt_env.spheres_host,
+// point_lights_host): everything the fast policy's kernel reads of the scene, as one kernel parameter.
+bool small_table(const rt_env* env, int32_t n_spheres, const double* origin0, rt::SmallTable* table) {
+    if (!small_scene(env, n_spheres)) return false;
     memset(table, 0, sizeof(*table));
     const double* f = env->spheres_host;
     const size_t n = (size_t)n_spheres;
@@ -184,6 +192,8 @@ struct CounterRing {
 };
 CounterRing g_rings[kMaxDevices];
 std::mutex g_ring_mutex;
+// one pinned, device-mapped word per device: kernels report through it (rt::DeviceError)
+unsigned int* g_error_words[kMaxDevices] = {};
 
 }  // namespace
 
@@ -210,6 +220,26 @@ cudaError_t ticket_counter(unsigned int** counter_out) {
     return cudaSuccess;
 }
 
+cudaError_t device_error_word(unsigned int** device_pointer_out) {
+    int device = 0;
+    cudaError_t err = cudaGetDevice(&device);
+    if (err != cudaSuccess) return err;
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    if (g_error_words[device] == nullptr) {
+        std::lock_guard<std::mutex> lock(g_ring_mutex);
+        if (g_error_words[device] == nullptr) {
+            unsigned int* p = nullptr;
+            if ((err = cudaHostAlloc(&p, sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable)) != cudaSuccess) return err;
+            *p = 0u;
+            g_error_words[device] = p;
+        }
+    }
+    void* dev = nullptr;
+    if ((err = cudaHostGetDevicePointer(&dev, g_error_words[device], 0)) != cudaSuccess) return err;
+    *device_pointer_out = static_cast<unsigned int*>(dev);
+    return cudaSuccess;
+}
+
 void release_ticket_counters() {
     std::lock_guard<std::mutex> lock(g_ring_mutex);
     int previous = -1;
@@ -224,6 +254,21 @@ void release_ticket_counters() {
 }  // namespace rt
 
 namespace {
+
+// What a kernel of an earlier launch on `device` reported (sticky until read here).
+int pending_device_error(int device) {
+    if (device < 0 || device >= kMaxDevices || g_error_words[device] == nullptr) return RT_OK;
+    const unsigned int code = *reinterpret_cast<volatile unsigned int*>(g_error_words[device]);
+    if (code == rt::kDevOk) return RT_OK;
+    *reinterpret_cast<volatile unsigned int*>(g_error_words[device]) = rt::kDevOk;
+    if (code == rt::kDevBadAccelBlob)
+        return fail(RT_ERR_UNSUPPORTED, "an earlier launch on device %d was given an rt_env.accel_dev that is not a blob of "
+                    "rt_accel_build_host for its sphere table (magic, shape count or size disagree): it rendered nothing", device);
+    if (code == rt::kDevAccelStack)
+        return fail(RT_ERR_UNSUPPORTED, "an earlier launch on device %d walked a tree deeper than the traversal stack (%d): "
+                    "not a blob of rt_accel_build_host; its pixels are wrong", device, rt::kAccelStack);
+    return fail(RT_ERR_UNSUPPORTED, "an earlier launch on device %d reported device error %u", device, code);
+}
 
 const rt::Launchers& launchers(int mode) { return mode == RT_MODE_FAST ? rt::fast_launchers() : rt::exact_launchers(); }
 
@@ -259,6 +304,13 @@ const char* rt_last_error(void) { return g_error; }
 __attribute__((visibility("hidden"))) void rt_internal_set_error(const char* message) {
     snprintf(g_error, sizeof(g_error), "%s", message);
 }
+// not part of the ABI: will a camera launch with this env take the kernel-parameter path (and so never
+// read the device copies of the tables)?
+__attribute__((visibility("hidden"))) int rt_internal_small_scene(const rt_env* env, int32_t n_spheres) {
+    return small_scene(env, n_spheres) ? 1 : 0;
+}
+
+int rt_device_status(int device) { return pending_device_error(device); }
 
 int rt_device_count(int* count_out) {
     if (count_out == nullptr) return fail(RT_ERR_BAD_ARG, "count_out is NULL");
@@ -310,6 +362,7 @@ int rt_render_rows_dev(int device, const double* spheres_dev, int32_t n_spheres,
                        int32_t rgb_dtype, int64_t plane_stride, uint8_t* rgba8_dev, uint64_t* stats_dev,
                        void* stream) {
     int rc;
+    if ((rc = pending_device_error(device)) != RT_OK) return rc;
     if ((rc = check_env(env, n_spheres)) != RT_OK) return rc;
     if ((rc = check_camera(cam, row0, row1)) != RT_OK) return rc;
     return render_camera(device, spheres_dev, n_spheres, point_lights_dev, env, camera_params(cam, row0, row1), rgb_dev,
@@ -331,6 +384,7 @@ int rt_render_strips_dev(int device, const double* spheres_dev, int32_t n_sphere
                          int32_t strip_step, void* rgb_dev, int32_t rgb_dtype, int64_t plane_stride,
                          uint8_t* rgba8_dev, uint64_t* stats_dev, void* stream) {
     int rc;
+    if ((rc = pending_device_error(device)) != RT_OK) return rc;
     if ((rc = check_env(env, n_spheres)) != RT_OK) return rc;
     if ((rc = check_camera(cam, 0, cam != nullptr ? cam->height : 0)) != RT_OK) return rc;
     if (strip_rows <= 0 || strip_step <= 0 || strip_first < 0 || strip_first >= strip_step)
@@ -394,6 +448,7 @@ int rt_trace_rays_dev(int device, const double* spheres_dev, int32_t n_spheres, 
                       const double* directions_dev, int64_t n_rays, void* rgb_dev, int32_t rgb_dtype,
                       int64_t plane_stride, uint64_t* stats_dev, void* stream) {
     int rc;
+    if ((rc = pending_device_error(device)) != RT_OK) return rc;
     if ((rc = check_env(env, n_spheres)) != RT_OK) return rc;
     if (spheres_dev == nullptr || point_lights_dev == nullptr) return fail(RT_ERR_BAD_ARG, "scene pointers are NULL");
     if (n_rays < 0) return fail(RT_ERR_BAD_ARG, "n_rays = %lld", (long long)n_rays);

@@ -34,6 +34,7 @@ struct DeviceCache {
 thread_local DeviceCache g_cache[kMaxDevices];
 // defined in rt_abi.cu: records the message rt_last_error() returns
 extern "C" void rt_internal_set_error(const char* message);
+extern "C" int rt_internal_small_scene(const rt_env* env, int32_t n_spheres);
 
 cudaError_t reserve(Scratch& s, size_t bytes) {
     if (bytes <= s.bytes) return cudaSuccess;
@@ -172,14 +173,20 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
     int rc = enter(device, restore, &c);
     if (rc != RT_OK) return rc;
 
-    const double *spheres_dev, *lights_dev;
-    if ((rc = upload_scene(*c, spheres_host, n_spheres, point_lights_host, env->n_point_lights, &spheres_dev, &lights_dev)) != RT_OK) return rc;
     rt_env with_tree;
     if ((rc = attach_accel(*c, spheres_host, n_spheres, env, &with_tree)) != RT_OK) return rc;
     env = &with_tree;
     // the tables are host memory here by definition: per-scene constants are formed on the host
     with_tree.spheres_host = spheres_host;
     with_tree.point_lights_host = point_lights_host;
+    const double *spheres_dev, *lights_dev;
+    if (rt_internal_small_scene(env, n_spheres)) {
+        // the camera kernel of a small scene reads its table from the kernel parameters: nothing to upload
+        HOST_CUDA(reserve(c->scene, 256));
+        spheres_dev = lights_dev = static_cast<const double*>(c->scene.ptr);
+    } else if ((rc = upload_scene(*c, spheres_host, n_spheres, point_lights_host, env->n_point_lights, &spheres_dev, &lights_dev)) != RT_OK) {
+        return rc;
+    }
     // the scratch buffers hold the band, chunk by chunk: a caller's whole-frame addressing flag
     // (meant for rt_render_rows_dev with its own frame buffer) must not reach the kernel
     with_tree.flags &= ~RT_FLAG_IMAGE_ORDER;

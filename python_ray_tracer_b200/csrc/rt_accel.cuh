@@ -20,14 +20,27 @@ struct AccelView {
     const SphereAux* aux;
     const ShadeRec* rec;
     const int* large;
+    unsigned int* error;  // SceneParams::error_word
     int n_nodes, n_large;
     double local_bound, gain_bound;
     float extent;
 };
 
-__device__ __forceinline__ AccelView accel_view(const unsigned char* blob) {
+// Is sp.accel a blob built for this sphere table?  A stale or foreign blob would render a mixed scene or
+// read out of bounds: the launch reports it and renders nothing.  Same answer in every thread.
+__device__ __forceinline__ bool accel_blob_ok(const SceneParams& sp) {
+    const AccelHeader* h = reinterpret_cast<const AccelHeader*>(sp.accel);
+    const bool ok = sp.accel_bytes >= (long long)sizeof(AccelHeader) && __ldg(&h->magic) == kAccelMagic &&
+                    __ldg(&h->n_spheres) == sp.n_spheres && __ldg(&h->bytes) <= sp.accel_bytes;
+    if (!ok && sp.error_word != nullptr && threadIdx.x == 0) *reinterpret_cast<volatile unsigned int*>(sp.error_word) = kDevBadAccelBlob;
+    return ok;
+}
+
+__device__ __forceinline__ AccelView accel_view(const SceneParams& sp) {
+    const unsigned char* blob = sp.accel;
     const AccelHeader* h = reinterpret_cast<const AccelHeader*>(blob);
     AccelView v;
+    v.error = sp.error_word;
     v.nodes = reinterpret_cast<const AccelNode*>(blob + h->off_nodes);
     v.order = reinterpret_cast<const int*>(blob + h->off_order);
     v.leaf_geom = reinterpret_cast<const SphereGeom*>(blob + h->off_leaf_geom);
@@ -178,6 +191,9 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
                     stack_t[top] = b_first ? ta : tb;
                     stack_ref[top] = b_first ? ref_a : ref_b;
                     ++top;
+                } else if (av.error != nullptr) {
+                    // deeper than any tree rt_accel_build_host makes: the far child is lost -- say so
+                    *reinterpret_cast<volatile unsigned int*>(av.error) = kDevAccelStack;
                 }
                 ref = b_first ? ref_b : ref_a;
                 popped = false;
@@ -239,7 +255,10 @@ __device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, V
             slab_enter(ray, a, limit, hit_a);
             slab_enter(ray, b, limit, hit_b);
             if (hit_a || hit_b) {
-                if (hit_a && hit_b && top < kAccelStack) stack[top++] = b.ref;
+                if (hit_a && hit_b) {
+                    if (top < kAccelStack) stack[top++] = b.ref;
+                    else if (av.error != nullptr) *reinterpret_cast<volatile unsigned int*>(av.error) = kDevAccelStack;
+                }
                 ref = hit_a ? a.ref : b.ref;
                 popped = false;
             }

@@ -249,6 +249,12 @@ struct Builder {
 
 size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
 
+extern "C" void rt_internal_set_error(const char* message);  // rt_abi.cu: what rt_last_error() returns
+int build_fail(int status, const char* message) {
+    rt_internal_set_error(message);
+    return status;
+}
+
 // rt_chain.cuh:material_bound() on the host (same expression; it only has to be an upper bound)
 double material_bound_host(const double* f, int n, int s, const rt_env* env) {
     const double dg = f[(size_t)RT_F_DIFFUSE_GAIN * n + s], sg = f[(size_t)RT_F_SPECULAR_GAIN * n + s];
@@ -282,14 +288,17 @@ int64_t rt_accel_bytes(int32_t n_spheres) {
 int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_env* env, void* blob_out,
                         int64_t capacity, int64_t* bytes_out) {
     if (spheres_host == nullptr || env == nullptr || blob_out == nullptr || bytes_out == nullptr || n_spheres <= 0)
-        return RT_ERR_BAD_ARG;
-    if (capacity < rt_accel_bytes(n_spheres)) return RT_ERR_BAD_ARG;
+        return build_fail(RT_ERR_BAD_ARG, "rt_accel_build_host: NULL pointer or no spheres");
+    if (capacity < rt_accel_bytes(n_spheres))
+        return build_fail(RT_ERR_BAD_ARG, "rt_accel_build_host: capacity is smaller than rt_accel_bytes(n_spheres)");
     const int n = n_spheres;
-    if (n > (1 << 26)) return RT_ERR_UNSUPPORTED;  // traversal packs a node index and a leaf count into 32 bits
+    if (n > (1 << 26))  // traversal packs a node index and a leaf count into 32 bits
+        return build_fail(RT_ERR_UNSUPPORTED, "rt_accel_build_host: more than 2^26 spheres");
     for (int s = 0; s < n; ++s) {
         double reach = std::fabs(spheres_host[(size_t)RT_F_RADIUS * n + s]);
         for (int a = 0; a < 3; ++a) reach = std::max(reach, std::fabs(spheres_host[(size_t)a * n + s]));
-        if (!(reach <= rt::kAccelMaxCoordinate)) return RT_ERR_UNSUPPORTED;  // (NaN lands here too)
+        if (!(reach <= rt::kAccelMaxCoordinate))  // (NaN lands here too)
+            return build_fail(RT_ERR_UNSUPPORTED, "rt_accel_build_host: a coordinate or radius beyond 1e15 (or NaN): the tree's boxes are FP32");
     }
     Builder b;
     if (env->flags & RT_FLAG_ACCEL_FAST_BUILD) b.sah_depth = 0;
@@ -311,7 +320,8 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
         b.nodes.push_back(AccelNode());
         b.build(0, 0, (int)b.items.size(), 0, b.bounds(0, (int)b.items.size()));
         // the traversal keeps at most one pending sibling per level on its stack
-        if (b.deepest + 1 > rt::kAccelStack) return RT_ERR_UNSUPPORTED;
+        if (b.deepest + 1 > rt::kAccelStack)
+            return build_fail(RT_ERR_UNSUPPORTED, "rt_accel_build_host: the tree came out deeper than the traversal stack of 64");
     }
 
     AccelHeader h;
@@ -337,7 +347,7 @@ int rt_accel_build_host(const double* spheres_host, int32_t n_spheres, const rt_
     h.off_large = (int64_t)off;
     off += align16(4 * large.size());
     h.bytes = (int64_t)off;
-    if ((int64_t)off > capacity) return RT_ERR_BAD_ARG;
+    if ((int64_t)off > capacity) return build_fail(RT_ERR_BAD_ARG, "rt_accel_build_host: capacity too small for the blob");
     double lmax = 0.0, gmax = 0.0;
     for (int s = 0; s < n; ++s) {
         lmax = std::max(lmax, material_bound_host(spheres_host, n, s, env));

@@ -96,7 +96,7 @@ __device__ __forceinline__ StagedScene stage_fast(const SceneParams& sp, unsigne
 
 __device__ __forceinline__ TreeScene stage_tree(const SceneParams& sp, unsigned char* smem) {
     TreeScene sc;
-    sc.av = accel_view(sp.accel);
+    sc.av = accel_view(sp);
     sc.lights = stage_lights(sp, reinterpret_cast<double*>(smem));
     __syncthreads();
     sc.lights_used = sp.n_lights_used;

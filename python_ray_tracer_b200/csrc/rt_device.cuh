@@ -46,6 +46,8 @@ struct SceneParams {
     const double* spheres;  // field-major sphere SoA (rt_abi.h), device
     const double* lights;   // n_point_lights x 3, device
     const unsigned char* accel;  // BVH blob (rt_accel.h) or nullptr: test every sphere
+    long long accel_bytes;       // size the caller gave for it
+    unsigned int* error_word;    // host-mapped word a kernel sets when it cannot render what it was given (DeviceError)
     int n_spheres;
     int n_lights_used;      // 1 unless RT_FLAG_ALL_POINT_LIGHTS
     int n_dome;
@@ -62,6 +64,14 @@ struct SceneParams {
                             // copy of the table (rt_env.spheres_host); < 0: no cut-off possible; see host_bound
     int host_bound;         // 1: chain_bound is valid; 0: the staging loop computes it (no host copy of the table)
     double light0[3];       // lights[0] when the host copy of the light table was given (small-scene kernels)
+};
+
+// What a kernel reports through SceneParams::error_word; the next ABI call on the device fails loudly with it
+// (rt_device_status() reads and clears it).  Pixels of a launch that reported one are undefined.
+enum DeviceError : unsigned int {
+    kDevOk = 0,
+    kDevBadAccelBlob = 1,    // rt_env.accel_dev is not a blob of rt_accel_build_host for THIS sphere table
+    kDevAccelStack = 2       // a tree deeper than the traversal stack (not a blob of rt_accel_build_host)
 };
 
 // Camera rows -> rays (base.py:123-141).  The linspace steps are divided on the host

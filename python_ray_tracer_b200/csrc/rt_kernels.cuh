@@ -365,8 +365,9 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (KIND == 1 ? R
     render_rows_kernel(const __grid_constant__ SceneParams sp, const __grid_constant__ CameraParams cp,
                        const __grid_constant__ OutputParams out, const __grid_constant__ Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
+    if (KIND == 1 && !accel_blob_ok(sp)) return;
     if constexpr (MODE == kModeExact) {
-        const ExactTracer tr = {sp, stage_exact(sp, smem), KIND == 1 ? accel_view(sp.accel) : AccelView{}};
+        const ExactTracer tr = {sp, stage_exact(sp, smem), KIND == 1 ? accel_view(sp) : AccelView{}};
         const Vec3 eye = {cp.cam[0], cp.cam[1], cp.cam[2]};
         render_rows_body<STATS, BLOCK, PW>(cp, out, tk, [&](int col, int row, Counters& k) {
             return tr.template ray<STATS, KIND == 1>(eye, primary_direction<kModeExact>(cp, col, row), k);
@@ -428,8 +429,9 @@ __global__ void __launch_bounds__(BLOCK, BLOCK == kBlockThreads ? (KIND == 1 ? R
     trace_rays_kernel(const __grid_constant__ SceneParams sp, const __grid_constant__ RayBatch rb,
                       const __grid_constant__ OutputParams out, const __grid_constant__ Tickets tk) {
     extern __shared__ __align__(16) unsigned char smem[];
+    if (KIND == 1 && !accel_blob_ok(sp)) return;
     if constexpr (MODE == kModeExact) {
-        const ExactTracer tr = {sp, stage_exact(sp, smem), KIND == 1 ? accel_view(sp.accel) : AccelView{}};
+        const ExactTracer tr = {sp, stage_exact(sp, smem), KIND == 1 ? accel_view(sp) : AccelView{}};
         trace_rays_body<STATS, BLOCK>(rb, out, tk, [&](Vec3 o, Vec3 d, Counters& k) { return tr.template ray<STATS, KIND == 1>(o, d, k); });
     } else if constexpr (KIND == 1) {
         const TreeScene sc = stage_tree(sp, smem);

@@ -27,6 +27,10 @@ const Launchers& fast_launchers();   // trace_fast.cu
 cudaError_t ticket_counter(unsigned int** counter_out);
 void release_ticket_counters();
 
+// The word kernels of the current device report errors through (DeviceError, rt_device.cuh): pinned host memory
+// mapped into the device, so the host reads it without touching a stream.  Defined in rt_abi.cu.
+cudaError_t device_error_word(unsigned int** device_pointer_out);
+
 // Largest scene whose sphere records fit one block's shared memory.
 int max_staged_spheres();
 

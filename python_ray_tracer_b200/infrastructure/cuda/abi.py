@@ -122,6 +122,7 @@ PROTOTYPES = {
     "rt_last_error": (C.c_char_p, []),
     "rt_device_count": (C.c_int, [C.POINTER(C.c_int)]),
     "rt_release_cache": (C.c_int, []),
+    "rt_device_status": (C.c_int, [C.c_int]),
     "rt_measure_fma_peak": (C.c_int, [C.c_int, C.c_int32, C.POINTER(C.c_double)]),
     "rt_accel_bytes": (C.c_int64, [C.c_int32]),
     "rt_accel_build_host": (C.c_int, [_P, C.c_int32, C.POINTER(RtEnv), _P, C.c_int64, C.POINTER(C.c_int64)]),

@@ -112,6 +112,8 @@ class DeviceColor(NumpyRGBColor):
     def numpy(self) -> np.ndarray:
         if self._host is None:
             self._host = self.planes.cpu().numpy()
+            # the copy synchronised with the launch: did its kernel report anything? (rt_device_status)
+            abi.check(abi.load().rt_device_status(self.device), "rt_device_status")
         return self._host
 
     x = property(lambda self: self.numpy()[0])
@@ -537,6 +539,7 @@ class CudaRenderer(Renderer):
                 self._rgb8_pinned = torch.empty((width * height, channels), dtype=torch.uint8).pin_memory()
             self._rgb8_pinned.copy_(dev8, non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()  # the kernel and the copy
+            abi.check(abi.load().rt_device_status(self.device), "rt_device_status")
         t1 = time.perf_counter()
         with _Nvtx("rt: PNG encode + write"):
             if self._png_pool is None and self.png_threads > 1:

@@ -126,7 +126,7 @@ def main() -> None:
         save_case(f"readme_{w}x{h}", flat, w, h, rgb, counters)
 
     # C2 / C4 -- README scene at 1080p and 8K: subsets (rows 0, H/2, H-1 + random pixels)
-    for tag, (w, h), k in (("c2_readme_1080p", (1920, 1080), 8192), ("c4_readme_8k", (7680, 4320), 16384)):
+    for tag, (w, h), k in (("c2_readme_1080p", (1920, 1080), 8192), ("c4_readme_8k", (7680, 4320), 65536)):
         print(tag)
         flat = flatten_scene(scenes.readme_scene(w, h), README_DEFAULT)
         rng = np.random.default_rng(13)
@@ -145,11 +145,11 @@ def main() -> None:
     _, rgb, counters = reference_render(flat, 192, 108, max_depth=1)
     save_case("c3_small_48_192x108_depth1", flat, 192, 108, rgb, counters, max_depth=1)
 
-    # C3 -- 1024 random spheres + ground at 4K, depth 8, 512-pixel subset (heavy)
+    # C3 -- 1024 random spheres + ground at 4K, depth 8, the 4096-pixel subset of SURVEY.md 8d (heavy)
     if args.heavy:
         print("C3 (1025 shapes) 4K subset, depth 8 -- this takes minutes")
         flat = flatten_scene(scenes.random_spheres_scene(3840, 2160), README_DEFAULT)
-        pixels = np.sort(np.random.default_rng(4321).choice(3840 * 2160, 512, replace=False))
+        pixels = np.sort(np.random.default_rng(4321).choice(3840 * 2160, 4096, replace=False))
         _, rgb, counters = reference_render(flat, 3840, 2160, pixels=pixels, max_depth=8)
         save_case("c3_1024_4k_subset_depth8", flat, 3840, 2160, rgb, counters, pixels=pixels, max_depth=8)
 

@@ -154,6 +154,28 @@ def test_exact_and_fast_agree_at_1080p(rt):
     assert rep["max_abs"] < 1e-5  # the fast policy shades in single precision (values up to ~1.7)
 
 
+def test_full_1080p_frame_against_the_oracle(rt, c_oracle):
+    """BASELINE configs[1] at size, EVERY pixel: the README frame at 1920x1080 in both policies
+    against oracle/librt_oracle.so (the C restatement, OpenMP over the box's cores), linear values
+    and the fused 8-bit image; exact policy: identical ray / hit / depth counters."""
+    case = load_case("c2_readme_1080p_subset")
+    want, counters = c_oracle.render(case.flat, case.width, case.height)
+    assert_linear_parity(want[:, case.pixels], case.rgb, 1e-12, "oracle vs the reference's own 1080p pixels")
+    want8 = c_oracle.quantize(want)
+    for precision in PRECISIONS:
+        color = _render(rt(precision), case)
+        got = color.numpy()
+        rep = assert_linear_parity(got, want, EXACT_TOL if precision == "exact" else 1e-4, f"full 1080p frame/{precision}")
+        assert rep["max_abs"] < (1e-12 if precision == "exact" else 1e-5), rep
+        got8 = color.rgba8.cpu().numpy()[:, :3]
+        assert_png_parity(got8, want8, f"full 1080p frame/{precision}")
+        off = int((got8.astype(np.int16) != want8.astype(np.int16)).any(axis=1).sum())
+        assert off <= (0 if precision == "exact" else 6_000), off  # bytes next to a rounding boundary (of 2 073 600 pixels)
+        if precision == "exact":
+            k = color.counters()
+            assert (k["rays_traced"], k["hits_shaded"], k["generations"]) == (int(counters[0]), int(counters[1]), int(counters[2]))
+
+
 def test_c3_1024_spheres_4k_band(rt, c_oracle):
     """Config 3 at size: a 4K band of the 1025-shape scene (depth 8) against the oracle."""
     case = load_case("c3_1024_4k_subset_depth8")
@@ -553,6 +575,38 @@ def test_bvh_gives_the_same_picture_as_testing_every_sphere(precision, c_oracle)
     # the all-lights extension walks the tree once per light
     plain, tree = pair(max_depth=8, all_point_lights=True)
     assert np.array_equal(_render(plain, case).numpy(), _render(tree, case).numpy())
+
+
+def test_a_blob_of_another_scene_fails_loudly(rt):
+    """rt_env.accel_dev must be the blob of THIS sphere table: a launch given another scene's tree renders
+    nothing and says so -- through rt_device_status() and through the next device call -- instead of
+    quietly mixing two scenes (materials from the table, geometry from the blob)."""
+    import torch
+
+    from python_ray_tracer_b200.infrastructure.cuda import abi
+
+    lib = abi.load()
+    case, other = load_case("c3_small_48_192x108"), load_case("stress_random20_48x27")
+    renderer = rt("fast", accel=True)
+    good = _render(renderer, case).numpy()  # builds and caches the tree of `case`
+    assert lib.rt_device_status(0) == 0
+    spheres, lights = (torch.from_numpy(a).cuda() for a in (other.flat.spheres, other.flat.point_lights))
+    env = renderer._plain_env(other.flat)
+    env.accel_dev, env.accel_bytes = renderer._accel_dev.data_ptr(), renderer._accel_dev.numel()  # the WRONG blob
+    cam = abi.make_camera(other.flat.eye, other.width, other.height)
+    n = other.width * other.height
+    planes = torch.full((3, n), -1.0, dtype=torch.float64, device="cuda")
+    call = lambda: lib.rt_render_rows_dev(0, spheres.data_ptr(), other.flat.n_spheres, lights.data_ptr(), C.byref(env), C.byref(cam),  # noqa: E731
+                                          0, other.height, planes.data_ptr(), abi.RT_DTYPE_F64, n, None, None, None)
+    assert call() == 0  # enqueued: the mismatch is only visible on the device
+    torch.cuda.synchronize()
+    assert (planes == -1.0).all()  # nothing was rendered
+    assert lib.rt_device_status(0) == -4 and b"not a blob" in lib.rt_last_error()
+    assert lib.rt_device_status(0) == 0  # reading it clears it
+    assert call() == 0
+    torch.cuda.synchronize()
+    assert call() == -4 and b"not a blob" in lib.rt_last_error()  # ... and the next device call refuses
+    assert np.array_equal(_render(renderer, case).numpy(), good)
 
 
 def test_bvh_lifts_the_shared_memory_limit(rt, c_oracle):

@@ -3,6 +3,7 @@ scene flattener, the PNG container and the C-ABI library's symbol table (no comp
 
 import ctypes
 import re
+import sys
 from pathlib import Path
 
 import numpy as np
@@ -395,3 +396,89 @@ def test_accel_depth_stays_within_the_traversal_stack():
             else:
                 todo += [(first, depth + 1), (first + 1, depth + 1)]
         assert sorted(seen + a["large"].tolist()) == list(range(n)) and deepest < 63
+
+
+REFERENCE = Path("/root/reference")
+
+
+@pytest.mark.reference
+@pytest.mark.skipif(not (REFERENCE / "ray_tracer").is_dir(), reason="the reference tree is only mounted in the build container")
+def test_scenes_built_from_the_reference_classes_flatten_identically():
+    """objects built with the REFERENCE's own classes (HEAD API, as main.py:11-51
+    builds them) feed the flattener by duck typing and give the table this package's classes give."""
+    sys.path.insert(0, str(REFERENCE))
+    try:
+        from ray_tracer.domain import Camera, DomeLight, PointLight, Scene3D
+        from ray_tracer.infrastructure.numpy.base import NumpyRGBColor, NumpyVector3D
+        from ray_tracer.infrastructure.numpy.shader import NumpyShader, Texture, TextureChecker
+        from ray_tracer.infrastructure.numpy.shape import NumpySphere
+    finally:
+        sys.path.remove(str(REFERENCE))
+    from python_ray_tracer_b200 import scenes
+    from python_ray_tracer_b200.infrastructure.flatten import flatten_scene
+
+    g = scenes.README_GAINS
+
+    def shader(texture):
+        return NumpyShader(g["reflection_gain"], g["specular_gain"], g["specular_roughness"], g["iridescence_gain"],
+                           g["diffuse_gain"], texture)
+
+    theirs = Scene3D(
+        [NumpySphere(NumpyVector3D(0.55, 0.5, 3), 1.0, shader(Texture(NumpyRGBColor(1, 0, 1)))),
+         NumpySphere(NumpyVector3D(-0.45, 0.1, 1), 0.4, shader(Texture(NumpyRGBColor(0.5, 0.5, 0.5)))),
+         NumpySphere(NumpyVector3D(0, -99999.5, 0), 99999, shader(TextureChecker()))],
+        [PointLight(NumpyVector3D(5, 10, -10)), DomeLight(0.1, NumpyRGBColor(1, 1, 1))],
+        Camera(NumpyVector3D(0, 0.2, -2), 1920, 1080))
+    a = flatten_scene(theirs)
+    b = flatten_scene(scenes.readme_scene(1920, 1080), __import__("python_ray_tracer_b200.infrastructure.flatten", fromlist=["DefaultMaterial"]).DefaultMaterial(**g))
+    assert np.array_equal(a.spheres, b.spheres) and np.array_equal(a.point_lights, b.point_lights)
+    assert a.eye == b.eye and a.dome_intensity == b.dome_intensity and a.dome_color == b.dome_color
+
+
+@pytest.mark.reference
+@pytest.mark.skipif(not (REFERENCE / "ray_tracer").is_dir(), reason="the reference tree is only mounted in the build container")
+def test_integration_stub_runs_verbatim_against_the_library(tmp_path):
+    """INTEGRATION.md section 2, executed as printed (only the library's path is made absolute): the
+    ctypes ``CudaRenderer(Renderer)`` a reference maintainer would add imports the reference's own port,
+    its struct matches the header as compiled, every symbol it binds exists, and -- without a GPU --
+    ``raytrace_scene`` comes back through the error path with the library's message."""
+    text = (ROOT / "INTEGRATION.md").read_text()
+    section = text[text.index("## 2."):text.index("## 3.")]
+    code = section[section.index("```python") + len("```python"):]
+    code = code[:code.index("```")]
+    assert 'C.CDLL("librt_b200.so")' in code
+    code = code.replace('C.CDLL("librt_b200.so")', f'C.CDLL("{abi.library_path()}")')
+    abi.load()
+    sys.path.insert(0, str(REFERENCE))
+    try:
+        ns = {}
+        exec(compile(code, "INTEGRATION.md#2", "exec"), ns)
+        assert ctypes.sizeof(ns["rt_env"]) == ctypes.sizeof(abi.RtEnv) and ctypes.sizeof(ns["rt_camera"]) == ctypes.sizeof(abi.RtCamera)
+        for (name, ctype), (name2, ctype2) in zip(ns["rt_env"]._fields_, abi.RtEnv._fields_):
+            assert name == name2 and ctypes.sizeof(ctype) == ctypes.sizeof(ctype2)
+        sys.path.insert(0, str(REFERENCE))
+        import importlib
+
+        main_scene = importlib.import_module("ray_tracer.domain")
+        from ray_tracer.infrastructure.numpy.base import NumpyRGBColor, NumpyVector3D
+        from ray_tracer.infrastructure.numpy.shader import NumpyShader, Texture, TextureChecker
+        from ray_tracer.infrastructure.numpy.shape import NumpySphere
+
+        scene = main_scene.Scene3D(
+            [NumpySphere(NumpyVector3D(0.55, 0.5, 3), 1.0, NumpyShader(0.0, 0, 0.01, 0, 0.0, Texture(NumpyRGBColor(1, 1, 1)))),
+             NumpySphere(NumpyVector3D(0, -99999.5, 0), 99999, NumpyShader(0.0, 0.1, 0.5, 0.0, 1.0, TextureChecker()))],
+            [main_scene.PointLight(NumpyVector3D(-2, 1, 2)), main_scene.DomeLight(0.1, NumpyRGBColor(1, 1, 1))],
+            main_scene.Camera(NumpyVector3D(0, 0.2, -2), 32, 18))
+        renderer = ns["CudaRenderer"]()
+        rays = renderer.get_ray_directions(scene.camera)
+        import torch
+
+        if torch.cuda.is_available():
+            color = renderer.raytrace_scene(scene.camera.position, rays, scene)
+            assert color.x.shape == (32 * 18,) and float(color.x.max()) > 0
+        else:
+            with pytest.raises(RuntimeError, match="CUDA device"):
+                renderer.raytrace_scene(scene.camera.position, rays, scene)
+    finally:
+        while str(REFERENCE) in sys.path:
+            sys.path.remove(str(REFERENCE))
