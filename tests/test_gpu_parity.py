@@ -577,6 +577,35 @@ def test_bvh_gives_the_same_picture_as_testing_every_sphere(precision, c_oracle)
     assert np.array_equal(_render(plain, case).numpy(), _render(tree, case).numpy())
 
 
+def test_camera_rays_that_do_not_start_at_the_scene_camera(rt, c_oracle):
+    """``raytrace_scene`` handed ``CameraRays`` of a camera that is NOT ``scene.camera``: the reference shades
+    "towards scene.camera.position" at every generation (shader.py:76) while the rays leave the other camera.
+    The camera kernel takes that direction from the ray, so such calls are traced as explicit rays instead
+    (the C entry point refuses them): fast and exact agree with each other and with the oracle."""
+    from python_ray_tracer_b200 import Camera, scenes
+    from python_ray_tracer_b200.infrastructure import NumpyVector3D
+    from python_ray_tracer_b200.infrastructure.cuda import abi
+
+    scene = scenes.readme_scene(96, 54)
+    other = Camera(NumpyVector3D(0.4, 0.5, -1.5), 96, 54)
+    got = {}
+    for precision in PRECISIONS:
+        renderer = rt(precision)
+        rays = renderer.get_ray_directions(other)
+        got[precision] = renderer.raytrace_scene(other.position, rays, scene).numpy()
+    flat = rt("exact").flatten(scene)
+    d = c_oracle.ray_directions((0.4, 0.5, -1.5), 96, 54)
+    want, _ = c_oracle.trace_rays(flat, (0.4, 0.5, -1.5), d)
+    assert_linear_parity(got["exact"], want, EXACT_TOL, "rays from another camera / exact")
+    assert_linear_parity(got["fast"], want, 1e-4, "rays from another camera / fast")
+    # the C entry point: camera rays must start at env->eye
+    lib = abi.load()
+    env = rt("fast")._plain_env(flat)
+    cam = abi.make_camera((0.4, 0.5, -1.5), 96, 54)
+    assert lib.rt_render_rows_dev(0, 8, flat.n_spheres, 8, C.byref(env), C.byref(cam), 0, 54, None, 0, 0, None, None, None) == -1
+    assert b"env->eye" in lib.rt_last_error()
+
+
 def test_a_blob_of_another_scene_fails_loudly(rt):
     """rt_env.accel_dev must be the blob of THIS sphere table: a launch given another scene's tree renders
     nothing and says so -- through rt_device_status() and through the next device call -- instead of
