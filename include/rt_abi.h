@@ -358,6 +358,37 @@ int rt_png_deflate_rows(const uint8_t* pixels, int32_t width, int32_t rows, int3
                         int64_t row_stride, int32_t last, uint8_t* out, int64_t capacity,
                         int64_t* bytes_out, uint32_t* adler_out, int64_t* raw_bytes_out);
 
+/*
+ * The same PNG, encoded ON THE DEVICE (csrc/rt_png_dev.cu): where the 8-bit image has to travel -- over PCIe to
+ * the host, over NVLink into rank 0's framebuffer -- it travels as the ~10x smaller file.  Sub filter, matches
+ * at distance 3, one fixed Huffman code; the image is cut into bands of rt_png_rows_per_band() rows, each of
+ * which becomes one IDAT chunk (with its own CRC-32), so bands are encoded independently -- by different thread
+ * blocks, and by different GPUs when a frame is sharded.  Decoded pixels equal the input.
+ *   rt_png_encode_bands_dev  encodes the bands of the `n_rows` rows at pixels_dev (8-bit, pixel_bytes = 3: R,G,B
+ *                            or 4: R,G,B,A with A dropped) into `scratch_dev` (rt_png_scratch_bytes(); device
+ *                            memory of `device` or of a peer: one slot per band of the IMAGE).  The rows are image
+ *                            rows row0.. (strip_step = 1) or the interleaved shard of rt_render_strips_dev (strips
+ *                            of strip_rows rows, every strip_step-th, starting at image row row0): strip_rows and
+ *                            row0 must then be multiples of rt_png_rows_per_band().
+ *   rt_png_pack_dev          once every band of the image is in scratch_dev: writes the file (signature, IHDR, the
+ *                            IDAT chunks in order, a tail chunk with the Adler-32, IEND) to png_out and its size to
+ *                            *png_bytes_out (0 if capacity was too small; rt_png_file_bound() always suffices).
+ *                            Both may be device memory or device-mapped (pinned) host memory.
+ * Both only enqueue work on `stream`.  rt_render_png_host: rt_render_frame_host + the two calls above; the file
+ * is all that crosses PCIe.
+ */
+int32_t rt_png_rows_per_band(int32_t width, int32_t height);
+int64_t rt_png_scratch_bytes(int32_t width, int32_t height);
+int64_t rt_png_file_bound(int32_t width, int32_t height);
+int rt_png_encode_bands_dev(int device, const uint8_t* pixels_dev, int32_t pixel_bytes, int64_t row_stride,
+                            int32_t n_rows, int32_t width, int32_t height, int32_t row0, int32_t strip_rows,
+                            int32_t strip_step, void* scratch_dev, int64_t scratch_bytes, void* stream);
+int rt_png_pack_dev(int device, int32_t width, int32_t height, const void* scratch_dev, uint8_t* png_out,
+                    int64_t capacity, uint64_t* png_bytes_out, void* stream);
+int rt_render_png_host(int device, const double* spheres_host, int32_t n_spheres,
+                       const double* point_lights_host, const rt_env* env, const rt_camera* cam,
+                       uint8_t* png_host, int64_t capacity, int64_t* png_bytes_out);
+
 #ifdef __cplusplus
 }
 #endif

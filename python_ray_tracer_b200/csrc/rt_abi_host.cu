@@ -28,7 +28,11 @@ struct DeviceCache {
     cudaStream_t stream = nullptr;       // uploads and kernels
     cudaStream_t copy_stream = nullptr;  // downloads, overlapped with the next chunk's kernel
     cudaEvent_t rendered[kMaxChunks] = {};
-    Scratch scene, rays, rgb, rgb8, stats, accel;
+    Scratch scene, rays, rgb, rgb8, stats, accel, png;
+    // pinned, device-mapped landing zone of rt_render_png_host (file + its size word) for callers whose own
+    // buffer the device cannot write
+    void* png_stage = nullptr;
+    size_t png_stage_bytes = 0;
 };
 
 thread_local DeviceCache g_cache[kMaxDevices];
@@ -150,6 +154,10 @@ int rt_release_cache(void) {
         release(c.rgb8);
         release(c.stats);
         release(c.accel);
+        release(c.png);
+        if (c.png_stage != nullptr) cudaFreeHost(c.png_stage);
+        c.png_stage = nullptr;
+        c.png_stage_bytes = 0;
         if (c.stream != nullptr) {
             cudaStreamDestroy(c.stream);
             cudaStreamDestroy(c.copy_stream);
@@ -255,6 +263,80 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
     if (stats_host != nullptr)
         HOST_CUDA(cudaMemcpyAsync(stats_host, c->stats.ptr, sizeof(uint64_t) * RT_STATS_WORDS, cudaMemcpyDeviceToHost, c->stream));
     HOST_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+// save_image's file without the 8-bit image ever leaving the device: trace (8-bit image only), encode the bands,
+// pack the file -- into the caller's buffer directly if it is pinned memory the device can address, into a
+// pinned staging buffer otherwise -- and wait once.
+int rt_render_png_host(int device, const double* spheres_host, int32_t n_spheres, const double* point_lights_host,
+                       const rt_env* env, const rt_camera* cam, uint8_t* png_host, int64_t capacity, int64_t* png_bytes_out) {
+    if (spheres_host == nullptr || point_lights_host == nullptr || env == nullptr || cam == nullptr || png_host == nullptr ||
+        png_bytes_out == nullptr || n_spheres <= 0 || env->n_point_lights < 1 || cam->width <= 0 || cam->height <= 0)
+        return host_fail(RT_ERR_BAD_ARG, "rt_render_png_host: NULL pointer or bad size");
+    const int64_t bound = rt_png_file_bound(cam->width, cam->height);
+    if (bound < 0) return host_fail(RT_ERR_UNSUPPORTED, "rt_render_png_host: rows wider than 21 666 pixels");
+    Restore restore;
+    DeviceCache* c = nullptr;
+    int rc = enter(device, restore, &c);
+    if (rc != RT_OK) return rc;
+    rt_env use;
+    if ((rc = attach_accel(*c, spheres_host, n_spheres, env, &use)) != RT_OK) return rc;
+    use.spheres_host = spheres_host;
+    use.point_lights_host = point_lights_host;
+    use.flags = (use.flags & ~RT_FLAG_IMAGE_ORDER) | RT_FLAG_RGB8;
+    const double *spheres_dev, *lights_dev;
+    if (rt_internal_small_scene(&use, n_spheres)) {
+        HOST_CUDA(reserve(c->scene, 256));
+        spheres_dev = lights_dev = static_cast<const double*>(c->scene.ptr);
+    } else if ((rc = upload_scene(*c, spheres_host, n_spheres, point_lights_host, env->n_point_lights, &spheres_dev, &lights_dev)) != RT_OK) {
+        return rc;
+    }
+    const int64_t n = (int64_t)cam->width * cam->height;
+    const int64_t scratch_bytes = rt_png_scratch_bytes(cam->width, cam->height);
+    HOST_CUDA(reserve(c->rgb8, (size_t)n * 3 + 16));
+    HOST_CUDA(reserve(c->png, (size_t)scratch_bytes));
+    // where the pack kernel writes: the caller's buffer if the device can address it (pinned host memory)
+    uint8_t* out_dev = nullptr;
+    unsigned long long* size_word = nullptr;
+    cudaPointerAttributes attr;
+    const bool direct = capacity >= 128 + 8 && cudaPointerGetAttributes(&attr, png_host) == cudaSuccess && attr.type == cudaMemoryTypeHost &&
+                        attr.devicePointer != nullptr;
+    cudaGetLastError();  // (an unregistered pointer is reported as an error by older runtimes: not ours)
+    const size_t stage_need = (size_t)bound + 64;
+    if (c->png_stage_bytes < (direct ? 64 : stage_need)) {
+        if (c->png_stage != nullptr) cudaFreeHost(c->png_stage);
+        c->png_stage = nullptr;
+        c->png_stage_bytes = 0;
+        HOST_CUDA(cudaHostAlloc(&c->png_stage, direct ? 64 : stage_need, cudaHostAllocMapped));
+        c->png_stage_bytes = direct ? 64 : stage_need;
+    }
+    void* stage_dev = nullptr;
+    HOST_CUDA(cudaHostGetDevicePointer(&stage_dev, c->png_stage, 0));
+    size_word = static_cast<unsigned long long*>(stage_dev);  // first 8 bytes of the staging area: the size
+    volatile unsigned long long* size_host = static_cast<volatile unsigned long long*>(c->png_stage);
+    *size_host = ~0ull;
+    int64_t out_capacity;
+    if (direct) {
+        out_dev = static_cast<uint8_t*>(attr.devicePointer);
+        out_capacity = capacity;
+    } else {
+        out_dev = static_cast<uint8_t*>(stage_dev) + 64;
+        out_capacity = (int64_t)c->png_stage_bytes - 64;
+    }
+    rc = rt_render_rows_dev(device, spheres_dev, n_spheres, lights_dev, &use, cam, 0, cam->height, nullptr, RT_DTYPE_F32, n,
+                            static_cast<uint8_t*>(c->rgb8.ptr), nullptr, c->stream);
+    if (rc != RT_OK) return rc;
+    rc = rt_png_encode_bands_dev(device, static_cast<const uint8_t*>(c->rgb8.ptr), 3, (int64_t)cam->width * 3, cam->height, cam->width,
+                                 cam->height, 0, cam->height, 1, c->png.ptr, scratch_bytes, c->stream);
+    if (rc == RT_OK) rc = rt_png_pack_dev(device, cam->width, cam->height, c->png.ptr, out_dev, out_capacity, reinterpret_cast<uint64_t*>(size_word), c->stream);
+    HOST_CUDA(cudaStreamSynchronize(c->stream));
+    if (rc != RT_OK) return rc;
+    const unsigned long long bytes = *size_host;
+    if (bytes == 0ull || bytes == ~0ull || (int64_t)bytes > capacity)
+        return host_fail(RT_ERR_BAD_ARG, "rt_render_png_host: png_host is too small for this frame (rt_png_file_bound always suffices)");
+    if (!direct) memcpy(png_host, static_cast<const uint8_t*>(c->png_stage) + 64, (size_t)bytes);
+    *png_bytes_out = (int64_t)bytes;
     return RT_OK;
 }
 

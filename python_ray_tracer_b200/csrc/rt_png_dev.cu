@@ -1,0 +1,744 @@
+// rt_png_dev.cu -- the PNG save_image writes (base.py:143-151), encoded ON THE DEVICE.
+//
+// The reference hands its 8-bit array to Pillow (zlib level 6: 0.45 s per 1080p frame on one core).  Once the
+// frame is traced in ~0.06 ms the 8-bit image itself is the bottleneck wherever it has to travel: 6.2 MB over
+// PCIe to the host (0.11 ms), 87 MB over NVLink into rank 0 when eight GPUs share an 8K frame (0.11 ms at best),
+// 2.5 ms of host deflate on eight cores.  So the file is made where the pixels are.  Rendered frames compress
+// ~10:1 with very little work (rt_png_host.cpp does the same on the host):
+//   * PNG filter 1 (Sub) on every row: flat areas become zeros, gradients small residuals;
+//   * matches only at distance 3 (a run of one RGB residual; a run of one byte is one too from its fourth
+//     byte on), at least 3 long, cut at 258: found by comparing with the byte three behind, no hashing;
+//   * ONE fixed Huffman code (rt_png_table.h, made from the token statistics of rendered frames by
+//     tools/png_static_table.py) sent in every band's dynamic-block header: no histogram, no tree building;
+//   * a band that would grow is stored instead.
+// The image is cut into bands of a few rows, one thread block each.  A band is one byte stream; every thread owns
+// a contiguous piece of it.  Whether a byte continues a run, where its run began and ends, and therefore which
+// token covers it, follow from two small scans over the threads' summaries; bit positions from a third.  Every
+// band becomes one IDAT chunk (PNG allows any number): its deflate block ends byte-aligned on an empty stored
+// block (BFINAL = 0), its CRC-32 is computed by the block that made it, so nothing serial is left but the
+// Adler-32 of the whole image (combined from the bands' sums) in a 9-byte tail chunk.  A second small kernel packs
+// the chunks, header and tail into one contiguous file -- in device memory or straight into mapped host memory.
+// What a consumer compares is the decoded image, which does not depend on the encoder (tests decode with zlib).
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/rt_abi.h"
+#include "rt_png_table.h"
+
+extern "C" void rt_internal_set_error(const char* message);
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kHeaderWords = 40;       // the dynamic-block header, LSB-first, at most 1280 bits
+constexpr uint32_t kCrcPoly = 0xedb88320u;
+constexpr uint32_t kAdlerMod = 65521u;
+constexpr int kChunkOverhead = 12;     // length + type + CRC
+constexpr int kBandSlack = 64;         // stored-block header, zlib header, sync block, rounding
+
+// a(x) * b(x) mod the CRC-32 polynomial, reflected bit order (zlib crc32.c: multmodp)
+__host__ __device__ inline uint32_t multmodp(uint32_t a, uint32_t b) {
+    uint32_t m = 1u << 31, p = 0;
+    for (;;) {
+        if (a & m) {
+            p ^= b;
+            if ((a & (m - 1)) == 0) break;
+        }
+        m >>= 1;
+        b = b & 1u ? (b >> 1) ^ kCrcPoly : b >> 1;
+    }
+    return p;
+}
+// x^(n * 2^k) mod the polynomial
+__host__ __device__ inline uint32_t x2nmodp(const uint32_t* x2n, uint64_t n, unsigned k) {
+    uint32_t p = 1u << 31;  // x^0
+    while (n) {
+        if (n & 1) p = multmodp(x2n[k & 31], p);
+        n >>= 1;
+        k++;
+    }
+    return p;
+}
+
+// Everything of the code a block needs, as a kernel parameter (constant bank), copied to shared memory for
+// indexed access.  Entries: bits | count << 24, bits already reversed for the LSB-first stream.
+struct PngCode {
+    uint32_t lit[256];        // literal byte
+    uint32_t match[256];      // match of length 3 + index: length symbol, its extra bits, the 1-bit distance code
+    uint32_t eob;             // end of block
+    uint32_t header[kHeaderWords];
+    uint32_t header_bits;
+    uint32_t x2n[32];         // x^(2^k) mod the CRC-32 polynomial (zlib's crc32_combine arithmetic)
+};
+
+struct BandJob {
+    const uint8_t* pixels;    // first row of the launch's pixel buffer
+    long long row_stride;     // bytes between rows of that buffer
+    int pixel_bytes;          // 3 or 4 (alpha skipped)
+    int width, height;        // of the IMAGE
+    int rows_per_band;
+    int n_rows;               // rows in the pixel buffer
+    // local row r of the buffer is image row row0 + r + (r / strip_rows) * (strip_step - 1) * strip_rows
+    // (a contiguous band: strip_step = 1; an interleaved shard of a frame rendered by several GPUs otherwise);
+    // strip_rows is a multiple of rows_per_band, so a band never straddles two strips
+    int row0, strip_rows, strip_step;
+    uint8_t* slots;           // band b of the IMAGE writes its chunk at slots + b * slot_bytes (may be peer memory)
+    long long slot_bytes;
+    uint32_t* sizes;          // [n_bands_of_image] bytes of band b's chunk
+    uint32_t* adlers;         // [n_bands_of_image] Adler-32 of band b's filtered bytes (as if it started a stream)
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// host: the fixed code
+// ---------------------------------------------------------------------------------------------------------------
+void canonical(const uint8_t* len, int n, uint16_t* code) {  // RFC 1951 3.2.2, bit-reversed
+    int count[16] = {0}, next[16] = {0};
+    for (int s = 0; s < n; ++s) count[len[s]]++;
+    count[0] = 0;
+    int c = 0;
+    for (int b = 1; b <= 15; ++b) {
+        c = (c + count[b - 1]) << 1;
+        next[b] = c;
+    }
+    for (int s = 0; s < n; ++s) {
+        const int l = len[s];
+        int v = l ? next[l]++ : 0, r = 0;
+        for (int i = 0; i < l; ++i) {
+            r = (r << 1) | (v & 1);
+            v >>= 1;
+        }
+        code[s] = (uint16_t)r;
+    }
+}
+
+struct HostBits {
+    uint32_t words[kHeaderWords] = {0};
+    uint32_t n = 0;
+    bool overflow = false;
+    void put(uint32_t bits, int count) {
+        for (int i = 0; i < count; ++i, ++n) {
+            if (n >= 32u * kHeaderWords) {
+                overflow = true;
+                return;
+            }
+            if ((bits >> i) & 1u) words[n >> 5] |= 1u << (n & 31);
+        }
+    }
+};
+
+const PngCode& png_code() {
+    static PngCode code;
+    static bool made = false;
+    if (made) return code;
+    static const int base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
+    static const int bits[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
+    uint16_t lit_code[286];
+    canonical(rt::kPngLitLen, 286, lit_code);
+    // distances: codes 0 and 2 with one bit each (a complete code); only code 2 (distance 3, no extra bits) is used
+    const uint8_t dist_len[3] = {1, 0, 1};
+    uint16_t dist_code[3];
+    canonical(dist_len, 3, dist_code);
+    for (int v = 0; v < 256; ++v) code.lit[v] = (uint32_t)lit_code[v] | ((uint32_t)rt::kPngLitLen[v] << 24);
+    for (int len = 3; len <= 258; ++len) {
+        int k = 28;
+        while (base[k] > len) --k;
+        if (len != 258 && k == 28) k = 27;  // 258 has its own symbol; 227..257 belong to symbol 284
+        const int sym = 257 + k;
+        uint32_t v = lit_code[sym];
+        int n = rt::kPngLitLen[sym];
+        v |= (uint32_t)(len - base[k]) << n;
+        n += bits[k];
+        v |= (uint32_t)dist_code[2] << n;
+        n += dist_len[2];
+        code.match[len - 3] = v | ((uint32_t)n << 24);
+    }
+    code.eob = (uint32_t)lit_code[256] | ((uint32_t)rt::kPngLitLen[256] << 24);
+    // ---- the block header: BFINAL = 0, BTYPE = 2, the code lengths run-length coded (symbol 16: repeat the
+    // previous length 3..6 times), themselves Huffman coded by a code built here
+    struct Sym {
+        int sym, extra, extra_bits;
+    };
+    static Sym seq[400];
+    int n_seq = 0;
+    uint8_t all[286 + 3];
+    memcpy(all, rt::kPngLitLen, 286);
+    memcpy(all + 286, dist_len, 3);
+    for (int i = 0; i < 289;) {
+        int run = 1;
+        while (i + run < 289 && all[i + run] == all[i]) ++run;
+        seq[n_seq++] = {all[i], 0, 0};
+        int left = run - 1;
+        if (all[i] == 0) {  // (only the unused distance code: a single zero)
+            i += 1;
+            continue;
+        }
+        while (left >= 3) {
+            const int r = left > 6 ? 6 : left;
+            seq[n_seq++] = {16, r - 3, 2};
+            left -= r;
+        }
+        for (; left > 0; --left) seq[n_seq++] = {all[i], 0, 0};
+        i += run;
+    }
+    uint32_t freq[19] = {0};
+    for (int i = 0; i < n_seq; ++i) freq[seq[i].sym]++;
+    // code-length code (<= 7 bits): 19 symbols, plain Huffman by repeated merging of the two rarest; a tree
+    // deeper than 7 is rebuilt from a flattened histogram
+    uint8_t cl_len[19] = {0};
+    for (bool fits = false; !fits;) {
+        memset(cl_len, 0, sizeof(cl_len));
+        struct Node {
+            uint32_t w;
+            int left, right;
+        } nodes[40];
+        int alive[40], n_alive = 0, n_nodes = 0;
+        for (int s = 0; s < 19; ++s)
+            if (freq[s]) {
+                nodes[n_nodes] = {freq[s], -1 - s, 0};
+                alive[n_alive++] = n_nodes++;
+            }
+        while (n_alive > 1) {
+            int a = 0, b = 1;
+            if (nodes[alive[b]].w < nodes[alive[a]].w) a = 1, b = 0;
+            for (int i = 2; i < n_alive; ++i) {
+                if (nodes[alive[i]].w < nodes[alive[a]].w) b = a, a = i;
+                else if (nodes[alive[i]].w < nodes[alive[b]].w) b = i;
+            }
+            nodes[n_nodes] = {nodes[alive[a]].w + nodes[alive[b]].w, alive[a], alive[b]};
+            const int hi = a > b ? a : b, lo = a > b ? b : a;
+            alive[hi] = alive[--n_alive];
+            alive[lo] = n_nodes++;
+        }
+        int depth[40] = {0};
+        for (int i = n_nodes - 1; i >= 0; --i)
+            if (nodes[i].left >= 0) depth[nodes[i].left] = depth[nodes[i].right] = depth[i] + 1;
+            else cl_len[-1 - nodes[i].left] = (uint8_t)(depth[i] ? depth[i] : 1);
+        fits = true;
+        for (int k = 0; k < 19; ++k) fits = fits && cl_len[k] <= 7;
+        if (!fits)
+            for (int k = 0; k < 19; ++k) freq[k] = freq[k] ? (freq[k] + 1) / 2 : 0;
+    }
+    uint16_t cl_code[19];
+    canonical(cl_len, 19, cl_code);
+    HostBits hb;
+    hb.put(0u, 1);
+    hb.put(2u, 2);
+    hb.put(286 - 257, 5);
+    hb.put(3 - 1, 5);
+    hb.put(19 - 4, 4);
+    static const int order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+    for (int k = 0; k < 19; ++k) hb.put(cl_len[order[k]], 3);
+    for (int i = 0; i < n_seq; ++i) {
+        hb.put(cl_code[seq[i].sym], cl_len[seq[i].sym]);
+        if (seq[i].extra_bits) hb.put((uint32_t)seq[i].extra, seq[i].extra_bits);
+    }
+    memcpy(code.header, hb.words, sizeof(code.header));
+    code.header_bits = hb.overflow ? 0u : hb.n;  // 0 = the header did not fit: every band is stored
+    uint32_t p = 1u << 30;  // x^1
+    code.x2n[0] = p;
+    for (int k = 1; k < 32; ++k) code.x2n[k] = p = multmodp(p, p);
+    made = true;
+    return code;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// device: one band -> one IDAT chunk
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int job_image_row(const BandJob& j, int local_row) {
+    return j.strip_step == 1 ? j.row0 + local_row
+                             : j.row0 + local_row + (local_row / j.strip_rows) * (j.strip_step - 1) * j.strip_rows;
+}
+
+// exclusive prefix sum over the block's kThreads values; *total = their sum.  `scratch`: kThreads / 32 + 1 words.
+__device__ __forceinline__ uint32_t block_exclusive_sum(uint32_t v, uint32_t* scratch, uint32_t* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += up;
+    }
+    __syncthreads();  // scratch may still be read from the previous use
+    if (lane == 31) scratch[warp] = inc;
+    __syncthreads();
+    uint32_t before = 0, all = 0;
+    for (int w = 0; w < kThreads / 32; ++w) {
+        const uint32_t s = scratch[w];
+        if (w < warp) before += s;
+        all += s;
+    }
+    *total = all;
+    return before + inc - v;
+}
+__device__ __forceinline__ unsigned long long block_sum64(unsigned long long v, unsigned long long* scratch) {
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = v;
+    __syncthreads();
+    unsigned long long all = 0;
+    for (int w = 0; w < kThreads / 32; ++w) all += scratch[w];
+    return all;
+}
+
+// LSB-first bit writer of one thread into the block's output words.  A thread's tokens are contiguous in the
+// stream, but its first and last words are shared with its neighbours (and a thread may emit fewer than 32
+// bits), so every word goes out with an atomic OR into the zeroed buffer.
+struct BitSink {
+    uint32_t* words;
+    unsigned long long acc;
+    uint32_t w;
+    int n;
+    __device__ __forceinline__ BitSink(uint32_t* out_words, uint32_t bit) : words(out_words), acc(0), w(bit >> 5), n((int)(bit & 31u)) {}
+    __device__ __forceinline__ void put(uint32_t entry) {  // bits | count << 24
+        acc |= (unsigned long long)(entry & 0xffffffu) << n;
+        n += (int)(entry >> 24);
+        if (n >= 32) {
+            atomicOr(words + w, (uint32_t)acc);
+            acc >>= 32;
+            n -= 32;
+            ++w;
+        }
+    }
+    __device__ __forceinline__ void flush() {
+        if (n > 0 && (uint32_t)acc != 0u) atomicOr(words + w, (uint32_t)acc);
+    }
+};
+struct BitCount {
+    uint32_t bits = 0;
+    __device__ __forceinline__ void put(uint32_t entry) { bits += entry >> 24; }
+};
+
+// The tokens whose first byte lies in [a, b) of the band's stream S.  m(i) = "S[i] equals S[i - 3]".  run_in =
+// how many bytes just before a continue a run into a; run_out = how many from b on continue the run that
+// reaches b.  A run is cut into chunks of 258 from its start; a chunk of at least 3 bytes is one match token
+// (emitted by the thread that owns its first byte), a shorter one is literals.
+template <class Sink>
+__device__ __forceinline__ void walk_tokens(const uint8_t* S, int a, int b, int run_in, int run_out, const uint32_t* lit,
+                                            const uint32_t* match, Sink& sink) {
+    int i = a;
+    while (i < b) {
+        const bool mi = i >= 3 && S[i] == S[i - 3];
+        if (!mi) {
+            sink.put(lit[S[i]]);
+            ++i;
+            continue;
+        }
+        int j = i + 1;
+        while (j < b && S[j] == S[j - 3]) ++j;
+        const int off = i == a ? run_in : 0;                       // offset of byte i in its run
+        const int runlen = off + (j - i) + (j == b ? run_out : 0); // the whole run
+        const int mine_end = off + (j - i);                        // my part: run offsets [off, mine_end)
+        int o = off, pos = i;
+        while (o < mine_end) {
+            const int cs = (o / 258) * 258;
+            const int cl = min(258, runlen - cs);
+            const int take = min(cs + cl, mine_end) - o;
+            if (cl >= 3) {
+                if (o == cs) sink.put(match[cl - 3]);
+            } else {
+                for (int q = 0; q < take; ++q) sink.put(lit[S[pos + q]]);
+            }
+            o += take;
+            pos += take;
+        }
+        i = j;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constant__ PngCode code, const __grid_constant__ BandJob job) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ uint32_t s_lit[256], s_match[256], s_crc[256], s_x2n[32];
+    __shared__ uint32_t s_len[kThreads], s_lead[kThreads], s_trail[kThreads];
+    __shared__ uint32_t s_scan[kThreads / 32 + 1];
+    __shared__ unsigned long long s_sum[kThreads / 32];
+    __shared__ uint32_t s_g[9], s_part[kThreads];
+
+    const int t = threadIdx.x;
+    const int line = 1 + 3 * job.width;
+    const int first_local = blockIdx.x * job.rows_per_band;
+    const int first_image = job_image_row(job, first_local);
+    const int band = first_image / job.rows_per_band;
+    const int rows = min(job.rows_per_band, min(job.n_rows - first_local, job.height - first_image));
+    const int n = rows * line;                               // bytes of the band's stream
+    const int cap = job.rows_per_band * line;
+    uint8_t* filt = smem;                                    // [cap] the filtered rows
+    uint8_t* out = smem + ((cap + 15) & ~15);                // the chunk: length, type, data, CRC
+    uint32_t* out_words = reinterpret_cast<uint32_t*>(out);
+    const int out_words_n = (cap + kBandSlack + kChunkOverhead + 3) / 4;
+
+    s_lit[t] = code.lit[t];
+    s_match[t] = code.match[t];
+    {
+        uint32_t c = (uint32_t)t;
+        for (int k = 0; k < 8; ++k) c = c & 1u ? (c >> 1) ^ kCrcPoly : c >> 1;
+        s_crc[t] = c;
+    }
+    if (t < 32) s_x2n[t] = code.x2n[t];
+    for (int i = t; i < out_words_n; i += kThreads) out_words[i] = 0u;
+
+    // ---- filter 1 (Sub): byte minus the byte of the pixel to the left; Adler-32 sums on the way
+    unsigned long long s1 = 0, s2 = 0;
+    for (int r = 0; r < rows; ++r) {
+        const uint8_t* src = job.pixels + (long long)(first_local + r) * job.row_stride;
+        uint8_t* dst = filt + r * line;
+        if (t == 0) {
+            dst[0] = 1;
+            s1 += 1u;
+            s2 += (unsigned long long)(r * line);
+        }
+        for (int x = t; x < 3 * job.width; x += kThreads) {
+            const int px = x / 3, ch = x - 3 * px;
+            const uint8_t cur = __ldg(src + (long long)px * job.pixel_bytes + ch);
+            const uint8_t left = px > 0 ? __ldg(src + (long long)(px - 1) * job.pixel_bytes + ch) : (uint8_t)0;
+            const uint8_t v = (uint8_t)(cur - left);
+            dst[1 + x] = v;
+            s1 += v;
+            s2 += (unsigned long long)(r * line + 1 + x) * v;
+        }
+    }
+    s1 = block_sum64(s1, s_sum);
+    s2 = block_sum64(s2, s_sum);  // (block_sum64 synchronises: filt is complete from here on)
+    const uint32_t adler_a = (uint32_t)((1ull + s1) % kAdlerMod);
+    const uint32_t adler_b = (uint32_t)((((unsigned long long)n % kAdlerMod) + ((unsigned long long)n % kAdlerMod) * (s1 % kAdlerMod) +
+                                         (unsigned long long)kAdlerMod - (s2 % kAdlerMod)) % kAdlerMod);
+
+    // ---- every thread's piece of the stream and what it knows about runs at its ends
+    const int piece = (n + kThreads - 1) / kThreads;
+    const int a = min(t * piece, n), b = min(a + piece, n);
+    {
+        int lead = 0;
+        while (a + lead < b && a + lead >= 3 && filt[a + lead] == filt[a + lead - 3]) ++lead;
+        int trail = 0;
+        while (b - 1 - trail >= a && b - 1 - trail >= 3 && filt[b - 1 - trail] == filt[b - 4 - trail]) ++trail;
+        s_len[t] = (uint32_t)(b - a);
+        s_lead[t] = (uint32_t)lead;
+        s_trail[t] = (uint32_t)trail;
+    }
+    __syncthreads();
+    int run_in = 0, run_out = 0;
+    for (int u = t - 1; u >= 0; --u) {  // (long runs span many pieces: black sky; bounded by kThreads steps)
+        run_in += (int)s_trail[u];
+        if (s_trail[u] != s_len[u]) break;
+    }
+    for (int u = t + 1; u < kThreads; ++u) {
+        run_out += (int)s_lead[u];
+        if (s_lead[u] != s_len[u]) break;
+    }
+
+    // ---- bit positions
+    BitCount counter;
+    walk_tokens(filt, a, b, run_in, run_out, s_lit, s_match, counter);
+    uint32_t token_bits = 0;
+    const uint32_t my_bit = block_exclusive_sum(counter.bits, s_scan, &token_bits);
+    const int prefix = band == 0 ? 2 : 0;  // the zlib header travels in the first band's chunk
+    const int data0 = 8 + prefix;
+    const uint32_t block_bits = code.header_bits + token_bits + (code.eob >> 24) + 3u;  // + the sync block's header
+    const uint32_t deflated = (block_bits + 7u) / 8u + 4u;  // ... its LEN / NLEN
+    const bool stored = code.header_bits == 0u || deflated >= (uint32_t)n + 5u;
+    int data_len;
+    if (!stored) {
+        const uint32_t bit0 = 8u * (uint32_t)data0;
+        if (t < kHeaderWords && code.header[t] != 0u) {
+            // the header starts byte-aligned at bit0, which need not be word-aligned
+            const unsigned long long v = (unsigned long long)code.header[t] << (bit0 & 31u);
+            const uint32_t w = (bit0 >> 5) + (uint32_t)t;
+            atomicOr(out_words + w, (uint32_t)v);
+            if ((uint32_t)(v >> 32) != 0u) atomicOr(out_words + w + 1, (uint32_t)(v >> 32));
+        }
+        BitSink sink(out_words, bit0 + code.header_bits + my_bit);
+        walk_tokens(filt, a, b, run_in, run_out, s_lit, s_match, sink);
+        if (t == kThreads - 1) sink.put(code.eob);  // the last piece ends the stream (empty pieces included)
+        sink.flush();
+        data_len = prefix + (int)deflated;
+    } else {
+        for (int i = t; i < n; i += kThreads) out[data0 + 5 + i] = filt[i];
+        data_len = prefix + 5 + n;
+    }
+    __syncthreads();
+    if (t == 0) {
+        if (prefix) out[8] = 0x78, out[9] = 0x01;  // zlib header: deflate, 32 KB window, no preset dictionary, fastest
+        if (stored) {
+            out[data0] = 0;  // BFINAL = 0, BTYPE = 00
+            out[data0 + 1] = (uint8_t)(n & 255), out[data0 + 2] = (uint8_t)(n >> 8);
+            out[data0 + 3] = (uint8_t)(~n & 255), out[data0 + 4] = (uint8_t)((~n >> 8) & 255);
+        } else {
+            // the empty stored block that byte-aligns the band: its three header bits are zero already
+            uint8_t* sync = out + 8 + data_len - 4;
+            sync[0] = 0, sync[1] = 0, sync[2] = 0xff, sync[3] = 0xff;
+        }
+        out[0] = (uint8_t)(data_len >> 24), out[1] = (uint8_t)(data_len >> 16), out[2] = (uint8_t)(data_len >> 8), out[3] = (uint8_t)data_len;
+        out[4] = 'I', out[5] = 'D', out[6] = 'A', out[7] = 'T';
+    }
+    __syncthreads();
+
+    // ---- CRC-32 of type + data: slices aligned to the END (every slice but the first has exactly `slice` bytes),
+    // each thread its slice's CRC, then a tree of crc32_combine steps: crc(A B) = crc(A) x^(8 |B|) + crc(B)
+    const int n_crc = 4 + data_len;
+    const int slice = (n_crc + kThreads - 1) / kThreads;
+    {
+        const int end = n_crc - (kThreads - 1 - t) * slice, begin = max(end - slice, 0);
+        uint32_t c = 0u;
+        if (end > begin) {
+            c = 0xffffffffu;
+            for (int i = begin; i < end; ++i) c = s_crc[(c ^ out[4 + i]) & 255u] ^ (c >> 8);
+            c ^= 0xffffffffu;
+        }
+        s_part[t] = c;
+    }
+    if (t == 0) {
+        uint32_t g = x2nmodp(s_x2n, (uint64_t)slice, 3);  // x^(8 slice)
+        for (int l = 0; l < 9; ++l) {
+            s_g[l] = g;
+            g = multmodp(g, g);
+        }
+    }
+    __syncthreads();
+    for (int l = 0, stride = 1; stride < kThreads; ++l, stride <<= 1) {
+        if ((t & (2 * stride - 1)) == 0) s_part[t] = multmodp(s_g[l], s_part[t]) ^ s_part[t + stride];
+        __syncthreads();
+    }
+    if (t == 0) {
+        const uint32_t crc = s_part[0];
+        uint8_t* p = out + 8 + data_len;
+        p[0] = (uint8_t)(crc >> 24), p[1] = (uint8_t)(crc >> 16), p[2] = (uint8_t)(crc >> 8), p[3] = (uint8_t)crc;
+        job.sizes[band] = (uint32_t)(kChunkOverhead + data_len);
+        job.adlers[band] = (adler_b << 16) | adler_a;
+    }
+    __syncthreads();
+    // ---- the finished chunk to its slot (whole words; the slot is word-aligned and has the slack)
+    uint32_t* slot = reinterpret_cast<uint32_t*>(job.slots + (long long)band * job.slot_bytes);
+    const int chunk_words = (kChunkOverhead + data_len + 3) / 4;
+    for (int i = t; i < chunk_words; i += kThreads) slot[i] = out_words[i];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// device: the chunks of all bands -> one contiguous PNG file
+// ---------------------------------------------------------------------------------------------------------------
+struct PackJob {
+    const uint8_t* slots;
+    long long slot_bytes;
+    const uint32_t* sizes;
+    const uint32_t* adlers;
+    int n_bands;
+    int band_bytes;        // filtered bytes of a full band (rows_per_band * (1 + 3 width))
+    long long raw_bytes;   // filtered bytes of the whole image
+    uint8_t head[33];      // signature + IHDR chunk
+    uint8_t* out;          // the file: device memory or mapped host memory
+    long long capacity;
+    unsigned long long* bytes_out;  // its size (0 if it did not fit)
+};
+
+__global__ void __launch_bounds__(kThreads) png_pack_kernel(const __grid_constant__ PackJob job) {
+    __shared__ unsigned long long s_sum[kThreads / 32];
+    const int t = threadIdx.x, b = blockIdx.x;
+    // where this band's chunk goes: after the head and the chunks of the bands before it
+    unsigned long long before = 0, all = 0;
+    for (int j = t; j < job.n_bands; j += kThreads) {
+        const unsigned long long s = job.sizes[j];
+        all += s;
+        if (j < b) before += s;
+    }
+    before = block_sum64(before, s_sum);
+    all = block_sum64(all, s_sum);
+    const unsigned long long total = 33ull + all + 21ull + 12ull;  // head, bands, tail chunk (9 data bytes), IEND
+    const bool fits = total <= (unsigned long long)job.capacity;
+    if (fits) {
+        const uint8_t* src = job.slots + (long long)b * job.slot_bytes;
+        uint8_t* dst = job.out + 33 + before;
+        const int size = (int)job.sizes[b];
+        // word copies where the destination allows (the slots are word-aligned), bytes otherwise
+        if (((uintptr_t)dst & 3) == 0) {
+            const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src);
+            uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
+            for (int i = t; i < size / 4; i += kThreads) d4[i] = s4[i];
+            for (int i = (size & ~3) + t; i < size; i += kThreads) dst[i] = src[i];
+        } else {
+            for (int i = t; i < size; i += kThreads) dst[i] = src[i];
+        }
+    }
+    if (b == 0 && fits)
+        for (int i = t; i < 33; i += kThreads) job.out[i] = job.head[i];
+    if (b != job.n_bands - 1) return;
+    // ---- the last block: Adler-32 of the whole image from the bands' sums, the tail chunk, IEND, the size.
+    // A band that starts at offset O in a stream of N bytes, with sums (a, b) taken as if it started a stream
+    // and n bytes, adds a - 1 to A and (b - n) + (N - O - n) (a - 1) to B;  A = 1 + sum, B = N + sum.
+    unsigned long long A = 0, B = 0;
+    for (int j = t; j < job.n_bands; j += kThreads) {
+        const uint32_t ad = job.adlers[j];
+        const unsigned long long a1 = ((ad & 0xffffu) + kAdlerMod - 1u) % kAdlerMod, bj = ad >> 16;
+        const long long start = (long long)j * job.band_bytes;
+        const long long n = (j == job.n_bands - 1) ? job.raw_bytes - start : job.band_bytes;
+        const unsigned long long after = (unsigned long long)(job.raw_bytes - start - n) % kAdlerMod;
+        A += a1;
+        B += (bj + kAdlerMod - (unsigned long long)(n % kAdlerMod)) % kAdlerMod + (after * a1) % kAdlerMod;
+    }
+    A = block_sum64(A, s_sum);
+    B = block_sum64(B, s_sum);
+    if (t != 0) return;
+    if (!fits) {
+        *job.bytes_out = 0ull;
+        return;
+    }
+    const uint32_t adler_a = (uint32_t)((1ull + A) % kAdlerMod);
+    const uint32_t adler_b = (uint32_t)(((unsigned long long)(job.raw_bytes % kAdlerMod) + B) % kAdlerMod);
+    uint8_t tail[21 + 12] = {0, 0, 0, 9, 'I', 'D', 'A', 'T',
+                             0x01, 0x00, 0x00, 0xff, 0xff,  // the final block: stored, empty, BFINAL = 1
+                             (uint8_t)(adler_b >> 8), (uint8_t)adler_b, (uint8_t)(adler_a >> 8), (uint8_t)adler_a,
+                             0, 0, 0, 0,
+                             0, 0, 0, 0, 'I', 'E', 'N', 'D', 0xae, 0x42, 0x60, 0x82};
+    uint32_t c = 0xffffffffu;
+    for (int i = 4; i < 17; ++i) {
+        c ^= tail[i];
+        for (int k = 0; k < 8; ++k) c = c & 1u ? (c >> 1) ^ kCrcPoly : c >> 1;
+    }
+    c ^= 0xffffffffu;
+    tail[17] = (uint8_t)(c >> 24), tail[18] = (uint8_t)(c >> 16), tail[19] = (uint8_t)(c >> 8), tail[20] = (uint8_t)c;
+    uint8_t* dst = job.out + 33 + all;
+    for (int i = 0; i < 33; ++i) dst[i] = tail[i];
+    __threadfence_system();
+    *job.bytes_out = total;
+}
+
+uint32_t host_crc32(const uint8_t* p, size_t n) {
+    uint32_t c = 0xffffffffu;
+    for (size_t i = 0; i < n; ++i) {
+        c ^= p[i];
+        for (int k = 0; k < 8; ++k) c = c & 1u ? (c >> 1) ^ kCrcPoly : c >> 1;
+    }
+    return c ^ 0xffffffffu;
+}
+
+int png_fail(int status, const char* message) {
+    rt_internal_set_error(message);
+    return status;
+}
+
+// Rows per band: about two bands per SM (one wave of blocks), a divisor of 16 (the strip height of the multi-GPU
+// partition: a band never straddles two strips), and small enough for the band to fit shared memory twice over
+// and a stored block (65 535 bytes).
+int rows_per_band(int width, int height) {
+    const long long line = 1 + 3ll * width;
+    int r = 16;
+    while (r > 1 && ((long long)height + r - 1) / r < 2 * 148) r >>= 1;
+    if (((long long)height + r - 1) / r < 148 && r > 1) r >>= 1;
+    while (r > 1 && (r * line > 40000)) r >>= 1;
+    return r;
+}
+size_t band_smem(int width, int rows) {
+    const size_t cap = (size_t)rows * (1 + 3 * (size_t)width);
+    return ((cap + 15) & ~(size_t)15) + ((cap + kBandSlack + kChunkOverhead + 3) / 4) * 4 + 16;
+}
+long long slot_bytes_of(int width, int rows) {
+    const long long cap = (long long)rows * (1 + 3ll * width);
+    return (cap + kBandSlack + kChunkOverhead + 15) & ~15ll;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t rt_png_rows_per_band(int32_t width, int32_t height) {
+    if (width <= 0 || height <= 0 || 1 + 3ll * width > 65000) return -1;
+    return rows_per_band(width, height);
+}
+
+int64_t rt_png_scratch_bytes(int32_t width, int32_t height) {
+    if (rt_png_rows_per_band(width, height) < 0) return -1;
+    const int r = rows_per_band(width, height);
+    const long long bands = (height + r - 1) / r;
+    return bands * slot_bytes_of(width, r) + bands * 8 + 64;
+}
+
+int64_t rt_png_file_bound(int32_t width, int32_t height) {
+    if (rt_png_rows_per_band(width, height) < 0) return -1;
+    const int r = rows_per_band(width, height);
+    const long long bands = (height + r - 1) / r;
+    return 33 + bands * (slot_bytes_of(width, r)) + 33;
+}
+
+int rt_png_encode_bands_dev(int device, const uint8_t* pixels_dev, int32_t pixel_bytes, int64_t row_stride, int32_t n_rows,
+                            int32_t width, int32_t height, int32_t row0, int32_t strip_rows, int32_t strip_step,
+                            void* scratch_dev, int64_t scratch_bytes, void* stream) {
+    if (pixels_dev == nullptr || scratch_dev == nullptr || (pixel_bytes != 3 && pixel_bytes != 4) || width <= 0 || height <= 0 ||
+        n_rows < 0 || row_stride < (int64_t)width * pixel_bytes || row0 < 0 || strip_rows <= 0 || strip_step <= 0)
+        return png_fail(RT_ERR_BAD_ARG, "rt_png_encode_bands_dev: NULL pointer or bad size");
+    if (rt_png_rows_per_band(width, height) < 0)
+        return png_fail(RT_ERR_UNSUPPORTED, "rt_png_encode_bands_dev: rows wider than 21 666 pixels do not fit a stored block");
+    if (scratch_bytes < rt_png_scratch_bytes(width, height)) return png_fail(RT_ERR_BAD_ARG, "rt_png_encode_bands_dev: scratch smaller than rt_png_scratch_bytes");
+    const int r = rows_per_band(width, height);
+    if (strip_step > 1 && (strip_rows % r != 0 || row0 % r != 0))
+        return png_fail(RT_ERR_BAD_ARG, "rt_png_encode_bands_dev: strips must be whole bands (rt_png_rows_per_band)");
+    if (strip_step == 1 && row0 % r != 0) return png_fail(RT_ERR_BAD_ARG, "rt_png_encode_bands_dev: row0 must be a multiple of rt_png_rows_per_band");
+    if (n_rows == 0) return RT_OK;
+    int previous = -1;
+    cudaGetDevice(&previous);
+    if (previous != device && cudaSetDevice(device) != cudaSuccess) return png_fail(RT_ERR_NO_DEVICE, "rt_png_encode_bands_dev: cudaSetDevice failed");
+    const long long bands = (height + r - 1) / r;
+    BandJob job;
+    job.pixels = pixels_dev;
+    job.row_stride = row_stride;
+    job.pixel_bytes = pixel_bytes;
+    job.width = width, job.height = height;
+    job.rows_per_band = r;
+    job.n_rows = n_rows;
+    job.row0 = row0, job.strip_rows = strip_step == 1 ? (n_rows > 0 ? n_rows : 1) : strip_rows, job.strip_step = strip_step;
+    job.slots = static_cast<uint8_t*>(scratch_dev);
+    job.slot_bytes = slot_bytes_of(width, r);
+    job.sizes = reinterpret_cast<uint32_t*>(job.slots + bands * job.slot_bytes);
+    job.adlers = job.sizes + bands;
+    const size_t smem = band_smem(width, r);
+    static thread_local size_t opted[64] = {0};
+    cudaError_t err = cudaSuccess;
+    if (smem > 48 * 1024 && device < 64 && opted[device] < smem) {
+        err = cudaFuncSetAttribute(png_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err == cudaSuccess) opted[device] = smem;
+    }
+    if (err == cudaSuccess) {
+        png_band_kernel<<<(unsigned)((n_rows + r - 1) / r), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(png_code(), job);
+        err = cudaGetLastError();
+    }
+    if (previous >= 0 && previous != device) cudaSetDevice(previous);
+    if (err != cudaSuccess) return png_fail(RT_ERR_CUDA, cudaGetErrorString(err));
+    return RT_OK;
+}
+
+int rt_png_pack_dev(int device, int32_t width, int32_t height, const void* scratch_dev, uint8_t* png_out, int64_t capacity,
+                    uint64_t* png_bytes_out, void* stream) {
+    if (scratch_dev == nullptr || png_out == nullptr || png_bytes_out == nullptr || rt_png_rows_per_band(width, height) < 0 || capacity < 128)
+        return png_fail(RT_ERR_BAD_ARG, "rt_png_pack_dev: NULL pointer or bad size");
+    const int r = rows_per_band(width, height);
+    const long long bands = (height + r - 1) / r;
+    PackJob job;
+    memset(&job, 0, sizeof(job));
+    job.slots = static_cast<const uint8_t*>(scratch_dev);
+    job.slot_bytes = slot_bytes_of(width, r);
+    job.sizes = reinterpret_cast<const uint32_t*>(job.slots + bands * job.slot_bytes);
+    job.adlers = job.sizes + bands;
+    job.n_bands = (int)bands;
+    job.band_bytes = r * (1 + 3 * width);
+    job.raw_bytes = (long long)height * (1 + 3ll * width);
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    memcpy(job.head, sig, 8);
+    uint8_t* ih = job.head + 8;
+    ih[0] = 0, ih[1] = 0, ih[2] = 0, ih[3] = 13;
+    memcpy(ih + 4, "IHDR", 4);
+    for (int i = 0; i < 4; ++i) ih[8 + i] = (uint8_t)((uint32_t)width >> (24 - 8 * i)), ih[12 + i] = (uint8_t)((uint32_t)height >> (24 - 8 * i));
+    ih[16] = 8, ih[17] = 2, ih[18] = 0, ih[19] = 0, ih[20] = 0;  // 8 bits, RGB, deflate, adaptive filters, not interlaced
+    const uint32_t crc = host_crc32(ih + 4, 17);
+    for (int i = 0; i < 4; ++i) ih[21 + i] = (uint8_t)(crc >> (24 - 8 * i));
+    job.out = png_out;
+    job.capacity = capacity;
+    job.bytes_out = reinterpret_cast<unsigned long long*>(png_bytes_out);
+    int previous = -1;
+    cudaGetDevice(&previous);
+    if (previous != device && cudaSetDevice(device) != cudaSuccess) return png_fail(RT_ERR_NO_DEVICE, "rt_png_pack_dev: cudaSetDevice failed");
+    png_pack_kernel<<<(unsigned)bands, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(job);
+    const cudaError_t err = cudaGetLastError();
+    if (previous >= 0 && previous != device) cudaSetDevice(previous);
+    if (err != cudaSuccess) return png_fail(RT_ERR_CUDA, cudaGetErrorString(err));
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -169,6 +169,18 @@ PROTOTYPES = {
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), _P, C.POINTER(C.c_double), _P, C.c_int64,
          _P, C.c_int32, _P],
     ),
+    "rt_png_rows_per_band": (C.c_int32, [C.c_int32, C.c_int32]),
+    "rt_png_scratch_bytes": (C.c_int64, [C.c_int32, C.c_int32]),
+    "rt_png_file_bound": (C.c_int64, [C.c_int32, C.c_int32]),
+    "rt_png_encode_bands_dev": (
+        C.c_int,
+        [C.c_int, _P, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, C.c_int64, _P],
+    ),
+    "rt_png_pack_dev": (C.c_int, [C.c_int, C.c_int32, C.c_int32, _P, _P, C.c_int64, _P, _P]),
+    "rt_render_png_host": (
+        C.c_int,
+        [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), C.POINTER(RtCamera), _P, C.c_int64, C.POINTER(C.c_int64)],
+    ),
     "rt_png_deflate_bound": (C.c_int64, [C.c_int32, C.c_int32]),
     "rt_png_deflate_rows": (
         C.c_int,

@@ -169,6 +169,9 @@ class CudaRenderer(Renderer):
                    default, byte-for-byte the kind of file the reference writes, ~30x slower).
                    Decoded pixels do not depend on it.
     ``png_threads``  threads ``save_image`` deflates with (default: up to 8 of the host's cores).
+    ``png_encoder``  ``"device"`` (default): the file is made on the GPU (``rt_png_encode_bands_dev``) and only it
+                   crosses PCIe; ``"host"``: the 8-bit image is copied to the host and deflated there
+                   (``png_compress_level`` / ``png_threads``).  Decoded pixels are the same.
     ``accel``      ``"auto"`` (default): scenes of at least ``ACCEL_MIN_SPHERES`` shapes get a
                    bounding-volume tree (``rt_accel_build_host``) so rays skip sphere tests
                    that provably miss; ``True`` / ``False`` force it on or off.  Results do
@@ -194,6 +197,7 @@ class CudaRenderer(Renderer):
         device: int = 0,
         png_compress_level: Optional[int] = None,
         png_threads: Optional[int] = None,
+        png_encoder: str = "device",
         accel: Any = "auto",
     ) -> None:
         if precision not in _PRECISIONS:
@@ -228,6 +232,11 @@ class CudaRenderer(Renderer):
                 png_threads = os.cpu_count() or 1
             png_threads = min(8, png_threads)
         self.png_threads = max(1, int(png_threads))
+        if png_encoder not in ("device", "host"):
+            raise ValueError("png_encoder must be 'device' or 'host'")
+        # a zlib level asks for a zlib file: that one is made on the host
+        self.png_encoder = "host" if self.png_compress_level is not None else png_encoder
+        self._png_device = None
         self._png_pool = None
         self._rgb8_dev = None     # reused across frames: the 8-bit image on the device ...
         self._rgb8_pinned = None  # ... and its pinned landing zone on the host
@@ -527,14 +536,33 @@ class CudaRenderer(Renderer):
         torch = _require_cuda(self.device)
         width, height = int(camera.width), int(camera.height)
         t0 = time.perf_counter()
+        if isinstance(color, DeviceColor) and color.rgba8 is not None:
+            dev8 = color.rgba8
+        else:
+            dev8 = self.quantize(color, 3)
+        if dev8.shape[0] != width * height:
+            raise ValueError(f"colour has {dev8.shape[0]} pixels, camera is {width}x{height}")
+        channels = int(dev8.shape[1])
+        if self.png_encoder == "device" and 1 + 3 * width <= 65000:
+            from ..png import DevicePngEncoder
+
+            with _Nvtx("rt: PNG encode on the device + file to host"):
+                enc = self._png_device
+                if enc is None or (enc.width, enc.height) != (width, height):
+                    enc = self._png_device = DevicePngEncoder(width, height, self.device)
+                stream = torch.cuda.current_stream(self.device)
+                enc.enqueue(dev8, int(stream.cuda_stream))
+                stream.synchronize()  # the trace kernel, the encoder and the file's way to the host
+                abi.check(abi.load().rt_device_status(self.device), "rt_device_status")
+                data = enc.finish()
+            t1 = time.perf_counter()
+            with _Nvtx("rt: PNG write"), open(output_path, "wb") as f:
+                f.write(data)
+            t2 = time.perf_counter()
+            self.last_timing = {"kernel_and_d2h_ms": (t1 - t0) * 1e3, "png_ms": (t2 - t1) * 1e3, "png_bytes": len(data),
+                                "encoder": "device (rt_png_encode_bands_dev + rt_png_pack_dev); kernel_and_d2h_ms includes the encode"}
+            return
         with _Nvtx("rt: 8-bit image to host"):
-            if isinstance(color, DeviceColor) and color.rgba8 is not None:
-                dev8 = color.rgba8
-            else:
-                dev8 = self.quantize(color, 3)
-            if dev8.shape[0] != width * height:
-                raise ValueError(f"colour has {dev8.shape[0]} pixels, camera is {width}x{height}")
-            channels = int(dev8.shape[1])
             if self._rgb8_pinned is None or tuple(self._rgb8_pinned.shape) != (width * height, channels):
                 self._rgb8_pinned = torch.empty((width * height, channels), dtype=torch.uint8).pin_memory()
             self._rgb8_pinned.copy_(dev8, non_blocking=True)

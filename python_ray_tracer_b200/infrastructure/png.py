@@ -148,6 +148,59 @@ def encode_png_fast(pixels: np.ndarray, threads: int = 1, pool=None) -> bytes:
     return b"".join((_SIGNATURE, _chunk(b"IHDR", header), _chunk(b"IDAT", stream), _chunk(b"IEND", b"")))
 
 
+class DevicePngEncoder:
+    """PNG files made on the GPU (``rt_png_encode_bands_dev`` + ``rt_png_pack_dev``, csrc/rt_png_dev.cu): the
+    8-bit image stays on the device, only the ~10x smaller file crosses PCIe -- written by the pack kernel
+    straight into a pinned host buffer.  One encoder holds the scratch and landing buffers of one frame size
+    on one device; ``encode`` returns the file's bytes.  Decoded pixels equal the input."""
+
+    def __init__(self, width: int, height: int, device: int = 0) -> None:
+        import torch
+
+        from .cuda import abi
+
+        self.lib = abi.load()
+        self.width, self.height, self.device = int(width), int(height), int(device)
+        self.rows_per_band = int(self.lib.rt_png_rows_per_band(self.width, self.height))
+        if self.rows_per_band < 0:
+            raise ValueError(f"the device encoder cannot take {width}x{height} frames (rows wider than 21 666 pixels)")
+        self.scratch_bytes = int(self.lib.rt_png_scratch_bytes(self.width, self.height))
+        self.capacity = int(self.lib.rt_png_file_bound(self.width, self.height))
+        self.scratch = torch.empty(self.scratch_bytes, dtype=torch.uint8, device=torch.device("cuda", self.device))
+        self.file = torch.empty(self.capacity, dtype=torch.uint8).pin_memory()
+        self.size = torch.zeros(1, dtype=torch.int64).pin_memory()
+
+    def enqueue(self, pixels, stream: int) -> None:
+        """``pixels``: uint8 device tensor ``[H * W, 3 or 4]`` (or ``[H, W, C]``), contiguous.  Enqueues the two
+        kernels on ``stream``; ``finish()`` after synchronising that stream."""
+        from .cuda import abi
+
+        channels = int(pixels.shape[-1])
+        if pixels.numel() != self.width * self.height * channels or channels not in (3, 4) or not pixels.is_contiguous():
+            raise ValueError("expected a contiguous uint8 image of the encoder's size with 3 or 4 channels")
+        self.size[0] = -1
+        abi.check(self.lib.rt_png_encode_bands_dev(self.device, pixels.data_ptr(), channels, self.width * channels, self.height,
+                                                   self.width, self.height, 0, self.height, 1, self.scratch.data_ptr(),
+                                                   self.scratch_bytes, stream), "rt_png_encode_bands_dev")
+        abi.check(self.lib.rt_png_pack_dev(self.device, self.width, self.height, self.scratch.data_ptr(), self.file.data_ptr(),
+                                           self.capacity, self.size.data_ptr(), stream), "rt_png_pack_dev")
+
+    def finish(self) -> memoryview:
+        """The file the last ``enqueue`` made (a view of the pinned buffer: copy or write it before the next one)."""
+        n = int(self.size[0])
+        if n <= 0:
+            raise RuntimeError("the device PNG encoder reported no file (stream not synchronised, or capacity too small)")
+        return memoryview(self.file.numpy())[:n]
+
+    def encode(self, pixels) -> bytes:
+        import torch
+
+        stream = torch.cuda.current_stream(self.device)
+        self.enqueue(pixels, int(stream.cuda_stream))
+        stream.synchronize()
+        return bytes(self.finish())
+
+
 def write_png(path: Path, rgb8: np.ndarray, compress_level: Optional[int] = 6, threads: int = 1, pool=None) -> None:
     """``compress_level=None``: the library's own deflate (``encode_png_fast``); an integer: zlib."""
     rgb8 = np.ascontiguousarray(rgb8)

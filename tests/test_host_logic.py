@@ -167,7 +167,7 @@ def test_product_never_imports_the_oracle():
 def test_abi_library_exports_every_declared_symbol():
     """include/rt_abi.h <-> librt_b200.so <-> abi.PROTOTYPES agree (no compute calls)."""
     header = (ROOT / "include" / "rt_abi.h").read_text()
-    declared = set(re.findall(r"^(?:int|int64_t|const char\*)\s+(rt_\w+)\s*\(", header, re.M))
+    declared = set(re.findall(r"^(?:int|int32_t|int64_t|const char\*)\s+(rt_\w+)\s*\(", header, re.M))
     assert declared == set(abi.PROTOTYPES), declared ^ set(abi.PROTOTYPES)
     lib = abi.load()  # raises if the library is not built: there is no fallback
     for name in declared:

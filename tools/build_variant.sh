@@ -14,4 +14,4 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function --expt-relaxed-constexpr"
 $NVCC $FLAGS "$@" -Xptxas -v -c "$src/trace_fast.cu" -o "$out/trace_fast.o" 2>&1 | grep -A2 "render_rows_small_kernelILb0ELi3ELi8" | grep -E "Used|spill" | sed "s/^/[$name] /"
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "$out/librt_b200.so" "$out/trace_fast.o" \
-  "$src"/{trace_exact,rt_abi,rt_abi_host,rt_peaks,rt_accel_build,rt_png_host}.o
+  "$src"/{trace_exact,rt_abi,rt_abi_host,rt_peaks,rt_accel_build,rt_png_host,rt_png_dev}.o
