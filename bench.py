@@ -428,6 +428,22 @@ def host_path(g: Gpu, tables, cam, width, height, use_tree: bool) -> dict:
     rgb8_ms = one_pass(True, False)
     planes_ms = one_pass(False, True)
     both_ms = one_pass(True, True)
+    # save_image's FILE made on the device (rt_render_png_host): only the PNG crosses PCIe
+    png_cap = int(lib.rt_png_file_bound(width, height))
+    png_ms, png_bytes = None, None
+    if png_cap > 0:
+        png_host = torch.empty(png_cap, dtype=torch.uint8).pin_memory()
+        used = C.c_int64(0)
+        times = []
+        for s in range(total):
+            env, flat = envs[s % len(envs)], tables[s % len(tables)][3]
+            t0 = time.perf_counter()
+            abi.check(lib.rt_render_png_host(g.local, flat.spheres.ctypes.data, flat.n_spheres, flat.point_lights.ctypes.data,
+                                             C.byref(env), C.byref(cam), png_host.data_ptr(), png_cap, C.byref(used)), "rt_render_png_host")
+            _ = int(png_host[used.value - 1])  # the file's last byte, read on the host
+            if s >= args.warmup:
+                times.append(time.perf_counter() - t0)
+        png_ms, png_bytes = g.max_over_ranks(float(np.mean(times)) * 1e3), int(used.value)
     flat = tables[-1][3]
     px = width * height * g.world
     rate = lambda ms: px / (ms * 1e-3) / 1e6  # noqa: E731
@@ -445,6 +461,11 @@ def host_path(g: Gpu, tables, cam, width, height, use_tree: bool) -> dict:
                               "d2h_gb_per_s_per_gpu": rgb_host.numel() * 4 / (planes_ms * 1e-3) / 1e9},
         "planes_and_rgb8": {"ms_per_step": both_ms, "value": rate(both_ms),
                             "d2h_bytes_per_step": int(rgb_host.numel() * 4 + rgb8_host.numel())},
+        # the finished PNG instead of the 8-bit image: traced, quantised, filtered, deflated and packed on the device
+        "png_file": None if png_ms is None else {
+            "ms_per_step": png_ms, "value": rate(png_ms), "d2h_bytes_per_step": png_bytes,
+            "api": "rt_render_png_host: trace kernel (8-bit image) + rt_png_encode_bands_dev + rt_png_pack_dev writing the file "
+                   "into the caller's pinned buffer; the file's last byte read on the host"},
     }
 
 
@@ -546,6 +567,7 @@ def c4_object(g: Gpu, steps: int, warmup: int) -> dict:
             e2e.append((time.perf_counter() - t0) * 1e3)
     e2e_ms = float(np.mean(e2e))
     peer.close()
+    png = c4_png_exchange(g, flat, cam, spheres, lights, width, height, max_depth, shard, solo, steps, warmup)
     if rank != 0:
         return {}
     px = width * height
@@ -561,8 +583,96 @@ def c4_object(g: Gpu, steps: int, warmup: int) -> dict:
         "e2e": {"ms_per_step": e2e_ms, "value": px / (e2e_ms * 1e-3) / 1e6,
                 "what": "launch on every rank -> stream sync + barrier -> D2H of the assembled frame on rank 0 into pinned host memory -> one pixel read",
                 "d2h_bytes_per_step": px * channels},
+        "png_exchange": png,
         "steps": steps, "warmup": warmup,
     }
+
+
+def c4_png_exchange(g: Gpu, flat, cam, spheres, lights, width, height, max_depth, shard, solo, steps: int, warmup: int):
+    """The same frame with the exchange step compressed: every rank renders its strips into LOCAL memory, encodes
+    their bands (rt_png_encode_bands_dev: each band of the image is one IDAT chunk) straight into rank 0's scratch
+    area over NVLink -- a tenth of the bytes -- and rank 0 packs the file into pinned host memory."""
+    torch, abi, lib, sharding = g.torch, g.abi, g.lib, g.sharding
+    world, rank = g.world, g.rank
+    r = int(lib.rt_png_rows_per_band(width, height))
+    if r < 0 or shard.strip_rows % r != 0:
+        return None
+    scratch_bytes = int(lib.rt_png_scratch_bytes(width, height))
+    cap = int(lib.rt_png_file_bound(width, height))
+    env = g.env_of(flat, max_depth, abi.RT_FLAG_RGB8)
+    local = torch.empty((shard.n_rows * width, 3), dtype=torch.uint8, device=g.dev)
+    peer = sharding.PeerBuffer(scratch_bytes, rank, world, g.local, dst=0)
+    file_host = torch.empty(cap, dtype=torch.uint8).pin_memory() if rank == 0 else None
+    size_host = torch.zeros(1, dtype=torch.int64).pin_memory() if rank == 0 else None
+
+    def launch(_step=0) -> None:
+        abi.check(lib.rt_render_strips_dev(g.local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
+                                           C.byref(cam), shard.strip_rows, rank, world, None, abi.RT_DTYPE_F32, 0,
+                                           local.data_ptr(), None, g.sptr), "rt_render_strips_dev")
+        abi.check(lib.rt_png_encode_bands_dev(g.local, local.data_ptr(), 3, width * 3, shard.n_rows, width, height,
+                                              rank * shard.strip_rows, shard.strip_rows, world, peer.ptr, scratch_bytes, g.sptr),
+                  "rt_png_encode_bands_dev")
+
+    def pack() -> int:
+        size_host[0] = -1
+        abi.check(lib.rt_png_pack_dev(g.local, width, height, peer.ptr, file_host.data_ptr(), cap, size_host.data_ptr(), g.sptr), "rt_png_pack_dev")
+        torch.cuda.current_stream(g.local).synchronize()
+        return int(size_host[0])
+
+    # the assembled file decodes to the single-GPU frame
+    launch()
+    peer.complete()
+    matches, png_bytes = None, None
+    if rank == 0:
+        from python_ray_tracer_b200.infrastructure.png import read_png
+
+        png_bytes = pack()
+        with tempfile.TemporaryDirectory() as tmp:
+            path = Path(tmp) / "c4.png"
+            path.write_bytes(bytes(file_host.numpy()[:png_bytes]))
+            decoded = read_png(path)
+        matches = bool(np.array_equal(decoded, solo[:, :, :3].cpu().numpy()))
+    ms = g.timed_steps(launch, steps, warmup, together=True)
+    per_rank = g.gather_floats(float(ms.mean()))
+    # the same two kernels for the WHOLE frame on rank 0 alone (the others wait): this path's own N = 1 time
+    solo_ms = None
+    if rank == 0:
+        whole = local if world == 1 else torch.empty((height * width, 3), dtype=torch.uint8, device=g.dev)
+
+        def launch_solo(_step=0) -> None:
+            abi.check(lib.rt_render_strips_dev(g.local, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env),
+                                               C.byref(cam), shard.strip_rows, 0, 1, None, abi.RT_DTYPE_F32, 0,
+                                               whole.data_ptr(), None, g.sptr), "rt_render_strips_dev")
+            abi.check(lib.rt_png_encode_bands_dev(g.local, whole.data_ptr(), 3, width * 3, height, width, height, 0, height, 1,
+                                                  peer.ptr, scratch_bytes, g.sptr), "rt_png_encode_bands_dev")
+
+        was = g.world
+        g.world = 1
+        solo_ms = float(g.timed_steps(launch_solo, steps, warmup).mean())
+        g.world = was
+    g.barrier()
+    e2e = []
+    for s in range(warmup + steps):
+        g.barrier()
+        t0 = time.perf_counter()
+        launch()
+        peer.complete()
+        if rank == 0:
+            n = pack()
+            _ = int(file_host[n - 1])
+        if s >= warmup:
+            e2e.append((time.perf_counter() - t0) * 1e3)
+    peer.close()
+    if rank != 0:
+        return None
+    px = width * height
+    return {"ms_per_step": max(per_rank), "value": px / (max(per_rank) * 1e-3) / 1e6, "per_rank_ms": per_rank,
+            "own_n1_ms": solo_ms, "efficiency_vs_own_n1": solo_ms / (world * max(per_rank)),
+            "what": "per rank: trace kernel into local RGB8 + band encoder storing IDAT chunks into rank 0's scratch over NVLink",
+            "rows_per_band": r, "png_bytes": png_bytes, "file_decodes_to_single_gpu_frame": matches,
+            "e2e": {"ms_per_step": float(np.mean(e2e)), "value": px / (float(np.mean(e2e)) * 1e-3) / 1e6,
+                    "what": "launches on every rank -> stream sync + barrier -> pack kernel on rank 0 writes the PNG into pinned host memory -> its last byte read",
+                    "d2h_bytes_per_step": png_bytes}}
 
 
 def c3_object(g: Gpu, steps: int, warmup: int) -> dict:

@@ -155,21 +155,17 @@ class _DeviceBytes:
         self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 3}
 
 
-class PeerFrame:
-    """A whole-frame RGBA8 (or, ``channels=3``, RGB8) buffer on rank ``dst`` that every rank of
-    the node can write.
+class PeerBuffer:
+    """``nbytes`` of device memory on rank ``dst`` that every rank of the node can write.
 
     Rank ``dst`` owns the memory (``rt_peer_buffer_create``) and sends the 64-byte IPC handle
-    to the other ranks (``broadcast_object_list``); they map it (``rt_peer_buffer_open``)
-    and hand the pointer to ``rt_render_strips_dev`` with ``RT_FLAG_IMAGE_ORDER``: each
-    rank's kernel stores its pixels straight into the owner's framebuffer over NVLink while
-    it renders, so the exchange step overlaps the compute and no gather or permutation
-    follows.  ``complete()`` is the only synchronisation: every rank drains its stream,
-    then a barrier tells the owner that all shards have landed.
+    to the other ranks (``broadcast_object_list``); they map it (``rt_peer_buffer_open``) and
+    hand ``ptr`` to a kernel, whose stores then go straight into the owner's memory over NVLink.
+    ``complete()`` is the only synchronisation: every rank drains its stream, then a barrier
+    tells the owner that everything has landed.
     """
 
-    def __init__(self, height: int, width: int, rank: int, world: int, device: int, dst: int = 0,
-                 group: Any = None, channels: int = 4) -> None:
+    def __init__(self, nbytes: int, rank: int, world: int, device: int, dst: int = 0, group: Any = None) -> None:
         import ctypes as C
 
         import torch
@@ -177,36 +173,33 @@ class PeerFrame:
 
         from . import abi
 
-        if channels not in (3, 4):
-            raise ValueError(f"a peer frame has 3 (RT_FLAG_RGB8) or 4 bytes per pixel, not {channels}")
-        self.height, self.width, self.rank, self.world, self.device, self.dst = height, width, rank, world, device, dst
-        self.group, self.channels = group, channels
+        self.nbytes, self.rank, self.world, self.device, self.dst, self.group = int(nbytes), rank, world, device, dst, group
         self._lib = abi.load()
         self._owner = rank == dst
         ptr = C.c_void_p()
         handle = C.create_string_buffer(abi.RT_IPC_HANDLE_BYTES)
         if self._owner:
-            abi.check(self._lib.rt_peer_buffer_create(device, height * width * channels, C.byref(ptr), handle), "rt_peer_buffer_create")
+            abi.check(self._lib.rt_peer_buffer_create(device, self.nbytes, C.byref(ptr), handle), "rt_peer_buffer_create")
         box = [handle.raw if self._owner else None]
         if world > 1:
             dist.broadcast_object_list(box, src=dst, group=group)
         if not self._owner:
             abi.check(self._lib.rt_peer_buffer_open(device, box[0], C.byref(ptr)), "rt_peer_buffer_open")
         self.ptr = int(ptr.value)
-        # the owner reads the frame through torch; the writers only need the pointer
-        self.frame = None
+        # the owner reads the buffer through torch; the writers only need the pointer
+        self.bytes = None
         if self._owner:
-            self.frame = torch.as_tensor(_DeviceBytes(self.ptr, (height, width, channels), "|u1"), device=torch.device("cuda", device))
+            self.bytes = torch.as_tensor(_DeviceBytes(self.ptr, (self.nbytes,), "|u1"), device=torch.device("cuda", device))
 
     def complete(self) -> Optional[Any]:
-        """Wait until every rank's kernel has finished writing; returns the frame on the owner."""
+        """Wait until every rank's kernels have finished writing; returns the owner's view (``None`` elsewhere)."""
         import torch
         import torch.distributed as dist
 
         torch.cuda.current_stream(self.device).synchronize()
         if self.world > 1:
             dist.barrier(group=self.group)
-        return self.frame
+        return self.bytes
 
     def close(self) -> None:
         if self.ptr:
@@ -214,7 +207,7 @@ class PeerFrame:
                 import torch.distributed as dist
 
                 dist.barrier(group=self.group)  # nobody unmaps or frees while a peer may still write
-            self.frame = None
+            self.bytes = None
             if self._owner:
                 self._lib.rt_peer_buffer_destroy(self.device, self.ptr)
             else:
@@ -222,8 +215,31 @@ class PeerFrame:
             self.ptr = 0
 
 
+class PeerFrame(PeerBuffer):
+    """A whole-frame RGBA8 (or, ``channels=3``, RGB8) buffer on rank ``dst`` that every rank of
+    the node can write: the ranks hand ``ptr`` to ``rt_render_strips_dev`` with
+    ``RT_FLAG_IMAGE_ORDER`` and each rank's kernel stores its pixels at their image position while
+    it renders, so the exchange step overlaps the compute and no gather or permutation follows."""
+
+    def __init__(self, height: int, width: int, rank: int, world: int, device: int, dst: int = 0,
+                 group: Any = None, channels: int = 4) -> None:
+        if channels not in (3, 4):
+            raise ValueError(f"a peer frame has 3 (RT_FLAG_RGB8) or 4 bytes per pixel, not {channels}")
+        super().__init__(height * width * channels, rank, world, device, dst, group)
+        self.height, self.width, self.channels = height, width, channels
+        self.frame = None if self.bytes is None else self.bytes.view(height, width, channels)
+
+    def complete(self) -> Optional[Any]:
+        super().complete()
+        return self.frame
+
+    def close(self) -> None:
+        self.frame = None
+        super().close()
+
+
 __all__: Sequence[str] = (
-    "PeerFrame",
+    "PeerBuffer", "PeerFrame",
     "DEFAULT_STRIP_ROWS", "StripShard", "strip_shards", "band_rows", "frames_of_rank", "image_order",
     "gather_frame", "render_frame_sharded", "render_frames_sharded", "covered_exactly_once",
 )
