@@ -32,7 +32,10 @@ extern "C" void rt_internal_set_error(const char* message);
 
 namespace {
 
-constexpr int kThreads = 256;
+#ifndef RT_PNG_THREADS
+#define RT_PNG_THREADS 256
+#endif
+constexpr int kThreads = RT_PNG_THREADS;  // per band (measured on B200, 1080p / 8K band kernel: 256: 58 / 569 us, 512: 62 / 544, 1024: 89 / 859)
 constexpr int kHeaderWords = 40;       // the dynamic-block header, LSB-first, at most 1280 bits
 constexpr uint32_t kCrcPoly = 0xedb88320u;
 constexpr uint32_t kAdlerMod = 65521u;
@@ -282,78 +285,47 @@ __device__ __forceinline__ unsigned long long block_sum64(unsigned long long v, 
     return all;
 }
 
-// LSB-first bit writer of one thread into the block's output words.  A thread's tokens are contiguous in the
-// stream, but its first and last words are shared with its neighbours (and a thread may emit fewer than 32
-// bits), so every word goes out with an atomic OR into the zeroed buffer.
-struct BitSink {
-    uint32_t* words;
-    unsigned long long acc;
-    uint32_t w;
-    int n;
-    __device__ __forceinline__ BitSink(uint32_t* out_words, uint32_t bit) : words(out_words), acc(0), w(bit >> 5), n((int)(bit & 31u)) {}
-    __device__ __forceinline__ void put(uint32_t entry) {  // bits | count << 24
-        acc |= (unsigned long long)(entry & 0xffffffu) << n;
-        n += (int)(entry >> 24);
-        if (n >= 32) {
-            atomicOr(words + w, (uint32_t)acc);
-            acc >>= 32;
-            n -= 32;
-            ++w;
-        }
-    }
-    __device__ __forceinline__ void flush() {
-        if (n > 0 && (uint32_t)acc != 0u) atomicOr(words + w, (uint32_t)acc);
-    }
-};
-struct BitCount {
-    uint32_t bits = 0;
-    __device__ __forceinline__ void put(uint32_t entry) { bits += entry >> 24; }
-};
+// m(i): byte i of the stream equals the byte three before it (it continues a run of one RGB residual)
+__device__ __forceinline__ bool continues_run(const uint8_t* S, int i) { return i >= 3 && S[i] == S[i - 3]; }
 
-// The tokens whose first byte lies in [a, b) of the band's stream S.  m(i) = "S[i] equals S[i - 3]".  run_in =
-// how many bytes just before a continue a run into a; run_out = how many from b on continue the run that
-// reaches b.  A run is cut into chunks of 258 from its start; a chunk of at least 3 bytes is one match token
-// (emitted by the thread that owns its first byte), a shorter one is literals.
-template <class Sink>
-__device__ __forceinline__ void walk_tokens(const uint8_t* S, int a, int b, int run_in, int run_out, const uint32_t* lit,
-                                            const uint32_t* match, Sink& sink) {
-    int i = a;
-    while (i < b) {
-        const bool mi = i >= 3 && S[i] == S[i - 3];
-        if (!mi) {
-            sink.put(lit[S[i]]);
-            ++i;
-            continue;
+// The tokens whose first byte lies in [a, b) of the band's stream S, visited from b - 1 DOWN to a with the same
+// instructions in every thread (a warp walks 32 pieces in lock step: nothing here may diverge).
+// A run of m = 1 bytes is cut into chunks of 258 counted from its END, so what covers byte i follows from
+// rem(i) = how many bytes from i on continue the run (a backward recurrence, carried in from the pieces to the
+// right as run_out) and from m(i - 1), m(i - 2):
+//   m(i) = 0                          literal
+//   rem % 258 = 0                     a match of 258 starts here
+//   the run starts here (m(i-1) = 0)  its head of rem % 258 bytes: a match if that is at least 3, else a literal
+//   rem % 258 = 1, the run started at i - 1   second byte of a two-byte head: literal
+//   otherwise                         inside a match: nothing
+// emit(i, entry) is called for every byte with its token's table entry (bits | count << 24; 0 = nothing).
+template <class Emit>
+__device__ __forceinline__ void walk_tokens(const uint8_t* S, int a, int b, int run_out, const uint32_t* lit,
+                                            const uint32_t* match, Emit&& emit) {
+    int q = run_out % 258;  // rem(i + 1) mod 258
+    bool cur = continues_run(S, b - 1), n1 = continues_run(S, b - 2), n2;
+    for (int i = b - 1; i >= a; --i) {
+        n2 = continues_run(S, i - 2);
+        q = cur ? (q == 257 ? 0 : q + 1) : 0;
+        const uint32_t literal = lit[S[i]];
+        uint32_t entry = literal;
+        if (cur) {
+            const uint32_t head = q >= 3 ? match[q - 3] : literal;  // (q = 1, 2 here: match[] is not read out of range)
+            entry = q == 0 ? match[255] : (!n1 ? head : ((q == 1 && !n2) ? literal : 0u));
         }
-        int j = i + 1;
-        while (j < b && S[j] == S[j - 3]) ++j;
-        const int off = i == a ? run_in : 0;                       // offset of byte i in its run
-        const int runlen = off + (j - i) + (j == b ? run_out : 0); // the whole run
-        const int mine_end = off + (j - i);                        // my part: run offsets [off, mine_end)
-        int o = off, pos = i;
-        while (o < mine_end) {
-            const int cs = (o / 258) * 258;
-            const int cl = min(258, runlen - cs);
-            const int take = min(cs + cl, mine_end) - o;
-            if (cl >= 3) {
-                if (o == cs) sink.put(match[cl - 3]);
-            } else {
-                for (int q = 0; q < take; ++q) sink.put(lit[S[pos + q]]);
-            }
-            o += take;
-            pos += take;
-        }
-        i = j;
+        emit(i, entry);
+        cur = n1;
+        n1 = n2;
     }
 }
 
 __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constant__ PngCode code, const __grid_constant__ BandJob job) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ uint32_t s_lit[256], s_match[256], s_crc[256], s_x2n[32];
-    __shared__ uint32_t s_len[kThreads], s_lead[kThreads], s_trail[kThreads];
+    __shared__ uint32_t s_len[kThreads], s_lead[kThreads];
     __shared__ uint32_t s_scan[kThreads / 32 + 1];
     __shared__ unsigned long long s_sum[kThreads / 32];
-    __shared__ uint32_t s_g[9], s_part[kThreads];
+    __shared__ uint32_t s_part[1];
 
     const int t = threadIdx.x;
     const int line = 1 + 3 * job.width;
@@ -368,30 +340,53 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
     uint32_t* out_words = reinterpret_cast<uint32_t*>(out);
     const int out_words_n = (cap + kBandSlack + kChunkOverhead + 3) / 4;
 
-    s_lit[t] = code.lit[t];
-    s_match[t] = code.match[t];
-    {
+    if (t < 256) {
+        s_lit[t] = code.lit[t];
+        s_match[t] = code.match[t];
         uint32_t c = (uint32_t)t;
         for (int k = 0; k < 8; ++k) c = c & 1u ? (c >> 1) ^ kCrcPoly : c >> 1;
         s_crc[t] = c;
     }
     if (t < 32) s_x2n[t] = code.x2n[t];
-    for (int i = t; i < out_words_n; i += kThreads) out_words[i] = 0u;
 
-    // ---- filter 1 (Sub): byte minus the byte of the pixel to the left; Adler-32 sums on the way
+    // ---- filter 1 (Sub): byte minus the byte of the pixel to the left; Adler-32 sums on the way.
+    // Packed RGB rows are first brought into shared memory (the `out` area is free until the tokens are
+    // written) with whole-word loads that are all in flight at once; a filter loop that reads its two bytes from
+    // global memory waits a memory latency per byte.
     unsigned long long s1 = 0, s2 = 0;
+    const int row_bytes = 3 * job.width;
+    const bool staged = job.pixel_bytes == 3 && job.row_stride == (long long)row_bytes;
+    if (staged) {
+        const uint8_t* src = job.pixels + (long long)first_local * job.row_stride;
+        const int total = rows * row_bytes;
+        if ((((uintptr_t)src) & 3) == 0) {
+            const uint32_t* src4 = reinterpret_cast<const uint32_t*>(src);
+            for (int i = t; i < total / 4; i += kThreads) out_words[i] = __ldg(src4 + i);
+            for (int i = (total & ~3) + t; i < total; i += kThreads) out[i] = __ldg(src + i);
+        } else {
+            for (int i = t; i < total; i += kThreads) out[i] = __ldg(src + i);
+        }
+        __syncthreads();
+    }
     for (int r = 0; r < rows; ++r) {
         const uint8_t* src = job.pixels + (long long)(first_local + r) * job.row_stride;
+        const uint8_t* raw = out + r * row_bytes;
         uint8_t* dst = filt + r * line;
         if (t == 0) {
             dst[0] = 1;
             s1 += 1u;
             s2 += (unsigned long long)(r * line);
         }
-        for (int x = t; x < 3 * job.width; x += kThreads) {
-            const int px = x / 3, ch = x - 3 * px;
-            const uint8_t cur = __ldg(src + (long long)px * job.pixel_bytes + ch);
-            const uint8_t left = px > 0 ? __ldg(src + (long long)(px - 1) * job.pixel_bytes + ch) : (uint8_t)0;
+        for (int x = t; x < row_bytes; x += kThreads) {
+            uint8_t cur, left;
+            if (staged) {
+                cur = raw[x];
+                left = x >= 3 ? raw[x - 3] : (uint8_t)0;
+            } else {
+                const int px = x / 3, ch = x - 3 * px;
+                cur = __ldg(src + (long long)px * job.pixel_bytes + ch);
+                left = px > 0 ? __ldg(src + (long long)(px - 1) * job.pixel_bytes + ch) : (uint8_t)0;
+            }
             const uint8_t v = (uint8_t)(cur - left);
             dst[1 + x] = v;
             s1 += v;
@@ -399,45 +394,44 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
         }
     }
     s1 = block_sum64(s1, s_sum);
-    s2 = block_sum64(s2, s_sum);  // (block_sum64 synchronises: filt is complete from here on)
+    s2 = block_sum64(s2, s_sum);  // (block_sum64 synchronises: filt is complete from here on, the staged rows are done with)
+    for (int i = t; i < out_words_n; i += kThreads) out_words[i] = 0u;  // (visible to all before the first token: syncs below)
     const uint32_t adler_a = (uint32_t)((1ull + s1) % kAdlerMod);
     const uint32_t adler_b = (uint32_t)((((unsigned long long)n % kAdlerMod) + ((unsigned long long)n % kAdlerMod) * (s1 % kAdlerMod) +
                                          (unsigned long long)kAdlerMod - (s2 % kAdlerMod)) % kAdlerMod);
 
-    // ---- every thread's piece of the stream and what it knows about runs at its ends
+    // ---- every thread's piece of the stream; how far the run that reaches its end goes on to the right
     const int piece = (n + kThreads - 1) / kThreads;
     const int a = min(t * piece, n), b = min(a + piece, n);
     {
-        int lead = 0;
-        while (a + lead < b && a + lead >= 3 && filt[a + lead] == filt[a + lead - 3]) ++lead;
-        int trail = 0;
-        while (b - 1 - trail >= a && b - 1 - trail >= 3 && filt[b - 1 - trail] == filt[b - 4 - trail]) ++trail;
+        int rem = 0;  // bytes from the piece's first byte on that continue a run (if all do: its length)
+        for (int i = b - 1; i >= a; --i) rem = continues_run(filt, i) ? rem + 1 : 0;
         s_len[t] = (uint32_t)(b - a);
-        s_lead[t] = (uint32_t)lead;
-        s_trail[t] = (uint32_t)trail;
+        s_lead[t] = (uint32_t)rem;
     }
     __syncthreads();
-    int run_in = 0, run_out = 0;
-    for (int u = t - 1; u >= 0; --u) {  // (long runs span many pieces: black sky; bounded by kThreads steps)
-        run_in += (int)s_trail[u];
-        if (s_trail[u] != s_len[u]) break;
-    }
-    for (int u = t + 1; u < kThreads; ++u) {
+    int run_out = 0;
+    for (int u = t + 1; u < kThreads; ++u) {  // (a run longer than a piece -- black sky -- is summed piece by piece)
         run_out += (int)s_lead[u];
         if (s_lead[u] != s_len[u]) break;
     }
 
     // ---- bit positions
-    BitCount counter;
-    walk_tokens(filt, a, b, run_in, run_out, s_lit, s_match, counter);
+    uint32_t my_bits = 0;
+    walk_tokens(filt, a, b, run_out, s_lit, s_match, [&](int, uint32_t entry) { my_bits += entry >> 24; });
     uint32_t token_bits = 0;
-    const uint32_t my_bit = block_exclusive_sum(counter.bits, s_scan, &token_bits);
+    const uint32_t my_bit = block_exclusive_sum(my_bits, s_scan, &token_bits);
     const int prefix = band == 0 ? 2 : 0;  // the zlib header travels in the first band's chunk
     const int data0 = 8 + prefix;
     const uint32_t block_bits = code.header_bits + token_bits + (code.eob >> 24) + 3u;  // + the sync block's header
     const uint32_t deflated = (block_bits + 7u) / 8u + 4u;  // ... its LEN / NLEN
     const bool stored = code.header_bits == 0u || deflated >= (uint32_t)n + 5u;
     int data_len;
+    auto put_bits = [&](uint32_t bit, uint32_t entry) {  // a token of at most 24 bits at an absolute bit position
+        const unsigned long long v = (unsigned long long)(entry & 0xffffffu) << (bit & 31u);
+        atomicOr(out_words + (bit >> 5), (uint32_t)v);
+        if ((uint32_t)(v >> 32) != 0u) atomicOr(out_words + (bit >> 5) + 1, (uint32_t)(v >> 32));
+    };
     if (!stored) {
         const uint32_t bit0 = 8u * (uint32_t)data0;
         if (t < kHeaderWords && code.header[t] != 0u) {
@@ -447,10 +441,14 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
             atomicOr(out_words + w, (uint32_t)v);
             if ((uint32_t)(v >> 32) != 0u) atomicOr(out_words + w + 1, (uint32_t)(v >> 32));
         }
-        BitSink sink(out_words, bit0 + code.header_bits + my_bit);
-        walk_tokens(filt, a, b, run_in, run_out, s_lit, s_match, sink);
-        if (t == kThreads - 1) sink.put(code.eob);  // the last piece ends the stream (empty pieces included)
-        sink.flush();
+        // the piece's tokens from its last one back to its first, each at its own bit position
+        uint32_t bit = bit0 + code.header_bits + my_bit + my_bits;
+        walk_tokens(filt, a, b, run_out, s_lit, s_match, [&](int, uint32_t entry) {
+            const uint32_t nb = entry >> 24;
+            bit -= nb;
+            if (nb) put_bits(bit, entry);
+        });
+        if (t == 0) put_bits(bit0 + code.header_bits + token_bits, code.eob);
         data_len = prefix + (int)deflated;
     } else {
         for (int i = t; i < n; i += kThreads) out[data0 + 5 + i] = filt[i];
@@ -473,32 +471,29 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
     }
     __syncthreads();
 
-    // ---- CRC-32 of type + data: slices aligned to the END (every slice but the first has exactly `slice` bytes),
-    // each thread its slice's CRC, then a tree of crc32_combine steps: crc(A B) = crc(A) x^(8 |B|) + crc(B)
+    // ---- CRC-32 of type + data by ONE warp (the combine step is a 32-iteration loop: eight warps running it for
+    // a handful of useful lanes each cost a fifth of the kernel).  Slices aligned to the END, so every slice but
+    // the first has exactly `slice` bytes; each lane its slice's CRC, then a shuffle tree of crc32_combine steps:
+    // crc(A B) = crc(A) x^(8 |B|) + crc(B), with |B| = slice * 2^level for every right-hand side.
     const int n_crc = 4 + data_len;
-    const int slice = (n_crc + kThreads - 1) / kThreads;
-    {
-        const int end = n_crc - (kThreads - 1 - t) * slice, begin = max(end - slice, 0);
+    if (t < 32) {
+        const int slice = (n_crc + 31) / 32;
+        const int end = n_crc - (31 - t) * slice, begin = max(end - slice, 0);
         uint32_t c = 0u;
         if (end > begin) {
             c = 0xffffffffu;
             for (int i = begin; i < end; ++i) c = s_crc[(c ^ out[4 + i]) & 255u] ^ (c >> 8);
             c ^= 0xffffffffu;
         }
-        s_part[t] = c;
-    }
-    if (t == 0) {
-        uint32_t g = x2nmodp(s_x2n, (uint64_t)slice, 3);  // x^(8 slice)
-        for (int l = 0; l < 9; ++l) {
-            s_g[l] = g;
-            g = multmodp(g, g);
+        const uint32_t g_mine = x2nmodp(s_x2n, (uint64_t)slice, 3u + (unsigned)(t & 7));  // lane l < 5: x^(8 slice 2^l)
+        for (int l = 0, stride = 1; stride < 32; ++l, stride <<= 1) {
+            const uint32_t g = __shfl_sync(0xffffffffu, g_mine, l);
+            const uint32_t right = __shfl_down_sync(0xffffffffu, c, stride);
+            if ((t & (2 * stride - 1)) == 0) c = multmodp(g, c) ^ right;
         }
+        if (t == 0) s_part[0] = c;
     }
     __syncthreads();
-    for (int l = 0, stride = 1; stride < kThreads; ++l, stride <<= 1) {
-        if ((t & (2 * stride - 1)) == 0) s_part[t] = multmodp(s_g[l], s_part[t]) ^ s_part[t + stride];
-        __syncthreads();
-    }
     if (t == 0) {
         const uint32_t crc = s_part[0];
         uint8_t* p = out + 8 + data_len;
@@ -691,7 +686,7 @@ int rt_png_encode_bands_dev(int device, const uint8_t* pixels_dev, int32_t pixel
     const size_t smem = band_smem(width, r);
     static thread_local size_t opted[64] = {0};
     cudaError_t err = cudaSuccess;
-    if (smem > 48 * 1024 && device < 64 && opted[device] < smem) {
+    if (smem + 8 * 1024 > 48 * 1024 && device < 64 && opted[device] < smem) {  // (static shared memory counts towards the 48 KB default)
         err = cudaFuncSetAttribute(png_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err == cudaSuccess) opted[device] = smem;
     }
