@@ -96,7 +96,8 @@ rt::SceneParams scene_params(const double* spheres_dev, int32_t n_spheres, const
     sp.accel = static_cast<const unsigned char*>(env->accel_dev);
     sp.accel_bytes = env->accel_bytes;
     sp.error_word = nullptr;
-    if (sp.accel != nullptr) rt::device_error_word(&sp.error_word);  // current device = the call's (DeviceScope)
+    // (the tree kernels and the exact policy's tie stack report through it; current device = the call's: DeviceScope)
+    if (sp.accel != nullptr || env->mode == RT_MODE_EXACT) rt::device_error_word(&sp.error_word);
     sp.n_spheres = n_spheres;
     sp.n_lights_used = (env->flags & RT_FLAG_ALL_POINT_LIGHTS) ? env->n_point_lights : 1;
     sp.n_dome = env->n_dome_lights;
@@ -267,6 +268,9 @@ int pending_device_error(int device) {
     if (code == rt::kDevAccelStack)
         return fail(RT_ERR_UNSUPPORTED, "an earlier launch on device %d walked a tree deeper than the traversal stack (%d): "
                     "not a blob of rt_accel_build_host; its pixels are wrong", device, rt::kAccelStack);
+    if (code == rt::kDevTieStack)
+        return fail(RT_ERR_UNSUPPORTED, "an earlier exact-policy launch on device %d met more shapes at exactly equal distances "
+                    "(duplicated shapes bouncing into each other) than its stack of pending rays holds: those pixels lack rays", device);
     return fail(RT_ERR_UNSUPPORTED, "an earlier launch on device %d reported device error %u", device, code);
 }
 

@@ -145,9 +145,12 @@ __device__ __forceinline__ float slab_enter(const RaySlabs& r, const NodeView& n
 // rounded up.
 template <class SphereT>
 __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 d, float limit_scale, double& tmin, int& sid,
-                                              unsigned long long& evaluated, SphereT&& sphere_t) {
+                                              unsigned long long& evaluated, SphereT&& sphere_t, int* ties = nullptr) {
     auto slab_limit = [&](double t) { return t < kMiss ? __fmul_ru(__double2float_ru(t), limit_scale) : INFINITY; };
+    // (`ties`: how many shapes lie at exactly the nearest distance; boxes entered at that distance are not culled --
+    // the cut is "entered beyond the limit" -- so every one of them is visited)
     auto consider = [&](int s, double t) {
+        if (ties != nullptr && t != kMiss) *ties = t < tmin ? 1 : (t == tmin ? *ties + 1 : *ties);
         if (t < tmin || (t == tmin && t != kMiss && s < sid)) {
             tmin = t;
             sid = s;

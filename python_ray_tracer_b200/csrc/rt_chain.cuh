@@ -130,43 +130,44 @@ __device__ __forceinline__ SmallScene<N> stage_small(const SceneParams& sp, cons
 // is compiled with -fmad=false).  Children of weight 0 are still traced, as the reference's unconditional
 // recursion does (shader.py:90): they add exactly 0 but count in the ray totals.
 // TREE: nearest hit and shadow test walk the BVH blob instead of the staged table.
-template <bool STATS, bool TREE>
-__device__ __forceinline__ bool bounce_exact(const SceneParams& sp, const Staged& st, const AccelView& av, const int generation,
-                                             Vec3& o, Vec3& d, Vec3& color, double& weight, unsigned long long& tests,
-                                             Counters& k) {
-    const int n = sp.n_spheres;
-    const Vec3 eye = {sp.eye[0], sp.eye[1], sp.eye[2]};
-    if (sp.max_depth > 0 && generation >= sp.max_depth) return false;
-    if (STATS) {
-        k.traced += 1;
-        k.deepest = generation + 1 > (int)k.deepest ? generation + 1 : k.deepest;
-        if (!TREE) tests += (unsigned long long)n;
-    }
 
-    // ---- nearest hit (base.py:97-105); exact ties resolve to the lowest shape index
-    double tmin = kMiss;
-    int sid = -1;
+// Nearest hit (base.py:97-105): smallest distance, the lowest shape index that has it, and how many shapes do.
+template <bool TREE>
+__device__ __forceinline__ void nearest_exact(const SceneParams& sp, const Staged& st, const AccelView& av, Vec3 o, Vec3 d,
+                                              double& tmin, int& sid, int& ties, unsigned long long& tests) {
+    tmin = kMiss;
+    sid = -1;
+    ties = 0;
     if (TREE) {
         accel_nearest(av, o, d, 1.0f, tmin, sid, tests,
-                      [&](const SphereGeom& g, int s) { return sphere_distance_exact(o, d, g, __ldg(&av.aux[s].cc)); });
+                      [&](const SphereGeom& g, int s) { return sphere_distance_exact(o, d, g, __ldg(&av.aux[s].cc)); }, &ties);
     } else {
-        for (int s = 0; s < n; ++s) {
-            double t = sphere_distance_exact(o, d, load_geom(st, s), load_aux(st, s).cc);
+        for (int s = 0; s < sp.n_spheres; ++s) {
+            const double t = sphere_distance_exact(o, d, load_geom(st, s), load_aux(st, s).cc);
             if (t < tmin) {
                 tmin = t;
                 sid = s;
+                ties = 1;
+            } else if (t == tmin && t != kMiss) {
+                ++ties;
             }
         }
     }
-    if (sid < 0) return false;
-    if (STATS) k.hits += 1;
+}
 
-    // ---- NumpyShader.create (shader.py:63-112)
+// NumpyShader.create (shader.py:63-112) for the hit of ray (o, d) on shape sid at distance t: adds weight * local
+// colour to `color`; (o, d, weight) become the mirror ray and its weight.
+template <bool STATS, bool TREE>
+__device__ __forceinline__ void shade_exact(const SceneParams& sp, const Staged& st, const AccelView& av, const int sid, const double t,
+                                            Vec3& o, Vec3& d, double& weight, Vec3& color, unsigned long long& tests, Counters& k) {
+    const int n = sp.n_spheres;
+    const Vec3 eye = {sp.eye[0], sp.eye[1], sp.eye[2]};
+    if (STATS) k.hits += 1;
     const SphereGeom g = TREE ? ldg_geom(av.geom + sid) : load_geom(st, sid);
     const double inv_r = TREE ? __ldg(&av.aux[sid].inv_r) : load_aux(st, sid).inv_r;
     const Material m = TREE ? load_material(sp, sid) : load_material(st, sid);
     const Vec3 centre = {g.cx, g.cy, g.cz};
-    const Vec3 hit = o + d * tmin;
+    const Vec3 hit = o + d * t;
     const Vec3 normal = (hit - centre) * inv_r;
     const Vec3 to_eye = norm_exact(eye - hit);
     const Vec3 nudged = hit + normal * kNudge;
@@ -232,8 +233,17 @@ __device__ __forceinline__ bool bounce_exact(const SceneParams& sp, const Staged
     // mirror direction (shader.py:151): D - (N*2)*(D.N), normalised
     d = norm_exact(d - (normal * 2.0) * dot(d, normal));
     o = nudged;
-    return true;
 }
+
+// Rays waiting their turn.  A ray normally has one child, so the chain is a loop; where several shapes lie at
+// exactly the nearest distance (a shape listed twice, coincident surfaces) the reference shades every one of
+// them and recurses from each (base.py:102-119): the first child continues the loop, the others wait here.
+struct PendingRay {
+    Vec3 o, d;
+    double weight;
+    int generation;
+};
+constexpr int kTieStack = 32;
 
 template <bool STATS, bool TREE>
 __device__ __forceinline__ Vec3 trace_chain_exact(const SceneParams& sp, const Staged& st, const AccelView& av, Vec3 o, Vec3 d,
@@ -241,9 +251,44 @@ __device__ __forceinline__ Vec3 trace_chain_exact(const SceneParams& sp, const S
     Vec3 color = {0.0, 0.0, 0.0};
     double weight = 1.0;
     unsigned long long tests = 0;
+    PendingRay pending[kTieStack];
+    int top = 0, generation = 0;
 #pragma unroll 1
-    for (int generation = 0;; ++generation)
-        if (!bounce_exact<STATS, TREE>(sp, st, av, generation, o, d, color, weight, tests, k)) break;
+    for (;;) {
+        bool goes_on = false;
+        if (!(sp.max_depth > 0 && generation >= sp.max_depth)) {
+            if (STATS) {
+                k.traced += 1;
+                k.deepest = generation + 1 > (int)k.deepest ? generation + 1 : k.deepest;
+                if (!TREE) tests += (unsigned long long)sp.n_spheres;
+            }
+            double tmin;
+            int sid, ties;
+            nearest_exact<TREE>(sp, st, av, o, d, tmin, sid, ties, tests);
+            if (sid >= 0) {
+                goes_on = true;
+                if (ties > 1) {
+                    // every other shape at that distance, highest index first onto the stack (so they come off in
+                    // the reference's order); found by testing all shapes again: ties are rare
+                    for (int s = sp.n_spheres - 1; s > sid; --s) {
+                        const SphereGeom g = TREE ? ldg_geom(av.geom + s) : load_geom(st, s);
+                        const double cc = TREE ? __ldg(&av.aux[s].cc) : load_aux(st, s).cc;
+                        if (sphere_distance_exact(o, d, g, cc) != tmin) continue;
+                        PendingRay child = {o, d, weight, generation + 1};
+                        shade_exact<STATS, TREE>(sp, st, av, s, tmin, child.o, child.d, child.weight, color, tests, k);
+                        if (top < kTieStack) pending[top++] = child;
+                        else if (sp.error_word != nullptr) *reinterpret_cast<volatile unsigned int*>(sp.error_word) = kDevTieStack;
+                    }
+                }
+                shade_exact<STATS, TREE>(sp, st, av, sid, tmin, o, d, weight, color, tests, k);
+                ++generation;
+            }
+        }
+        if (goes_on) continue;
+        if (top == 0) break;
+        --top;
+        o = pending[top].o, d = pending[top].d, weight = pending[top].weight, generation = pending[top].generation;
+    }
     if (STATS) k.tests += tests;
     return color;
 }

@@ -71,7 +71,8 @@ struct SceneParams {
 enum DeviceError : unsigned int {
     kDevOk = 0,
     kDevBadAccelBlob = 1,    // rt_env.accel_dev is not a blob of rt_accel_build_host for THIS sphere table
-    kDevAccelStack = 2       // a tree deeper than the traversal stack (not a blob of rt_accel_build_host)
+    kDevAccelStack = 2,      // a tree deeper than the traversal stack (not a blob of rt_accel_build_host)
+    kDevTieStack = 3         // exact policy: more rays pending from shapes at exactly equal distance than the stack holds
 };
 
 // Camera rows -> rays (base.py:123-141).  The linspace steps are divided on the host

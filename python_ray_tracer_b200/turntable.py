@@ -64,14 +64,73 @@ def frames_to_render(out_dir: Path, n_frames: int, rank: int = 0, world: int = 1
     return [k for k in mine if not (resume and frame_path(out_dir, k).exists())]
 
 
+def _write_atomically(path: Path, data) -> None:
+    partial = path.with_suffix(".png.tmp")
+    with open(partial, "wb") as f:
+        f.write(data)
+    os.replace(partial, path)  # atomic within the directory
+
+
+def _render_frames_device(renderer, scene_of_frame, todo, out_dir: Path, stats: Dict[str, float]) -> Dict[str, float]:
+    """The batch with the PNGs made on the GPU (``DevicePngEncoder``): per frame one trace launch (8-bit image
+    only), the band encoder and the pack kernel, which writes the ~0.6 MB file into a pinned host buffer; two
+    frames in flight, so the host writes frame ``k`` while the GPU traces and encodes frame ``k + 1``."""
+    import torch
+
+    from .infrastructure.cuda import abi
+    from .infrastructure.png import DevicePngEncoder
+
+    device = renderer.device
+    first = scene_of_frame(todo[0]).camera
+    width, height = int(first.width), int(first.height)
+    stream = torch.cuda.current_stream(device)
+    dev = torch.device("cuda", device)
+    slots = [{"rgb8": torch.empty((width * height, 3), dtype=torch.uint8, device=dev), "enc": DevicePngEncoder(width, height, device),
+              "done": torch.cuda.Event(), "start": torch.cuda.Event(enable_timing=True), "end": torch.cuda.Event(enable_timing=True),
+              "frame": None} for _ in range(2)]
+
+    def retire(slot) -> None:
+        if slot["frame"] is None:
+            return
+        slot["done"].synchronize()
+        stats["gpu_s"] += slot["start"].elapsed_time(slot["end"]) * 1e-3
+        t0 = time.perf_counter()
+        _write_atomically(frame_path(out_dir, slot["frame"]), slot["enc"].finish())
+        stats["encode_s"] += time.perf_counter() - t0
+        stats["frames"] += 1
+        slot["frame"] = None
+
+    wall0 = time.perf_counter()
+    for i, frame in enumerate(todo):
+        slot = slots[i % 2]
+        retire(slot)
+        scene = scene_of_frame(frame)
+        flat = renderer.flatten(scene)
+        slot["start"].record(stream)
+        renderer.render_rows(flat, scene.camera, 0, height, rgba8=slot["rgb8"], flags=abi.RT_FLAG_RGB8, no_planes=True)
+        slot["enc"].enqueue(slot["rgb8"], int(stream.cuda_stream))
+        slot["end"].record(stream)
+        slot["done"].record(stream)
+        slot["frame"] = frame
+    for slot in slots:
+        retire(slot)
+    abi.check(abi.load().rt_device_status(device), "rt_device_status")
+    stats["wall_s"] = time.perf_counter() - wall0
+    stats["encoder"] = "device (rt_png_encode_bands_dev + rt_png_pack_dev); encode_s = file writes"
+    return stats
+
+
 def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: int, out_dir: Path, *,
                   rank: int = 0, world: int = 1, encoder_threads: Optional[int] = None,
-                  compress_level: Optional[int] = None, resume: bool = True, bands_per_frame: int = 2) -> Dict[str, float]:
+                  compress_level: Optional[int] = None, resume: bool = True, bands_per_frame: int = 2,
+                  encoder: str = "device") -> Dict[str, float]:
     """Render this rank's frames of an ``n_frames`` batch to ``out_dir/frame_NNNN.png``.
 
     ``scene_of_frame(k)`` builds frame ``k``'s ``Scene3D`` (``scenes.turntable_scene`` for the
-    BASELINE turntable).  ``compress_level``: see ``encode_frame``.  Returns timing totals
-    (seconds) and the number of frames written.
+    BASELINE turntable).  ``encoder``: ``"device"`` (default) makes the PNGs on the GPU;
+    ``"host"`` copies the 8-bit images to the host and deflates them on a thread pool
+    (``compress_level``: see ``encode_frame``; a zlib level implies the host).  Returns timing
+    totals (seconds) and the number of frames written.
     """
     import torch
 
@@ -84,6 +143,9 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
              "wall_s": 0.0, "gpu_s": 0.0, "encode_s": 0.0, "encoder_threads": threads}
     if not todo:
         return stats
+    first_camera = scene_of_frame(todo[0]).camera
+    if encoder == "device" and compress_level is None and 1 + 3 * int(first_camera.width) <= 65000:
+        return _render_frames_device(renderer, scene_of_frame, todo, out_dir, stats)
 
     render_stream = torch.cuda.current_stream(device)
     copy_stream = torch.cuda.Stream(device)
@@ -107,10 +169,7 @@ def render_frames(renderer, scene_of_frame: Callable[[int], Scene3D], n_frames: 
     def encode_and_write(frame: int, rgba: np.ndarray) -> float:
         t0 = time.perf_counter()
         data = encode_frame(rgba, width, height, compress_level, bands_per_frame, band_pool)  # off the main thread
-        final = frame_path(out_dir, frame)
-        partial = final.with_suffix(".png.tmp")
-        partial.write_bytes(data)
-        os.replace(partial, final)  # atomic within the directory
+        _write_atomically(frame_path(out_dir, frame), data)
         return time.perf_counter() - t0
 
     def retire(slot) -> None:
@@ -173,6 +232,8 @@ def main() -> None:
     parser.add_argument("--compress-level", type=int, default=None,
                         help="zlib level for the PNGs; default: the library's own faster deflate (rt_png_deflate_rows)")
     parser.add_argument("--encoder-threads", type=int, default=None)
+    parser.add_argument("--encoder", choices=["device", "host"], default="device",
+                        help="device: PNGs made on the GPU (default); host: 8-bit images deflated on host threads")
     parser.add_argument("--no-resume", action="store_true")
     args = parser.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
@@ -185,11 +246,12 @@ def main() -> None:
     renderer = CudaRenderer(**scenes.README_GAINS, device=local, output_dtype="float32")
     stats = render_turntable(renderer, args.frames, args.out, args.width, args.height, rank=rank, world=world,
                              encoder_threads=args.encoder_threads, compress_level=args.compress_level,
-                             resume=not args.no_resume)
+                             resume=not args.no_resume, encoder=args.encoder)
     fps = stats["frames"] / stats["wall_s"] if stats["wall_s"] else 0.0
     print(f"rank {rank}/{world}: {stats['frames']} frames written ({stats['skipped']} skipped) in {stats['wall_s']:.2f} s "
-          f"= {fps:.1f} frames/s; GPU {stats['gpu_s'] * 1e3:.1f} ms total, encoder {stats['encode_s']:.2f} s over "
-          f"{stats['encoder_threads']} threads")
+          f"= {fps:.1f} frames/s; GPU {stats['gpu_s'] * 1e3:.1f} ms total, "
+          + (f"PNGs made on the device, {stats['encode_s']:.2f} s of file writes" if "encoder" in stats else
+             f"encoder {stats['encode_s']:.2f} s over {stats['encoder_threads']} threads"))
 
 
 if __name__ == "__main__":

@@ -310,14 +310,17 @@ def test_edge_cases(rt, c_oracle):
     assert empty.numpy().shape == (3, 0)
     # zero rows
     assert renderer.render_rows(renderer.flatten(behind), behind.camera, 5, 5).numpy().shape == (3, 0)
-    # exact tie between two identical spheres: the reference adds both contributions (and
-    # recurses on both); the kernel shades the lowest index once -- documented deviation
+    # exact tie between two identical spheres: the reference adds both contributions (and recurses on both,
+    # base.py:102-119).  The exact policy does the same (a lone sphere: twice the colour); the fast policy
+    # shades the lowest index once -- documented deviation, see test_a_shape_listed_twice
     one = Scene3D([NumpySphere(NumpyVector3D(0, 0, 3), 1.0, NumpyRGBColor(1, 0, 0))],
                   [PointLight(NumpyVector3D(5, 10, -10))], Camera(NumpyVector3D(0, 0.2, -2), 16, 9))
     two = Scene3D(list(one.shapes) * 2, one.lights, one.camera)
-    a = renderer.raytrace_scene(one.camera.position, renderer.get_ray_directions(one.camera), one).numpy()
-    b = renderer.raytrace_scene(two.camera.position, renderer.get_ray_directions(two.camera), two).numpy()
-    assert np.array_equal(a, b)
+    for precision in PRECISIONS:
+        r = rt(precision)
+        a = r.raytrace_scene(one.camera.position, r.get_ray_directions(one.camera), one).numpy()
+        b = r.raytrace_scene(two.camera.position, r.get_ray_directions(two.camera), two).numpy()
+        assert np.array_equal(b, a + a if precision == "exact" else a) and a.max() > 0
     # all-point-lights extension against its own CPU restatement (not the reference)
     case = load_case("c3_small_48_192x108_depth8")
     ext = rt("exact", max_depth=8, all_point_lights=True)
@@ -494,23 +497,25 @@ def test_peer_framebuffer_two_processes(rt):
     assert np.array_equal(frame, want8)
 
 
-def test_turntable_batch_writes_reference_frames(rt, c_oracle, tmp_path):
-    """Config 5 at small size: the batch driver (render || copy || parallel PNG encode) writes
-    the frames this rank owns; frame 37 decodes to the reference's fixture within 1 LSB,
-    a second call resumes (writes nothing)."""
+@pytest.mark.parametrize("encoder", ["device", "host"])
+def test_turntable_batch_writes_reference_frames(rt, c_oracle, tmp_path, encoder):
+    """Config 5 at small size: the batch driver (PNGs made on the device, or render || copy || parallel host
+    encode) writes the frames this rank owns; frame 37 decodes to the reference's fixture within 1 LSB, a frame
+    left half-written by a killed run is rendered again, a second call resumes (writes nothing)."""
     from python_ray_tracer_b200 import scenes, turntable
     from python_ray_tracer_b200.infrastructure import CudaRenderer
     from python_ray_tracer_b200.infrastructure.png import read_png
 
     case = load_case("turntable37_160x90")
     renderer = CudaRenderer(**scenes.README_GAINS, precision="fast")
-    stats = turntable.render_turntable(renderer, 256, tmp_path, 160, 90, rank=37, world=64, encoder_threads=4)
-    assert stats["frames"] == 4 and stats["skipped"] == 0
+    turntable.frame_path(tmp_path, 101).with_suffix(".png.tmp").write_bytes(b"\x89PNG cut short")
+    stats = turntable.render_turntable(renderer, 256, tmp_path, 160, 90, rank=37, world=64, encoder_threads=4, encoder=encoder)
+    assert stats["frames"] == 4 and stats["skipped"] == 0 and not list(tmp_path.glob("*.tmp"))
     assert sorted(p.name for p in tmp_path.glob("*.png")) == [f"frame_{k:04d}.png" for k in (37, 101, 165, 229)]
     got = read_png(turntable.frame_path(tmp_path, 37))
     assert got.shape == (90, 160, 3)
     assert_png_parity(got, c_oracle.quantize(case.rgb), "turntable frame 37")
-    again = turntable.render_turntable(renderer, 256, tmp_path, 160, 90, rank=37, world=64, encoder_threads=4)
+    again = turntable.render_turntable(renderer, 256, tmp_path, 160, 90, rank=37, world=64, encoder_threads=4, encoder=encoder)
     assert again["frames"] == 0 and again["skipped"] == 4
 
 
@@ -575,6 +580,30 @@ def test_bvh_gives_the_same_picture_as_testing_every_sphere(precision, c_oracle)
     # the all-lights extension walks the tree once per light
     plain, tree = pair(max_depth=8, all_point_lights=True)
     assert np.array_equal(_render(plain, case).numpy(), _render(tree, case).numpy())
+
+
+def test_a_shape_listed_twice(rt, c_oracle):
+    """Ties at the nearest distance, pinned by a reference-rendered fixture (tests/golden/make_stress.py:
+    tie_case): the reference lets every shape at exactly the nearest distance contribute and recurse
+    (base.py:102-119), so a duplicated sphere comes out twice as bright.  The exact policy (and the C oracle)
+    does the same, with and without the sphere tree, ray totals included.  The fast policy shades the lowest
+    index once -- the one documented deviation: it renders the reference's picture of the scene WITHOUT the
+    duplicate."""
+    z = np.load(GOLDEN / "tie_duplicate_48x27.npz")
+    case = load_case("tie_duplicate_48x27")
+    seen_twice = (np.abs(z["rgb"] - z["rgb_single"]) > 1e-12).any(axis=0)
+    assert 50 < int(seen_twice.sum()) < case.width * case.height // 2
+    assert (z["rgb"][:, seen_twice].sum(axis=0) > z["rgb_single"][:, seen_twice].sum(axis=0)).all()  # the reference adds both
+    want, counters = c_oracle.render(case.flat, case.width, case.height, max_depth=4)
+    assert_linear_parity(want, z["rgb"], 1e-12, "oracle vs reference on the duplicated scene")
+    for accel in (False, True):
+        color = _render(rt("exact", max_depth=4, accel=accel), case)
+        assert_linear_parity(color.numpy(), z["rgb"], EXACT_TOL, f"duplicate sphere/exact/tree={accel}")
+        k = color.counters()
+        assert (k["rays_traced"], k["hits_shaded"]) == (case.traced, int(counters[1])), (k, case.traced)
+        fast = _render(rt("fast", max_depth=4, accel=accel), case).numpy()
+        assert_linear_parity(fast, z["rgb_single"], 1e-4, f"duplicate sphere/fast/tree={accel}")
+        assert_linear_parity(fast[:, ~seen_twice], z["rgb"][:, ~seen_twice], 1e-4, "pixels without a tie")
 
 
 def test_camera_rays_that_do_not_start_at_the_scene_camera(rt, c_oracle):
