@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -22,7 +23,7 @@ struct Scratch {
     size_t bytes = 0;
 };
 
-constexpr int kMaxChunks = 8;
+constexpr int kMaxChunks = 16;
 
 struct DeviceCache {
     cudaStream_t stream = nullptr;       // uploads and kernels
@@ -216,15 +217,20 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
     // the frame costs about one chunk's kernel plus the copy time.  Small frames: one chunk.
     const int rows = row1 - row0;
     int chunks = 1;
-    if (n >= (int64_t)1 << 20) chunks = 4;
-    if (n >= (int64_t)1 << 23) chunks = kMaxChunks;
+    if (n >= (int64_t)1 << 20) chunks = 8;  // (profiles/r02/host_path.txt: 1080p RGB8 0.164 ms with 8, 0.180 with 4, 0.186 with 1)
+    int head_div = 32;
+    if (const char* e = getenv("RT_HOST_CHUNKS")) {  // measurement knob (tools/host_chunks_sweep.sh): "chunks[,head divisor]"
+        int c = 0, d = 0;
+        if (sscanf(e, "%d,%d", &c, &d) >= 1 && c >= 1 && c <= kMaxChunks) chunks = c;
+        if (d >= 2) head_div = d;
+    }
     if (chunks > rows) chunks = rows > 0 ? rows : 1;
     // Nothing is copied while the first chunk renders, so it is a small one: with more than one
     // chunk the first takes 1/16 of the rows and the others share the rest evenly.
     auto chunk_start = [&](int i) -> int {
         if (i <= 0) return 0;
         if (i >= chunks) return rows;
-        const int64_t head = rows / 16;
+        const int64_t head = rows / head_div;
         return (int)((head + ((int64_t)rows - head) * (i - 1) / (chunks - 1)) & ~3LL);  // multiples of 4 rows (the patch height)
     };
     char* rgb_base = static_cast<char*>(c->rgb.ptr);
