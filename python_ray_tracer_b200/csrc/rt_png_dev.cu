@@ -340,12 +340,12 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
     uint32_t* out_words = reinterpret_cast<uint32_t*>(out);
     const int out_words_n = (cap + kBandSlack + kChunkOverhead + 3) / 4;
 
-    if (t < 256) {
-        s_lit[t] = code.lit[t];
-        s_match[t] = code.match[t];
-        uint32_t c = (uint32_t)t;
+    for (int i = t; i < 256; i += kThreads) {
+        s_lit[i] = code.lit[i];
+        s_match[i] = code.match[i];
+        uint32_t c = (uint32_t)i;
         for (int k = 0; k < 8; ++k) c = c & 1u ? (c >> 1) ^ kCrcPoly : c >> 1;
-        s_crc[t] = c;
+        s_crc[i] = c;
     }
     if (t < 32) s_x2n[t] = code.x2n[t];
 
