@@ -19,9 +19,10 @@ One JSON line is printed by rank 0.  Besides the contract's keys it carries
 Metric: Mrays/s = primary rays (= pixels) per second / 1e6; ``ms_per_step`` is ms/frame.
 ``value`` is device time with the scene resident in HBM (CUDA events on the launch stream,
 L2 flushed between steps, max over ranks).  ``e2e`` is the same frame through the host-buffer
-C-ABI entry point ``rt_render_frame_host``: scene upload, kernel, and the 8-bit image
-``save_image`` consumes (base.py:143-151) copied into pinned host memory, every step; the figure
-with the linear float planes copied back instead is reported beside it.
+C-ABI entry point ``rt_render_png_host``: kernel, PNG encoder on the device, the finished file
+``save_image`` writes (base.py:143-151) in pinned host memory, every step.  Beside it: the 8-bit
+image ``save_image`` consumes brought back instead (``rgb8_image``, ``rt_render_frame_host``; PCIe-bound,
+and bound by the host when several ranks copy at once) and the linear float planes.
 """
 
 from __future__ import annotations
@@ -447,25 +448,34 @@ def host_path(g: Gpu, tables, cam, width, height, use_tree: bool) -> dict:
     flat = tables[-1][3]
     px = width * height * g.world
     rate = lambda ms: px / (ms * 1e-3) / 1e6  # noqa: E731
-    return {
-        "value": rate(rgb8_ms), "unit": UNIT, "ms_per_step": rgb8_ms,
-        "h2d_bytes_per_step": int(flat.spheres.nbytes + flat.point_lights.nbytes),
-        "d2h_bytes_per_step": int(rgb8_host.numel()),
-        "d2h_gb_per_s_per_gpu": rgb8_host.numel() / (rgb8_ms * 1e-3) / 1e9,
+    table_bytes = int(flat.spheres.nbytes + flat.point_lights.nbytes)
+    rgb8 = {
+        "value": rate(rgb8_ms), "unit": UNIT, "ms_per_step": rgb8_ms, "h2d_bytes_per_step": table_bytes,
+        "d2h_bytes_per_step": int(rgb8_host.numel()), "d2h_gb_per_s_per_gpu": rgb8_host.numel() / (rgb8_ms * 1e-3) / 1e9,
+        "api": "rt_render_frame_host(rgb8_host): kernel (8-bit image quantised by the trace kernel, no linear planes written) + D2H "
+               "of the RGB8 image save_image consumes (base.py:143-151) into pinned host memory, 8 row chunks pipelined",
+    }
+    extras = {
         "host_cpus_bound": len(g.bound) if g.bound else None,
-        "api": "rt_render_frame_host(rgb8_host): scene upload + kernel (8-bit image quantised by the trace kernel, no linear "
-               "planes written) + D2H of the RGB8 image save_image consumes (base.py:143-151) into pinned host memory, row "
-               "chunks pipelined (kernel of chunk i+1 under the copy of chunk i)",
         # what raytrace_scene returns to a caller that reads .x/.y/.z: the linear planes
         "linear_planes_f32": {"ms_per_step": planes_ms, "value": rate(planes_ms), "d2h_bytes_per_step": int(rgb_host.numel() * 4),
                               "d2h_gb_per_s_per_gpu": rgb_host.numel() * 4 / (planes_ms * 1e-3) / 1e9},
         "planes_and_rgb8": {"ms_per_step": both_ms, "value": rate(both_ms),
                             "d2h_bytes_per_step": int(rgb_host.numel() * 4 + rgb8_host.numel())},
-        # the finished PNG instead of the 8-bit image: traced, quantised, filtered, deflated and packed on the device
-        "png_file": None if png_ms is None else {
-            "ms_per_step": png_ms, "value": rate(png_ms), "d2h_bytes_per_step": png_bytes,
-            "api": "rt_render_png_host: trace kernel (8-bit image) + rt_png_encode_bands_dev + rt_png_pack_dev writing the file "
-                   "into the caller's pinned buffer; the file's last byte read on the host"},
+        "d2h_note": "with N ranks copying at once this box moves 130-170 GB/s to the host in all (plain cudaMemcpyAsync, no kernel: "
+                    "profiles/r02/d2h_aggregate_n8.txt), so paths that bring pixels back stop scaling; the PNG path brings back a tenth",
+    }
+    if png_ms is None:  # rows too wide for the device encoder: the 8-bit image is the headline
+        return {**rgb8, **extras, "png_file": None}
+    # Headline: save_image's FILE in host memory -- the end of the reference's pipeline (application.py:43-52), one step
+    # further than the 8-bit image it is made from: traced, quantised, filtered, deflated and packed on the device.
+    return {
+        "value": rate(png_ms), "unit": UNIT, "ms_per_step": png_ms, "h2d_bytes_per_step": table_bytes,
+        "d2h_bytes_per_step": png_bytes,
+        "api": "rt_render_png_host: trace kernel (8-bit image, stays on the device) + rt_png_encode_bands_dev + rt_png_pack_dev "
+               "writing the finished PNG into the caller's pinned buffer; the file's last byte read on the host",
+        "rgb8_image": rgb8,
+        **extras,
     }
 
 
