@@ -182,10 +182,8 @@ __device__ __forceinline__ unsigned int quantize_channel(double v) {
 // the exact product 255 * v (which FP64 holds exactly: 8 x 24 bits), so the fused 8-bit image equals
 // rt_quantize_dev of the stored planes, bit for bit.
 __device__ __forceinline__ unsigned int quantize_channel(float v) {
-    const int bits = __float_as_int(v);
-    if (bits < 0) return 0u;
-    if (bits >= 0x3f800000) return 255u;
-    return (unsigned int)__fmul_rz(255.0f, v);
+    // saturate is a modifier of the multiply on sm_100a: two instructions, no branch
+    return __float2uint_rz(__fmul_rz(255.0f, __saturatef(v)));
 }
 
 template <typename T>
@@ -232,9 +230,8 @@ __device__ __forceinline__ void store_pixel(const OutputParams& out, long long p
     }
     if (out.rgba8 != nullptr) {
         if (out.bytes8 == kRgba8) {
-            uchar4 q = make_uchar4((unsigned char)quantize_channel(c.x), (unsigned char)quantize_channel(c.y),
-                                   (unsigned char)quantize_channel(c.z), 255);
-            reinterpret_cast<uchar4*>(out.rgba8)[p] = q;
+            reinterpret_cast<unsigned int*>(out.rgba8)[p] =
+                quantize_channel(c.x) | (quantize_channel(c.y) << 8) | (quantize_channel(c.z) << 16) | 0xff000000u;
         } else if (out.bytes8 == kRgb8Bytes) {
             out.rgba8[3 * p + 0] = (unsigned char)quantize_channel(c.x);
             out.rgba8[3 * p + 1] = (unsigned char)quantize_channel(c.y);
