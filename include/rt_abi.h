@@ -389,6 +389,30 @@ int rt_render_png_host(int device, const double* spheres_host, int32_t n_spheres
                        const double* point_lights_host, const rt_env* env, const rt_camera* cam,
                        uint8_t* png_host, int64_t capacity, int64_t* png_bytes_out);
 
+/*
+ * rt_png_encode_static_dev -- rt_png_encode_bands_dev + rt_png_pack_dev for one whole image, ALLOCATING NOTHING:
+ * the band scratch is a file-scope device array of RT_PNG_STATIC_SCRATCH_BYTES inside the library instead of
+ * memory the caller made.  It has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  No cudaMalloc, cudaFree or allocating library routine is called; the caller still passes the
+ * input and both outputs, and the file is byte for byte the one the two calls above produce.
+ *   pixels_dev            height rows of 8-bit pixels (pixel_bytes = 3 or 4, rows row_stride bytes apart)
+ *   png_out, capacity     the file (device memory or device-mapped pinned host memory; rt_png_file_bound() suffices)
+ *   png_bytes_out         its size, written by the pack kernel (0 if capacity was too small)
+ * Limit: images with rt_png_scratch_bytes(width, height) <= RT_PNG_STATIC_SCRATCH_BYTES (8 MiB: every frame up to
+ * 1920 x 1080, e.g. 2048 x 1024); larger ones return RT_ERR_UNSUPPORTED with the two sizes in rt_last_error().
+ * Every GPU that loads the library holds the array until the process exits.  All calls on a device SHARE it, and it
+ * keeps the last call's contents (nothing in it has to start at zero: every byte that is read was written by the
+ * same call): two calls whose kernels overlap on the GPU -- different streams, or replays of two captured graphs
+ * at once -- race; order them on one stream or with events.  The array's device address is looked up
+ * (cudaGetSymbolAddress) on the first call per device, which like any first launch also loads the module: make
+ * that call before capturing.  Only enqueues work on `stream`.
+ */
+#define RT_PNG_STATIC_SCRATCH_BYTES (8u << 20)
+int rt_png_encode_static_dev(int device, const uint8_t* pixels_dev, int32_t pixel_bytes, int64_t row_stride,
+                             int32_t width, int32_t height, uint8_t* png_out, int64_t capacity,
+                             uint64_t* png_bytes_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -737,3 +737,55 @@ int rt_png_pack_dev(int device, int32_t width, int32_t height, const void* scrat
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// rt_png_encode_static_dev: the two calls above for a whole image, with the band scratch in a file-scope device
+// array instead of memory the caller allocated -- for callers that cannot call cudaMalloc (graph capture, serving
+// loops, harnesses that forbid it).  Every GPU that loads the library holds the array until the process exits.
+// In HOST code `g_png_static_scratch` is only a stand-in for the symbol, not a device address: the address a
+// kernel can use comes from cudaGetSymbolAddress, asked once per device with that device current.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_png_static_scratch[RT_PNG_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kStaticDevices = 64;
+void* g_static_scratch_ptr[kStaticDevices] = {nullptr};  // device address of the array on device d, once asked for
+}  // namespace
+
+extern "C" int rt_png_encode_static_dev(int device, const uint8_t* pixels_dev, int32_t pixel_bytes, int64_t row_stride,
+                                        int32_t width, int32_t height, uint8_t* png_out, int64_t capacity,
+                                        uint64_t* png_bytes_out, void* stream) {
+    if (pixels_dev == nullptr || png_out == nullptr || png_bytes_out == nullptr || (pixel_bytes != 3 && pixel_bytes != 4) ||
+        width <= 0 || height <= 0 || row_stride < (int64_t)width * pixel_bytes || capacity < 128)
+        return png_fail(RT_ERR_BAD_ARG, "rt_png_encode_static_dev: NULL pointer or bad size");
+    if (device < 0 || device >= kStaticDevices) return png_fail(RT_ERR_NO_DEVICE, "rt_png_encode_static_dev: device index out of range");
+    const int64_t need = rt_png_scratch_bytes(width, height);
+    if (need < 0 || need > (int64_t)RT_PNG_STATIC_SCRATCH_BYTES) {
+        char message[320];
+        snprintf(message, sizeof(message),
+                 "rt_png_encode_static_dev: a %d x %d image needs %lld bytes of band scratch, the static array holds %lld "
+                 "(RT_PNG_STATIC_SCRATCH_BYTES); use rt_png_encode_bands_dev + rt_png_pack_dev with your own scratch",
+                 (int)width, (int)height, (long long)need, (long long)RT_PNG_STATIC_SCRATCH_BYTES);
+        return png_fail(RT_ERR_UNSUPPORTED, message);
+    }
+    void* scratch = __atomic_load_n(&g_static_scratch_ptr[device], __ATOMIC_ACQUIRE);
+    if (scratch == nullptr) {  // set-up, once per device, with that device current (two threads racing here ask twice and get the same answer)
+        int previous = -1;
+        cudaGetDevice(&previous);
+        if (previous != device && cudaSetDevice(device) != cudaSuccess) return png_fail(RT_ERR_NO_DEVICE, "rt_png_encode_static_dev: cudaSetDevice failed");
+        const cudaError_t err = cudaGetSymbolAddress(&scratch, g_png_static_scratch);
+        if (previous >= 0 && previous != device) cudaSetDevice(previous);
+        if (err != cudaSuccess || scratch == nullptr) {
+            char message[160];
+            snprintf(message, sizeof(message), "rt_png_encode_static_dev: cudaGetSymbolAddress failed: %s", cudaGetErrorString(err));
+            return png_fail(RT_ERR_CUDA, message);
+        }
+        __atomic_store_n(&g_static_scratch_ptr[device], scratch, __ATOMIC_RELEASE);
+    }
+    // Nothing in the array has to start at zero: the band kernel writes every byte the pack kernel reads (each
+    // band's chunk, size and Adler sums, for every band of the image), so what the last call left is never read.
+    const int status = rt_png_encode_bands_dev(device, pixels_dev, pixel_bytes, row_stride, height, width, height, 0, height, 1,
+                                               scratch, (int64_t)RT_PNG_STATIC_SCRATCH_BYTES, stream);
+    if (status != RT_OK) return status;
+    return rt_png_pack_dev(device, width, height, scratch, png_out, capacity, png_bytes_out, stream);
+}
