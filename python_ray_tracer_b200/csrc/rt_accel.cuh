@@ -12,6 +12,21 @@
 
 namespace rt {
 
+// Measurement builds only (-DRT_ACCEL_PROBE=k, tools/c3_probe.sh): the `evaluated` counter counts something else
+// than sphere tests.  1 / 2: inner-node visits per thread / per warp;  3 / 4: leaf visits per thread / per warp;
+// 5 / 6: traversals per thread / per warp.
+#ifndef RT_ACCEL_PROBE
+#define RT_ACCEL_PROBE 0
+#endif
+__device__ __forceinline__ void accel_probe(unsigned long long& evaluated, int what, unsigned long long sphere_tests) {
+#if RT_ACCEL_PROBE == 0
+    if (what == 0) evaluated += sphere_tests;
+#else
+    const bool leader = (threadIdx.x & 31) == (unsigned)(__ffs(__activemask()) - 1);
+    if (what == (RT_ACCEL_PROBE + 1) / 2 && ((RT_ACCEL_PROBE & 1) || leader)) evaluated += 1ull;
+#endif
+}
+
 struct AccelView {
     const AccelNode* nodes;
     const int* order;
@@ -160,7 +175,8 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
         const int s = __ldg(av.large + i);
         consider(s, sphere_t(ldg_geom(av.geom + s), s));
     }
-    evaluated += (unsigned long long)av.n_large;
+    accel_probe(evaluated, 0, (unsigned long long)av.n_large);
+    accel_probe(evaluated, 3, 0);
     if (av.n_nodes == 0) return;
     const RaySlabs ray = ray_slabs(o, d, av.extent);
     float stack_t[kAccelStack];  // entry distance of a pushed box
@@ -181,9 +197,11 @@ __device__ __forceinline__ void accel_nearest(const AccelView& av, Vec3 o, Vec3 
                 const int s = __ldg(av.order + slot);
                 consider(s, sphere_t(ldg_geom(av.leaf_geom + slot), s));
             }
-            evaluated += (unsigned long long)count;
+            accel_probe(evaluated, 0, (unsigned long long)count);
+            accel_probe(evaluated, 2, 0);
             limit = slab_limit(tmin);
         } else {
+            accel_probe(evaluated, 1, 0);
             const NodeView a = ldg_node(av.nodes + first), b = ldg_node(av.nodes + first + 1);
             bool hit_a, hit_b;
             const float ta = slab_enter(ray, a, limit, hit_a), tb = slab_enter(ray, b, limit, hit_b);
@@ -229,7 +247,8 @@ __device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, V
         const double t = sphere_t(ldg_geom(av.geom + s), s);
         if (t < own) return true;
     }
-    evaluated += (unsigned long long)av.n_large;
+    accel_probe(evaluated, 0, (unsigned long long)av.n_large);
+    accel_probe(evaluated, 3, 0);
     if (av.n_nodes == 0) return false;
     const RaySlabs ray = ray_slabs(p, l, av.extent);
     const float limit = own < kMiss ? __fmul_ru(__double2float_ru(own), limit_scale) : INFINITY;
@@ -251,8 +270,10 @@ __device__ __forceinline__ bool accel_occluded(const AccelView& av, int s_own, V
                 const double t = sphere_t(ldg_geom(av.leaf_geom + slot), s);
                 if (t < own) return true;
             }
-            evaluated += (unsigned long long)count;
+            accel_probe(evaluated, 0, (unsigned long long)count);
+            accel_probe(evaluated, 2, 0);
         } else {
+            accel_probe(evaluated, 1, 0);
             const NodeView a = ldg_node(av.nodes + first), b = ldg_node(av.nodes + first + 1);
             bool hit_a, hit_b;
             slab_enter(ray, a, limit, hit_a);
