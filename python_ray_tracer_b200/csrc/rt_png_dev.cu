@@ -92,6 +92,13 @@ struct BandJob {
     long long slot_bytes;
     uint32_t* sizes;          // [n_bands_of_image] bytes of band b's chunk
     uint32_t* adlers;         // [n_bands_of_image] Adler-32 of band b's filtered bytes (as if it started a stream)
+    // CRC-32 of a chunk by all threads: thread t takes `crc_slice` bytes (slices aligned to the chunk's END, so every
+    // slice but the first is full), then a tree of crc32_combine steps  crc(A B) = crc(A) x^(8 |B|) + crc(B)  whose
+    // right-hand sides are crc_slice * 2^level bytes long.  The multipliers are fixed per launch, so the products are
+    // sums over the set bits of crc(A) of crc_mul[level][k] = x^k * x^(8 crc_slice 2^level) mod the polynomial (made on
+    // the host): 32 independent AND / XORs against constant-bank operands instead of a 32-step shift-and-add loop.
+    int crc_slice;
+    uint32_t crc_mul[6][32];  // levels 0..4: inside a warp; 5: one warp's worth of bytes (Horner over the warps)
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -299,9 +306,27 @@ __device__ __forceinline__ bool continues_run(const uint8_t* S, int i) { return 
 //   rem % 258 = 1, the run started at i - 1   second byte of a two-byte head: literal
 //   otherwise                         inside a match: nothing
 // emit(i, entry) is called for every byte with its token's table entry (bits | count << 24; 0 = nothing).
+// `all_run`: every byte of the piece continues a run (black sky, flat colour: most pieces of a rendered frame).  Then
+// bytes a + 2 .. b - 1 lie inside the run whatever is to the left of the piece, and only the 258-boundaries among them
+// carry a token -- found by arithmetic on rem(i) = run_out + (b - i), no byte is looked at; bytes a + 1 and a take the
+// general rule (the run may start at a, and its head may be the two literals a, a + 1).
 template <class Emit>
-__device__ __forceinline__ void walk_tokens(const uint8_t* S, int a, int b, int run_out, const uint32_t* lit,
+__device__ __forceinline__ void walk_tokens(const uint8_t* S, int a, int b, int run_out, bool all_run, const uint32_t* lit,
                                             const uint32_t* match, Emit&& emit) {
+    if (all_run && b > a) {
+        const int span = b - a;
+        for (int r = ((run_out + 258) / 258) * 258; r <= run_out + span - 2; r += 258) emit(b - (r - run_out), match[255]);
+        const bool m1 = continues_run(S, a - 1), m2 = continues_run(S, a - 2);
+        if (span >= 2) {
+            const int q1 = (run_out + span - 1) % 258;
+            emit(a + 1, q1 == 0 ? match[255] : ((q1 == 1 && !m1) ? lit[S[a + 1]] : 0u));
+        }
+        const int q0 = (run_out + span) % 258;
+        const uint32_t literal = lit[S[a]];
+        const uint32_t head = q0 >= 3 ? match[q0 - 3] : literal;
+        emit(a, q0 == 0 ? match[255] : (!m1 ? head : ((q0 == 1 && !m2) ? literal : 0u)));
+        return;
+    }
     int q = run_out % 258;  // rem(i + 1) mod 258
     bool cur = continues_run(S, b - 1), n1 = continues_run(S, b - 2), n2;
     for (int i = b - 1; i >= a; --i) {
@@ -319,13 +344,21 @@ __device__ __forceinline__ void walk_tokens(const uint8_t* S, int a, int b, int 
     }
 }
 
+// c(x) * g(x) mod the CRC-32 polynomial for a multiplier fixed per launch: T[k] = x^k g(x), bit 31 - k of c selects it
+__device__ __forceinline__ uint32_t crc_mul_fixed(const uint32_t (&T)[32], uint32_t c) {
+    uint32_t r = 0u;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) r ^= (uint32_t)((int32_t)(c << k) >> 31) & T[k];
+    return r;
+}
+
 __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constant__ PngCode code, const __grid_constant__ BandJob job) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ uint32_t s_lit[256], s_match[256], s_crc[256], s_x2n[32];
+    __shared__ uint32_t s_lit[256], s_match[256], s_crc[256], s_wcrc[kThreads / 32];
     __shared__ uint32_t s_len[kThreads], s_lead[kThreads];
     __shared__ uint32_t s_scan[kThreads / 32 + 1];
     __shared__ unsigned long long s_sum[kThreads / 32];
-    __shared__ uint32_t s_part[1];
+    __shared__ uint32_t s_wsum[kThreads / 32], s_wopen[kThreads / 32];
 
     const int t = threadIdx.x;
     const int line = 1 + 3 * job.width;
@@ -347,7 +380,6 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
         for (int k = 0; k < 8; ++k) c = c & 1u ? (c >> 1) ^ kCrcPoly : c >> 1;
         s_crc[i] = c;
     }
-    if (t < 32) s_x2n[t] = code.x2n[t];
 
     // ---- filter 1 (Sub): byte minus the byte of the pixel to the left; Adler-32 sums on the way.
     // Packed RGB rows are first brought into shared memory (the `out` area is free until the tokens are
@@ -409,16 +441,38 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
         s_len[t] = (uint32_t)(b - a);
         s_lead[t] = (uint32_t)rem;
     }
-    __syncthreads();
-    int run_out = 0;
-    for (int u = t + 1; u < kThreads; ++u) {  // (a run longer than a piece -- black sky -- is summed piece by piece)
-        run_out += (int)s_lead[u];
-        if (s_lead[u] != s_len[u]) break;
+    // run_out(t) = lead(t + 1) + lead(t + 2) + ... up to and including the first piece that is not all run (a run longer
+    // than a piece -- black sky -- is summed piece by piece): a suffix scan under (s1, o1) o (s2, o2) = (s1 + (o1 ? s2 : 0),
+    // o1 && o2), by shuffles inside the warps and a walk over the (at most seven) warps to the right
+    const bool all_run = s_lead[t] == s_len[t];
+    int run_out;
+    {
+        const int lane = t & 31, warp = t >> 5;
+        int s = (int)s_lead[t];
+        bool o = all_run;
+        for (int d = 1; d < 32; d <<= 1) {
+            const int s2 = __shfl_down_sync(0xffffffffu, s, d);
+            const int o2 = __shfl_down_sync(0xffffffffu, (int)o, d);
+            if (lane + d < 32) {
+                s += o ? s2 : 0;
+                o = o && (o2 != 0);
+            }
+        }
+        if (lane == 0) s_wsum[warp] = s, s_wopen[warp] = o ? 1u : 0u;
+        int es = __shfl_down_sync(0xffffffffu, s, 1);
+        int eo = __shfl_down_sync(0xffffffffu, (int)o, 1);
+        if (lane == 31) es = 0, eo = 1;
+        __syncthreads();
+        for (int w = warp + 1; w < kThreads / 32 && eo; ++w) {
+            es += (int)s_wsum[w];
+            eo = (int)s_wopen[w];
+        }
+        run_out = es;
     }
 
     // ---- bit positions
     uint32_t my_bits = 0;
-    walk_tokens(filt, a, b, run_out, s_lit, s_match, [&](int, uint32_t entry) { my_bits += entry >> 24; });
+    walk_tokens(filt, a, b, run_out, all_run, s_lit, s_match, [&](int, uint32_t entry) { my_bits += entry >> 24; });
     uint32_t token_bits = 0;
     const uint32_t my_bit = block_exclusive_sum(my_bits, s_scan, &token_bits);
     const int prefix = band == 0 ? 2 : 0;  // the zlib header travels in the first band's chunk
@@ -443,7 +497,7 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
         }
         // the piece's tokens from its last one back to its first, each at its own bit position
         uint32_t bit = bit0 + code.header_bits + my_bit + my_bits;
-        walk_tokens(filt, a, b, run_out, s_lit, s_match, [&](int, uint32_t entry) {
+        walk_tokens(filt, a, b, run_out, all_run, s_lit, s_match, [&](int, uint32_t entry) {
             const uint32_t nb = entry >> 24;
             bit -= nb;
             if (nb) put_bits(bit, entry);
@@ -471,31 +525,30 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
     }
     __syncthreads();
 
-    // ---- CRC-32 of type + data by ONE warp (the combine step is a 32-iteration loop: eight warps running it for
-    // a handful of useful lanes each cost a fifth of the kernel).  Slices aligned to the END, so every slice but
-    // the first has exactly `slice` bytes; each lane its slice's CRC, then a shuffle tree of crc32_combine steps:
-    // crc(A B) = crc(A) x^(8 |B|) + crc(B), with |B| = slice * 2^level for every right-hand side.
+    // ---- CRC-32 of type + data by every thread (BandJob::crc_slice): a band of noise or fine gradients is a chunk of
+    // several KB, and one warp walking it byte by byte (two dependent shared-memory loads per byte) followed by bit-serial
+    // combine steps was the longest serial stretch of such a block
     const int n_crc = 4 + data_len;
-    if (t < 32) {
-        const int slice = (n_crc + 31) / 32;
-        const int end = n_crc - (31 - t) * slice, begin = max(end - slice, 0);
+    {
+        const int end = n_crc - (kThreads - 1 - t) * job.crc_slice, begin = max(end - job.crc_slice, 0);
         uint32_t c = 0u;
         if (end > begin) {
             c = 0xffffffffu;
             for (int i = begin; i < end; ++i) c = s_crc[(c ^ out[4 + i]) & 255u] ^ (c >> 8);
             c ^= 0xffffffffu;
         }
-        const uint32_t g_mine = x2nmodp(s_x2n, (uint64_t)slice, 3u + (unsigned)(t & 7));  // lane l < 5: x^(8 slice 2^l)
-        for (int l = 0, stride = 1; stride < 32; ++l, stride <<= 1) {
-            const uint32_t g = __shfl_sync(0xffffffffu, g_mine, l);
-            const uint32_t right = __shfl_down_sync(0xffffffffu, c, stride);
-            if ((t & (2 * stride - 1)) == 0) c = multmodp(g, c) ^ right;
+#pragma unroll
+        for (int l = 0; l < 5; ++l) {
+            const uint32_t right = __shfl_down_sync(0xffffffffu, c, 1 << l);
+            const uint32_t left = crc_mul_fixed(job.crc_mul[l], c);
+            if ((t & ((2 << l) - 1)) == 0) c = left ^ right;
         }
-        if (t == 0) s_part[0] = c;
+        if ((t & 31) == 0) s_wcrc[t >> 5] = c;
     }
     __syncthreads();
     if (t == 0) {
-        const uint32_t crc = s_part[0];
+        uint32_t crc = s_wcrc[0];
+        for (int w = 1; w < kThreads / 32; ++w) crc = crc_mul_fixed(job.crc_mul[5], crc) ^ s_wcrc[w];
         uint8_t* p = out + 8 + data_len;
         p[0] = (uint8_t)(crc >> 24), p[1] = (uint8_t)(crc >> 16), p[2] = (uint8_t)(crc >> 8), p[3] = (uint8_t)crc;
         job.sizes[band] = (uint32_t)(kChunkOverhead + data_len);
@@ -683,6 +736,24 @@ int rt_png_encode_bands_dev(int device, const uint8_t* pixels_dev, int32_t pixel
     job.slot_bytes = slot_bytes_of(width, r);
     job.sizes = reinterpret_cast<uint32_t*>(job.slots + bands * job.slot_bytes);
     job.adlers = job.sizes + bands;
+    {
+        // the chunk CRC's per-launch multipliers (see BandJob); kept for the next call of the same band size
+        static thread_local int made_for = 0;
+        static thread_local uint32_t made[6][32];
+        const int slice = (int)((r * (1 + 3ll * width) + kBandSlack + kChunkOverhead + kThreads - 1) / kThreads);
+        if (made_for != slice) {
+            for (int l = 0; l < 6; ++l) {
+                uint32_t g = x2nmodp(png_code().x2n, (uint64_t)slice, 3u + (unsigned)l);  // x^(8 slice 2^l)
+                for (int k = 0; k < 32; ++k) {
+                    made[l][k] = g;
+                    g = g & 1u ? (g >> 1) ^ kCrcPoly : g >> 1;  // times x
+                }
+            }
+            made_for = slice;
+        }
+        job.crc_slice = slice;
+        memcpy(job.crc_mul, made, sizeof(made));
+    }
     const size_t smem = band_smem(width, r);
     static thread_local size_t opted[64] = {0};
     cudaError_t err = cudaSuccess;
