@@ -596,15 +596,23 @@ __global__ void __launch_bounds__(kThreads) png_pack_kernel(const __grid_constan
         const uint8_t* src = job.slots + (long long)b * job.slot_bytes;
         uint8_t* dst = job.out + 33 + before;
         const int size = (int)job.sizes[b];
-        // word copies where the destination allows (the slots are word-aligned), bytes otherwise
-        if (((uintptr_t)dst & 3) == 0) {
-            const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src);
-            uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
-            for (int i = t; i < size / 4; i += kThreads) d4[i] = s4[i];
-            for (int i = (size & ~3) + t; i < size; i += kThreads) dst[i] = src[i];
-        } else {
-            for (int i = t; i < size; i += kThreads) dst[i] = src[i];
+        // 16-byte stores wherever the DESTINATION is aligned, whatever that makes of the source (a chunk lands at
+        // any byte offset, and three in four of them were copied byte by byte -- over PCIe when the file is mapped
+        // host memory): bytes up to the first aligned address, then units built from five source words by funnel
+        // shifts (the slots are 16-byte aligned and end in slack, so the fifth word is always there), then the rest
+        const int head = min(size, (int)((16u - (unsigned)((uintptr_t)dst & 15u)) & 15u));
+        for (int i = t; i < head; i += kThreads) dst[i] = src[i];
+        const int units = (size - head) >> 4;
+        const unsigned int shift = 8u * ((unsigned)head & 3u);
+        const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src) + (head >> 2);
+        uint4* d16 = reinterpret_cast<uint4*>(dst + head);
+        for (int u = t; u < units; u += kThreads) {
+            const uint32_t* w = s4 + 4 * u;
+            const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
+            d16[u] = make_uint4(__funnelshift_r(w0, w1, shift), __funnelshift_r(w1, w2, shift), __funnelshift_r(w2, w3, shift),
+                                __funnelshift_r(w3, w4, shift));
         }
+        for (int i = head + 16 * units + t; i < size; i += kThreads) dst[i] = src[i];
     }
     if (b == 0 && fits)
         for (int i = t; i < 33; i += kThreads) job.out[i] = job.head[i];
