@@ -35,6 +35,9 @@ namespace {
 #ifndef RT_PNG_THREADS
 #define RT_PNG_THREADS 256
 #endif
+#ifndef RT_PNG_BANDS_PER_SM
+#define RT_PNG_BANDS_PER_SM 2  // bands per SM the image is cut into at least (rows_per_band)
+#endif
 constexpr int kThreads = RT_PNG_THREADS;  // per band (measured on B200, 1080p / 8K band kernel: 256: 58 / 569 us, 512: 62 / 544, 1024: 89 / 859)
 constexpr int kHeaderWords = 40;       // the dynamic-block header, LSB-first, at most 1280 bits
 constexpr uint32_t kCrcPoly = 0xedb88320u;
@@ -677,7 +680,7 @@ int png_fail(int status, const char* message) {
 int rows_per_band(int width, int height) {
     const long long line = 1 + 3ll * width;
     int r = 16;
-    while (r > 1 && ((long long)height + r - 1) / r < 2 * 148) r >>= 1;
+    while (r > 1 && ((long long)height + r - 1) / r < RT_PNG_BANDS_PER_SM * 148) r >>= 1;
     if (((long long)height + r - 1) / r < 148 && r > 1) r >>= 1;
     while (r > 1 && (r * line > 40000)) r >>= 1;
     return r;
