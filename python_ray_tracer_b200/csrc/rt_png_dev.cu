@@ -347,6 +347,99 @@ __device__ __forceinline__ void walk_tokens(const uint8_t* S, int a, int b, int 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// device: the chunks of all bands -> one contiguous PNG file
+// ---------------------------------------------------------------------------------------------------------------
+struct PackJob {
+    const uint8_t* slots;
+    long long slot_bytes;
+    const uint32_t* sizes;
+    const uint32_t* adlers;
+    int n_bands;
+    int band_bytes;        // filtered bytes of a full band (rows_per_band * (1 + 3 width))
+    long long raw_bytes;   // filtered bytes of the whole image
+    uint8_t head[33];      // signature + IHDR chunk
+    uint8_t* out;          // the file: device memory or mapped host memory
+    long long capacity;
+    unsigned long long* bytes_out;  // its size (0 if it did not fit)
+};
+
+// One launch for a whole image (png_band_kernel<true>): no pack kernel, no slots.  Blocks take their band from a
+// ticket, so a block only ever waits for blocks that started before it; a band's chunk size is known half-way through
+// its block (once its bits are counted) and published at once (status 1 << 32 | size), and the position of the chunk in
+// the file is the sum of the sizes before it, which the block adds up when its chunk is finished.  The block that
+// finishes last writes the tail.
+struct FusedCtl {
+    unsigned int* ticket;        // zeroed before the launch
+    unsigned int* done;
+    unsigned long long* state;   // [n_bands] status << 32 | value, zeroed before the launch
+};
+
+// `size` bytes from src (16-byte aligned, readable one word past the end) to dst (any alignment): 16-byte stores
+// wherever the DESTINATION is aligned, whatever that makes of the source (a chunk lands at any byte offset, and three in
+// four of them were copied byte by byte -- over PCIe when the file is mapped host memory): bytes up to the first aligned
+// address, then units built from five source words by funnel shifts, then the rest
+__device__ __forceinline__ void copy_chunk(uint8_t* dst, const uint8_t* src, int size, int t) {
+    const int head = min(size, (int)((16u - (unsigned)((uintptr_t)dst & 15u)) & 15u));
+    for (int i = t; i < head; i += kThreads) dst[i] = src[i];
+    const int units = (size - head) >> 4;
+    const unsigned int shift = 8u * ((unsigned)head & 3u);
+    const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src) + (head >> 2);
+    uint4* d16 = reinterpret_cast<uint4*>(dst + head);
+    for (int u = t; u < units; u += kThreads) {
+        const uint32_t* w = s4 + 4 * u;
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
+        d16[u] = make_uint4(__funnelshift_r(w0, w1, shift), __funnelshift_r(w1, w2, shift), __funnelshift_r(w2, w3, shift),
+                            __funnelshift_r(w3, w4, shift));
+    }
+    for (int i = head + 16 * units + t; i < size; i += kThreads) dst[i] = src[i];
+}
+
+// The end of the file, by one whole block: Adler-32 of the image from the bands' sums, the tail chunk, IEND, the size.
+// A band that starts at offset O in a stream of N bytes, with sums (a, b) taken as if it started a stream
+// and n bytes, adds a - 1 to A and (b - n) + (N - O - n) (a - 1) to B;  A = 1 + sum, B = N + sum.
+// `all` = bytes of all the bands' chunks.
+__device__ __forceinline__ void write_tail(const PackJob& job, unsigned long long all, unsigned long long* s_sum) {
+    const int t = threadIdx.x;
+    const unsigned long long total = 33ull + all + 21ull + 12ull;  // head, bands, tail chunk (9 data bytes), IEND
+    const bool fits = total <= (unsigned long long)job.capacity;
+    unsigned long long A = 0, B = 0;
+    for (int j = t; j < job.n_bands; j += kThreads) {
+        const uint32_t ad = job.adlers[j];
+        const unsigned long long a1 = ((ad & 0xffffu) + kAdlerMod - 1u) % kAdlerMod, bj = ad >> 16;
+        const long long start = (long long)j * job.band_bytes;
+        const long long n = (j == job.n_bands - 1) ? job.raw_bytes - start : job.band_bytes;
+        const unsigned long long after = (unsigned long long)(job.raw_bytes - start - n) % kAdlerMod;
+        A += a1;
+        B += (bj + kAdlerMod - (unsigned long long)(n % kAdlerMod)) % kAdlerMod + (after * a1) % kAdlerMod;
+    }
+    A = block_sum64(A, s_sum);
+    B = block_sum64(B, s_sum);
+    if (t != 0) return;
+    if (!fits) {
+        *job.bytes_out = 0ull;
+        return;
+    }
+    const uint32_t adler_a = (uint32_t)((1ull + A) % kAdlerMod);
+    const uint32_t adler_b = (uint32_t)(((unsigned long long)(job.raw_bytes % kAdlerMod) + B) % kAdlerMod);
+    uint8_t tail[21 + 12] = {0, 0, 0, 9, 'I', 'D', 'A', 'T',
+                             0x01, 0x00, 0x00, 0xff, 0xff,  // the final block: stored, empty, BFINAL = 1
+                             (uint8_t)(adler_b >> 8), (uint8_t)adler_b, (uint8_t)(adler_a >> 8), (uint8_t)adler_a,
+                             0, 0, 0, 0,
+                             0, 0, 0, 0, 'I', 'E', 'N', 'D', 0xae, 0x42, 0x60, 0x82};
+    uint32_t c = 0xffffffffu;
+    for (int i = 4; i < 17; ++i) {
+        c ^= tail[i];
+        for (int k = 0; k < 8; ++k) c = c & 1u ? (c >> 1) ^ kCrcPoly : c >> 1;
+    }
+    c ^= 0xffffffffu;
+    tail[17] = (uint8_t)(c >> 24), tail[18] = (uint8_t)(c >> 16), tail[19] = (uint8_t)(c >> 8), tail[20] = (uint8_t)c;
+    uint8_t* dst = job.out + 33 + all;
+    for (int i = 0; i < 33; ++i) dst[i] = tail[i];
+    __threadfence_system();
+    *job.bytes_out = total;
+}
+
 // c(x) * g(x) mod the CRC-32 polynomial for a multiplier fixed per launch: T[k] = x^k g(x), bit 31 - k of c selects it
 __device__ __forceinline__ uint32_t crc_mul_fixed(const uint32_t (&T)[32], uint32_t c) {
     uint32_t r = 0u;
@@ -355,17 +448,26 @@ __device__ __forceinline__ uint32_t crc_mul_fixed(const uint32_t (&T)[32], uint3
     return r;
 }
 
-__global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constant__ PngCode code, const __grid_constant__ BandJob job) {
+template <bool FUSED>
+__global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constant__ PngCode code, const __grid_constant__ BandJob job,
+                                                            const __grid_constant__ PackJob file, const __grid_constant__ FusedCtl ctl) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ uint32_t s_lit[256], s_match[256], s_crc[256], s_wcrc[kThreads / 32];
     __shared__ uint32_t s_len[kThreads], s_lead[kThreads];
     __shared__ uint32_t s_scan[kThreads / 32 + 1];
     __shared__ unsigned long long s_sum[kThreads / 32];
     __shared__ uint32_t s_wsum[kThreads / 32], s_wopen[kThreads / 32];
+    __shared__ unsigned int s_ticket, s_last;
 
     const int t = threadIdx.x;
     const int line = 1 + 3 * job.width;
-    const int first_local = blockIdx.x * job.rows_per_band;
+    unsigned int block_index = blockIdx.x;
+    if (FUSED) {  // bands in the order the blocks start: a block only ever waits for blocks that are already running
+        if (t == 0) s_ticket = atomicAdd(ctl.ticket, 1u);
+        __syncthreads();
+        block_index = s_ticket;
+    }
+    const int first_local = (int)block_index * job.rows_per_band;
     const int first_image = job_image_row(job, first_local);
     const int band = first_image / job.rows_per_band;
     const int rows = min(job.rows_per_band, min(job.n_rows - first_local, job.height - first_image));
@@ -525,6 +627,8 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
         }
         out[0] = (uint8_t)(data_len >> 24), out[1] = (uint8_t)(data_len >> 16), out[2] = (uint8_t)(data_len >> 8), out[3] = (uint8_t)data_len;
         out[4] = 'I', out[5] = 'D', out[6] = 'A', out[7] = 'T';
+        if (FUSED)  // the chunk's size is known: the bands after this one can place themselves
+            *reinterpret_cast<volatile unsigned long long*>(ctl.state + band) = (1ull << 32) | (unsigned long long)(kChunkOverhead + data_len);
     }
     __syncthreads();
 
@@ -558,28 +662,44 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
         job.adlers[band] = (adler_b << 16) | adler_a;
     }
     __syncthreads();
-    // ---- the finished chunk to its slot (whole words; the slot is word-aligned and has the slack)
-    uint32_t* slot = reinterpret_cast<uint32_t*>(job.slots + (long long)band * job.slot_bytes);
-    const int chunk_words = (kChunkOverhead + data_len + 3) / 4;
-    for (int i = t; i < chunk_words; i += kThreads) slot[i] = out_words[i];
+    if (!FUSED) {
+        // ---- the finished chunk to its slot (whole words; the slot is word-aligned and has the slack)
+        uint32_t* slot = reinterpret_cast<uint32_t*>(job.slots + (long long)band * job.slot_bytes);
+        const int chunk_words = (kChunkOverhead + data_len + 3) / 4;
+        for (int i = t; i < chunk_words; i += kThreads) slot[i] = out_words[i];
+        return;
+    }
+    // ---- the finished chunk to its place in the file (device memory or mapped host memory), the head with band 0.
+    // Its place: behind the chunks of all bands before it, whose sizes were published when their bits were counted --
+    // half a block ago for bands that started with this one -- so the whole block just adds them up, waiting for the
+    // few that are not there yet (they belong to blocks that took their ticket earlier and are therefore running).
+    unsigned long long before = 0ull;
+    for (int j = t; j < band; j += kThreads) {
+        unsigned long long w;
+        while (((w = *reinterpret_cast<volatile unsigned long long*>(ctl.state + j)) >> 32) == 0ull) __nanosleep(64);
+        before += w & 0xffffffffull;
+    }
+    before = block_sum64(before, s_sum);
+    // a chunk that would not leave room for the tail is not written (the last block then reports 0 bytes)
+    const int size = kChunkOverhead + data_len;
+    if (33ull + before + (unsigned long long)size + 33ull <= (unsigned long long)file.capacity) {
+        copy_chunk(file.out + 33 + before, out, size, t);
+        if (band == 0)
+            for (int i = t; i < 33; i += kThreads) file.out[i] = file.head[i];
+    }
+    __syncthreads();
+    if (t == 0) {
+        __threadfence_system();  // (the file may be host memory: the block's bytes, and its sums above, before the count)
+        s_last = atomicAdd(ctl.done, 1u) == (unsigned int)(file.n_bands - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_last == 0u) return;
+    __threadfence();
+    unsigned long long all = 0ull;
+    for (int j = t; j < file.n_bands; j += kThreads) all += *reinterpret_cast<volatile unsigned long long*>(ctl.state + j) & 0xffffffffull;
+    all = block_sum64(all, s_sum);
+    write_tail(file, all, s_sum);
 }
-
-// ---------------------------------------------------------------------------------------------------------------
-// device: the chunks of all bands -> one contiguous PNG file
-// ---------------------------------------------------------------------------------------------------------------
-struct PackJob {
-    const uint8_t* slots;
-    long long slot_bytes;
-    const uint32_t* sizes;
-    const uint32_t* adlers;
-    int n_bands;
-    int band_bytes;        // filtered bytes of a full band (rows_per_band * (1 + 3 width))
-    long long raw_bytes;   // filtered bytes of the whole image
-    uint8_t head[33];      // signature + IHDR chunk
-    uint8_t* out;          // the file: device memory or mapped host memory
-    long long capacity;
-    unsigned long long* bytes_out;  // its size (0 if it did not fit)
-};
 
 __global__ void __launch_bounds__(kThreads) png_pack_kernel(const __grid_constant__ PackJob job) {
     __shared__ unsigned long long s_sum[kThreads / 32];
@@ -593,71 +713,12 @@ __global__ void __launch_bounds__(kThreads) png_pack_kernel(const __grid_constan
     }
     before = block_sum64(before, s_sum);
     all = block_sum64(all, s_sum);
-    const unsigned long long total = 33ull + all + 21ull + 12ull;  // head, bands, tail chunk (9 data bytes), IEND
-    const bool fits = total <= (unsigned long long)job.capacity;
-    if (fits) {
-        const uint8_t* src = job.slots + (long long)b * job.slot_bytes;
-        uint8_t* dst = job.out + 33 + before;
-        const int size = (int)job.sizes[b];
-        // 16-byte stores wherever the DESTINATION is aligned, whatever that makes of the source (a chunk lands at
-        // any byte offset, and three in four of them were copied byte by byte -- over PCIe when the file is mapped
-        // host memory): bytes up to the first aligned address, then units built from five source words by funnel
-        // shifts (the slots are 16-byte aligned and end in slack, so the fifth word is always there), then the rest
-        const int head = min(size, (int)((16u - (unsigned)((uintptr_t)dst & 15u)) & 15u));
-        for (int i = t; i < head; i += kThreads) dst[i] = src[i];
-        const int units = (size - head) >> 4;
-        const unsigned int shift = 8u * ((unsigned)head & 3u);
-        const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src) + (head >> 2);
-        uint4* d16 = reinterpret_cast<uint4*>(dst + head);
-        for (int u = t; u < units; u += kThreads) {
-            const uint32_t* w = s4 + 4 * u;
-            const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
-            d16[u] = make_uint4(__funnelshift_r(w0, w1, shift), __funnelshift_r(w1, w2, shift), __funnelshift_r(w2, w3, shift),
-                                __funnelshift_r(w3, w4, shift));
-        }
-        for (int i = head + 16 * units + t; i < size; i += kThreads) dst[i] = src[i];
-    }
+    const bool fits = 33ull + all + 21ull + 12ull <= (unsigned long long)job.capacity;
+    if (fits) copy_chunk(job.out + 33 + before, job.slots + (long long)b * job.slot_bytes, (int)job.sizes[b], t);
     if (b == 0 && fits)
         for (int i = t; i < 33; i += kThreads) job.out[i] = job.head[i];
     if (b != job.n_bands - 1) return;
-    // ---- the last block: Adler-32 of the whole image from the bands' sums, the tail chunk, IEND, the size.
-    // A band that starts at offset O in a stream of N bytes, with sums (a, b) taken as if it started a stream
-    // and n bytes, adds a - 1 to A and (b - n) + (N - O - n) (a - 1) to B;  A = 1 + sum, B = N + sum.
-    unsigned long long A = 0, B = 0;
-    for (int j = t; j < job.n_bands; j += kThreads) {
-        const uint32_t ad = job.adlers[j];
-        const unsigned long long a1 = ((ad & 0xffffu) + kAdlerMod - 1u) % kAdlerMod, bj = ad >> 16;
-        const long long start = (long long)j * job.band_bytes;
-        const long long n = (j == job.n_bands - 1) ? job.raw_bytes - start : job.band_bytes;
-        const unsigned long long after = (unsigned long long)(job.raw_bytes - start - n) % kAdlerMod;
-        A += a1;
-        B += (bj + kAdlerMod - (unsigned long long)(n % kAdlerMod)) % kAdlerMod + (after * a1) % kAdlerMod;
-    }
-    A = block_sum64(A, s_sum);
-    B = block_sum64(B, s_sum);
-    if (t != 0) return;
-    if (!fits) {
-        *job.bytes_out = 0ull;
-        return;
-    }
-    const uint32_t adler_a = (uint32_t)((1ull + A) % kAdlerMod);
-    const uint32_t adler_b = (uint32_t)(((unsigned long long)(job.raw_bytes % kAdlerMod) + B) % kAdlerMod);
-    uint8_t tail[21 + 12] = {0, 0, 0, 9, 'I', 'D', 'A', 'T',
-                             0x01, 0x00, 0x00, 0xff, 0xff,  // the final block: stored, empty, BFINAL = 1
-                             (uint8_t)(adler_b >> 8), (uint8_t)adler_b, (uint8_t)(adler_a >> 8), (uint8_t)adler_a,
-                             0, 0, 0, 0,
-                             0, 0, 0, 0, 'I', 'E', 'N', 'D', 0xae, 0x42, 0x60, 0x82};
-    uint32_t c = 0xffffffffu;
-    for (int i = 4; i < 17; ++i) {
-        c ^= tail[i];
-        for (int k = 0; k < 8; ++k) c = c & 1u ? (c >> 1) ^ kCrcPoly : c >> 1;
-    }
-    c ^= 0xffffffffu;
-    tail[17] = (uint8_t)(c >> 24), tail[18] = (uint8_t)(c >> 16), tail[19] = (uint8_t)(c >> 8), tail[20] = (uint8_t)c;
-    uint8_t* dst = job.out + 33 + all;
-    for (int i = 0; i < 33; ++i) dst[i] = tail[i];
-    __threadfence_system();
-    *job.bytes_out = total;
+    write_tail(job, all, s_sum);
 }
 
 uint32_t host_crc32(const uint8_t* p, size_t n) {
@@ -694,6 +755,70 @@ long long slot_bytes_of(int width, int rows) {
     return (cap + kBandSlack + kChunkOverhead + 15) & ~15ll;
 }
 
+// what the band kernel needs to know about the image and the scratch area (everything but the pixels)
+void fill_band_job(BandJob& job, int width, int height, int r, void* scratch_dev) {
+    const long long bands = (height + r - 1) / r;
+    job.width = width, job.height = height;
+    job.rows_per_band = r;
+    job.slots = static_cast<uint8_t*>(scratch_dev);
+    job.slot_bytes = slot_bytes_of(width, r);
+    job.sizes = reinterpret_cast<uint32_t*>(job.slots + bands * job.slot_bytes);
+    job.adlers = job.sizes + bands;
+    // the chunk CRC's per-launch multipliers (see BandJob); kept for the next call of the same band size
+    static thread_local int made_for = 0;
+    static thread_local uint32_t made[6][32];
+    const int slice = (int)((r * (1 + 3ll * width) + kBandSlack + kChunkOverhead + kThreads - 1) / kThreads);
+    if (made_for != slice) {
+        for (int l = 0; l < 6; ++l) {
+            uint32_t g = x2nmodp(png_code().x2n, (uint64_t)slice, 3u + (unsigned)l);  // x^(8 slice 2^l)
+            for (int k = 0; k < 32; ++k) {
+                made[l][k] = g;
+                g = g & 1u ? (g >> 1) ^ kCrcPoly : g >> 1;  // times x
+            }
+        }
+        made_for = slice;
+    }
+    job.crc_slice = slice;
+    memcpy(job.crc_mul, made, sizeof(made));
+}
+
+// ... and the file: header bytes, where the bands' sums are, where the file and its size go
+void fill_pack_job(PackJob& job, int width, int height, int r, const void* scratch_dev, uint8_t* png_out, long long capacity,
+                   uint64_t* png_bytes_out) {
+    const long long bands = (height + r - 1) / r;
+    memset(&job, 0, sizeof(job));
+    job.slots = static_cast<const uint8_t*>(scratch_dev);
+    job.slot_bytes = slot_bytes_of(width, r);
+    job.sizes = reinterpret_cast<const uint32_t*>(job.slots + bands * job.slot_bytes);
+    job.adlers = job.sizes + bands;
+    job.n_bands = (int)bands;
+    job.band_bytes = r * (1 + 3 * width);
+    job.raw_bytes = (long long)height * (1 + 3ll * width);
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    memcpy(job.head, sig, 8);
+    uint8_t* ih = job.head + 8;
+    ih[0] = 0, ih[1] = 0, ih[2] = 0, ih[3] = 13;
+    memcpy(ih + 4, "IHDR", 4);
+    for (int i = 0; i < 4; ++i) ih[8 + i] = (uint8_t)((uint32_t)width >> (24 - 8 * i)), ih[12 + i] = (uint8_t)((uint32_t)height >> (24 - 8 * i));
+    ih[16] = 8, ih[17] = 2, ih[18] = 0, ih[19] = 0, ih[20] = 0;  // 8 bits, RGB, deflate, adaptive filters, not interlaced
+    const uint32_t crc = host_crc32(ih + 4, 17);
+    for (int i = 0; i < 4; ++i) ih[21 + i] = (uint8_t)(crc >> (24 - 8 * i));
+    job.out = png_out;
+    job.capacity = capacity;
+    job.bytes_out = reinterpret_cast<unsigned long long*>(png_bytes_out);
+}
+
+// the band kernel's dynamic shared memory beyond the default 48 KB (static shared memory counts towards it), once per
+// device, thread and instantiation
+template <bool FUSED>
+cudaError_t opt_in_smem(int device, size_t smem) {
+    static thread_local size_t opted[64] = {0};
+    if (smem + 8 * 1024 <= 48 * 1024 || device < 0 || device >= 64 || opted[device] >= smem) return cudaSuccess;
+    const cudaError_t err = cudaFuncSetAttribute(png_band_kernel<FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err == cudaSuccess) opted[device] = smem;
+    return err;
+}
+
 }  // namespace
 
 extern "C" {
@@ -707,7 +832,8 @@ int64_t rt_png_scratch_bytes(int32_t width, int32_t height) {
     if (rt_png_rows_per_band(width, height) < 0) return -1;
     const int r = rows_per_band(width, height);
     const long long bands = (height + r - 1) / r;
-    return bands * slot_bytes_of(width, r) + bands * 8 + 64;
+    // slots, sizes, Adler sums; ticket, finished-count and one status word per band of the single-launch encoder
+    return bands * slot_bytes_of(width, r) + bands * 8 + 16 + bands * 8 + 64;
 }
 
 int64_t rt_png_file_bound(int32_t width, int32_t height) {
@@ -734,46 +860,17 @@ int rt_png_encode_bands_dev(int device, const uint8_t* pixels_dev, int32_t pixel
     int previous = -1;
     cudaGetDevice(&previous);
     if (previous != device && cudaSetDevice(device) != cudaSuccess) return png_fail(RT_ERR_NO_DEVICE, "rt_png_encode_bands_dev: cudaSetDevice failed");
-    const long long bands = (height + r - 1) / r;
     BandJob job;
     job.pixels = pixels_dev;
     job.row_stride = row_stride;
     job.pixel_bytes = pixel_bytes;
-    job.width = width, job.height = height;
-    job.rows_per_band = r;
     job.n_rows = n_rows;
     job.row0 = row0, job.strip_rows = strip_step == 1 ? (n_rows > 0 ? n_rows : 1) : strip_rows, job.strip_step = strip_step;
-    job.slots = static_cast<uint8_t*>(scratch_dev);
-    job.slot_bytes = slot_bytes_of(width, r);
-    job.sizes = reinterpret_cast<uint32_t*>(job.slots + bands * job.slot_bytes);
-    job.adlers = job.sizes + bands;
-    {
-        // the chunk CRC's per-launch multipliers (see BandJob); kept for the next call of the same band size
-        static thread_local int made_for = 0;
-        static thread_local uint32_t made[6][32];
-        const int slice = (int)((r * (1 + 3ll * width) + kBandSlack + kChunkOverhead + kThreads - 1) / kThreads);
-        if (made_for != slice) {
-            for (int l = 0; l < 6; ++l) {
-                uint32_t g = x2nmodp(png_code().x2n, (uint64_t)slice, 3u + (unsigned)l);  // x^(8 slice 2^l)
-                for (int k = 0; k < 32; ++k) {
-                    made[l][k] = g;
-                    g = g & 1u ? (g >> 1) ^ kCrcPoly : g >> 1;  // times x
-                }
-            }
-            made_for = slice;
-        }
-        job.crc_slice = slice;
-        memcpy(job.crc_mul, made, sizeof(made));
-    }
+    fill_band_job(job, width, height, r, scratch_dev);
     const size_t smem = band_smem(width, r);
-    static thread_local size_t opted[64] = {0};
-    cudaError_t err = cudaSuccess;
-    if (smem + 8 * 1024 > 48 * 1024 && device < 64 && opted[device] < smem) {  // (static shared memory counts towards the 48 KB default)
-        err = cudaFuncSetAttribute(png_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (err == cudaSuccess) opted[device] = smem;
-    }
+    cudaError_t err = opt_in_smem<false>(device, smem);
     if (err == cudaSuccess) {
-        png_band_kernel<<<(unsigned)((n_rows + r - 1) / r), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(png_code(), job);
+        png_band_kernel<false><<<(unsigned)((n_rows + r - 1) / r), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(png_code(), job, PackJob(), FusedCtl());
         err = cudaGetLastError();
     }
     if (previous >= 0 && previous != device) cudaSetDevice(previous);
@@ -788,31 +885,52 @@ int rt_png_pack_dev(int device, int32_t width, int32_t height, const void* scrat
     const int r = rows_per_band(width, height);
     const long long bands = (height + r - 1) / r;
     PackJob job;
-    memset(&job, 0, sizeof(job));
-    job.slots = static_cast<const uint8_t*>(scratch_dev);
-    job.slot_bytes = slot_bytes_of(width, r);
-    job.sizes = reinterpret_cast<const uint32_t*>(job.slots + bands * job.slot_bytes);
-    job.adlers = job.sizes + bands;
-    job.n_bands = (int)bands;
-    job.band_bytes = r * (1 + 3 * width);
-    job.raw_bytes = (long long)height * (1 + 3ll * width);
-    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
-    memcpy(job.head, sig, 8);
-    uint8_t* ih = job.head + 8;
-    ih[0] = 0, ih[1] = 0, ih[2] = 0, ih[3] = 13;
-    memcpy(ih + 4, "IHDR", 4);
-    for (int i = 0; i < 4; ++i) ih[8 + i] = (uint8_t)((uint32_t)width >> (24 - 8 * i)), ih[12 + i] = (uint8_t)((uint32_t)height >> (24 - 8 * i));
-    ih[16] = 8, ih[17] = 2, ih[18] = 0, ih[19] = 0, ih[20] = 0;  // 8 bits, RGB, deflate, adaptive filters, not interlaced
-    const uint32_t crc = host_crc32(ih + 4, 17);
-    for (int i = 0; i < 4; ++i) ih[21 + i] = (uint8_t)(crc >> (24 - 8 * i));
-    job.out = png_out;
-    job.capacity = capacity;
-    job.bytes_out = reinterpret_cast<unsigned long long*>(png_bytes_out);
+    fill_pack_job(job, width, height, r, scratch_dev, png_out, capacity, png_bytes_out);
     int previous = -1;
     cudaGetDevice(&previous);
     if (previous != device && cudaSetDevice(device) != cudaSuccess) return png_fail(RT_ERR_NO_DEVICE, "rt_png_pack_dev: cudaSetDevice failed");
     png_pack_kernel<<<(unsigned)bands, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(job);
     const cudaError_t err = cudaGetLastError();
+    if (previous >= 0 && previous != device) cudaSetDevice(previous);
+    if (err != cudaSuccess) return png_fail(RT_ERR_CUDA, cudaGetErrorString(err));
+    return RT_OK;
+}
+
+int rt_png_encode_file_dev(int device, const uint8_t* pixels_dev, int32_t pixel_bytes, int64_t row_stride, int32_t width, int32_t height,
+                           void* scratch_dev, int64_t scratch_bytes, uint8_t* png_out, int64_t capacity, uint64_t* png_bytes_out,
+                           void* stream) {
+    if (pixels_dev == nullptr || scratch_dev == nullptr || png_out == nullptr || png_bytes_out == nullptr || (pixel_bytes != 3 && pixel_bytes != 4) ||
+        width <= 0 || height <= 0 || row_stride < (int64_t)width * pixel_bytes || capacity < 128)
+        return png_fail(RT_ERR_BAD_ARG, "rt_png_encode_file_dev: NULL pointer or bad size");
+    if (rt_png_rows_per_band(width, height) < 0)
+        return png_fail(RT_ERR_UNSUPPORTED, "rt_png_encode_file_dev: rows wider than 21 666 pixels do not fit a stored block");
+    if (scratch_bytes < rt_png_scratch_bytes(width, height)) return png_fail(RT_ERR_BAD_ARG, "rt_png_encode_file_dev: scratch smaller than rt_png_scratch_bytes");
+    const int r = rows_per_band(width, height);
+    const long long bands = (height + r - 1) / r;
+    BandJob job;
+    job.pixels = pixels_dev;
+    job.row_stride = row_stride;
+    job.pixel_bytes = pixel_bytes;
+    job.n_rows = height;
+    job.row0 = 0, job.strip_rows = height, job.strip_step = 1;
+    fill_band_job(job, width, height, r, scratch_dev);
+    PackJob file;
+    fill_pack_job(file, width, height, r, scratch_dev, png_out, capacity, png_bytes_out);
+    FusedCtl ctl;
+    unsigned char* control = reinterpret_cast<unsigned char*>(job.adlers + bands);  // (8-byte aligned: slots are multiples of 16, 8 bytes per band before it)
+    ctl.ticket = reinterpret_cast<unsigned int*>(control);
+    ctl.done = ctl.ticket + 1;
+    ctl.state = reinterpret_cast<unsigned long long*>(control + 8);
+    int previous = -1;
+    cudaGetDevice(&previous);
+    if (previous != device && cudaSetDevice(device) != cudaSuccess) return png_fail(RT_ERR_NO_DEVICE, "rt_png_encode_file_dev: cudaSetDevice failed");
+    const size_t smem = band_smem(width, r);
+    cudaError_t err = opt_in_smem<true>(device, smem);
+    if (err == cudaSuccess) err = cudaMemsetAsync(control, 0, 8 + 8 * (size_t)bands, static_cast<cudaStream_t>(stream));
+    if (err == cudaSuccess) {
+        png_band_kernel<true><<<(unsigned)bands, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(png_code(), job, file, ctl);
+        err = cudaGetLastError();
+    }
     if (previous >= 0 && previous != device) cudaSetDevice(previous);
     if (err != cudaSuccess) return png_fail(RT_ERR_CUDA, cudaGetErrorString(err));
     return RT_OK;

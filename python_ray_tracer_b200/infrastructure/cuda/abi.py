@@ -33,6 +33,7 @@ RT_SMALL_SCENE_SPHERES = 4
 RT_ACCEL_AUTO_SPHERES = 32
 RT_IPC_HANDLE_BYTES = 64
 RT_PNG_STATIC_SCRATCH_BYTES = 8 << 20
+RT_PNG_ONE_LAUNCH_BANDS = 2048
 RT_DTYPE_F32 = 0
 RT_DTYPE_F64 = 1
 
@@ -181,6 +182,10 @@ PROTOTYPES = {
     "rt_render_png_host": (
         C.c_int,
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), C.POINTER(RtCamera), _P, C.c_int64, C.POINTER(C.c_int64)],
+    ),
+    "rt_png_encode_file_dev": (
+        C.c_int,
+        [C.c_int, _P, C.c_int32, C.c_int64, C.c_int32, C.c_int32, _P, C.c_int64, _P, C.c_int64, _P, _P],
     ),
     "rt_png_encode_static_dev": (
         C.c_int,

@@ -169,7 +169,7 @@ class CudaRenderer(Renderer):
                    default, byte-for-byte the kind of file the reference writes, ~30x slower).
                    Decoded pixels do not depend on it.
     ``png_threads``  threads ``save_image`` deflates with (default: up to 8 of the host's cores).
-    ``png_encoder``  ``"device"`` (default): the file is made on the GPU (``rt_png_encode_bands_dev``) and only it
+    ``png_encoder``  ``"device"`` (default): the file is made on the GPU (``rt_png_encode_bands_dev`` + ``rt_png_pack_dev``) and only it
                    crosses PCIe; ``"host"``: the 8-bit image is copied to the host and deflated there
                    (``png_compress_level`` / ``png_threads``).  Decoded pixels are the same.
     ``accel``      ``"auto"`` (default): scenes of at least ``ACCEL_MIN_SPHERES`` shapes get a

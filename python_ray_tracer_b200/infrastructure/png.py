@@ -149,7 +149,7 @@ def encode_png_fast(pixels: np.ndarray, threads: int = 1, pool=None) -> bytes:
 
 
 class DevicePngEncoder:
-    """PNG files made on the GPU (``rt_png_encode_bands_dev`` + ``rt_png_pack_dev``, csrc/rt_png_dev.cu): the
+    """PNG files made on the GPU (``rt_png_encode_bands_dev`` + ``rt_png_pack_dev``, or ``rt_png_encode_file_dev`` in one launch for frames of many bands; csrc/rt_png_dev.cu): the
     8-bit image stays on the device, only the ~10x smaller file crosses PCIe -- written by the pack kernel
     straight into a pinned host buffer.  One encoder holds the scratch and landing buffers of one frame size
     on one device; ``encode`` returns the file's bytes.  Decoded pixels equal the input."""
@@ -171,14 +171,19 @@ class DevicePngEncoder:
         self.size = torch.zeros(1, dtype=torch.int64).pin_memory()
 
     def enqueue(self, pixels, stream: int) -> None:
-        """``pixels``: uint8 device tensor ``[H * W, 3 or 4]`` (or ``[H, W, C]``), contiguous.  Enqueues the two
-        kernels on ``stream``; ``finish()`` after synchronising that stream."""
+        """``pixels``: uint8 device tensor ``[H * W, 3 or 4]`` (or ``[H, W, C]``), contiguous.  Enqueues the
+        encoder on ``stream``; ``finish()`` after synchronising that stream."""
         from .cuda import abi
 
         channels = int(pixels.shape[-1])
         if pixels.numel() != self.width * self.height * channels or channels not in (3, 4) or not pixels.is_contiguous():
             raise ValueError("expected a contiguous uint8 image of the encoder's size with 3 or 4 channels")
         self.size[0] = -1
+        if -(-self.height // self.rows_per_band) >= abi.RT_PNG_ONE_LAUNCH_BANDS:  # (measured: include/rt_abi.h)
+            abi.check(self.lib.rt_png_encode_file_dev(self.device, pixels.data_ptr(), channels, self.width * channels, self.width,
+                                                      self.height, self.scratch.data_ptr(), self.scratch_bytes, self.file.data_ptr(),
+                                                      self.capacity, self.size.data_ptr(), stream), "rt_png_encode_file_dev")
+            return
         abi.check(self.lib.rt_png_encode_bands_dev(self.device, pixels.data_ptr(), channels, self.width * channels, self.height,
                                                    self.width, self.height, 0, self.height, 1, self.scratch.data_ptr(),
                                                    self.scratch_bytes, stream), "rt_png_encode_bands_dev")

@@ -1,4 +1,4 @@
-"""The device PNG encoder (csrc/rt_png_dev.cu: rt_png_encode_bands_dev + rt_png_pack_dev, rt_render_png_host):
+"""The device PNG encoder (csrc/rt_png_dev.cu: rt_png_encode_file_dev, rt_png_encode_bands_dev + rt_png_pack_dev, rt_render_png_host):
 its files decode -- with zlib through this repo's reader, and with Pillow where installed -- to exactly the
 pixels that went in, whatever the content (rendered frames, flat colour whose runs span every thread of a band,
 noise that has to be stored, gradients), size (1x1 up to 8K rows, widths off every alignment) and pixel layout
@@ -113,6 +113,66 @@ def test_device_png_of_rendered_frames(rt_fast, tmp_path):
         small = torch.empty(4096, dtype=torch.uint8).pin_memory()
         assert lib.rt_render_png_host(0, flat.spheres.ctypes.data, flat.n_spheres, flat.point_lights.ctypes.data, C.byref(env),
                                       C.byref(cam), small.data_ptr(), 4096, C.byref(used)) == -1 and b"too small" in lib.rt_last_error()
+
+
+def test_single_launch_file_equals_bands_plus_pack(tmp_path):
+    """rt_png_encode_file_dev (one launch: chunk positions by a single-pass prefix sum, the last block writes the tail)
+    makes byte for byte the file of rt_png_encode_bands_dev + rt_png_pack_dev, for every content and size, again and
+    again on the same scratch area; a buffer too small for the file is reported as 0 bytes, never overrun."""
+    import torch
+
+    from python_ray_tracer_b200.infrastructure.cuda import abi
+
+    lib = abi.load()
+    rng = np.random.default_rng(7)
+    stream = int(torch.cuda.current_stream(0).cuda_stream)
+    for name, img in list(_images(rng)) + [("noise 1920x1080 (every band stored)", rng.integers(0, 256, (1080, 1920, 3), dtype=np.uint8))]:
+        h, w, _ = img.shape
+        pixels = torch.from_numpy(np.ascontiguousarray(img)).cuda()
+        scratch_bytes, capacity = int(lib.rt_png_scratch_bytes(w, h)), int(lib.rt_png_file_bound(w, h))
+        scratch = torch.full((scratch_bytes,), 0xA5, dtype=torch.uint8, device="cuda")  # (nothing relies on what the scratch held)
+        want_file = torch.zeros(capacity, dtype=torch.uint8, device="cuda")
+        want_size = torch.zeros(1, dtype=torch.int64, device="cuda")
+        abi.check(lib.rt_png_encode_bands_dev(0, pixels.data_ptr(), 3, 3 * w, h, w, h, 0, h, 1, scratch.data_ptr(), scratch_bytes, stream), "bands")
+        abi.check(lib.rt_png_pack_dev(0, w, h, scratch.data_ptr(), want_file.data_ptr(), capacity, want_size.data_ptr(), stream), "pack")
+        torch.cuda.synchronize()
+        n = int(want_size.item())
+        want = want_file[:n].cpu().numpy()
+        assert n > 0 and np.array_equal(_decode(want.tobytes(), tmp_path), img), name
+        guard = 64
+        for round_ in range(3):
+            got_file = torch.full((capacity + guard,), 0xEE, dtype=torch.uint8, device="cuda")
+            got_size = torch.full((1,), -1, dtype=torch.int64, device="cuda")
+            abi.check(lib.rt_png_encode_file_dev(0, pixels.data_ptr(), 3, 3 * w, w, h, scratch.data_ptr(), scratch_bytes,
+                                                 got_file.data_ptr(), capacity, got_size.data_ptr(), stream), "file")
+            torch.cuda.synchronize()
+            assert int(got_size.item()) == n, (name, round_)
+            assert np.array_equal(got_file[:n].cpu().numpy(), want), (name, round_)
+            assert bool((got_file[capacity:] == 0xEE).all().item()), name
+        # a buffer that cannot hold the file: 0 bytes reported, nothing written past its end
+        if n < 140:
+            continue
+        small = n - 5
+        got_file = torch.full((small + guard,), 0xEE, dtype=torch.uint8, device="cuda")
+        got_size = torch.full((1,), -1, dtype=torch.int64, device="cuda")
+        abi.check(lib.rt_png_encode_file_dev(0, pixels.data_ptr(), 3, 3 * w, w, h, scratch.data_ptr(), scratch_bytes,
+                                             got_file.data_ptr(), small, got_size.data_ptr(), stream), "file")
+        torch.cuda.synchronize()
+        assert int(got_size.item()) == 0 and bool((got_file[small:] == 0xEE).all().item()), name
+    # RGBA input and a pinned host destination
+    img = rng.integers(0, 256, (97, 333, 4), dtype=np.uint8)
+    img[:, 100:250] = 9
+    h, w, _ = img.shape
+    pixels = torch.from_numpy(img).cuda()
+    scratch_bytes, capacity = int(lib.rt_png_scratch_bytes(w, h)), int(lib.rt_png_file_bound(w, h))
+    scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device="cuda")
+    host_file = torch.zeros(capacity, dtype=torch.uint8).pin_memory()
+    host_size = torch.zeros(1, dtype=torch.int64).pin_memory()
+    abi.check(lib.rt_png_encode_file_dev(0, pixels.data_ptr(), 4, 4 * w, w, h, scratch.data_ptr(), scratch_bytes, host_file.data_ptr(),
+                                         capacity, host_size.data_ptr(), stream), "file")
+    torch.cuda.synchronize()
+    n = int(host_size[0])
+    assert n > 0 and np.array_equal(_decode(host_file.numpy()[:n].tobytes(), tmp_path), img[:, :, :3])
 
 
 def test_device_png_from_interleaved_strips(rt_fast, tmp_path):

@@ -1,4 +1,4 @@
-"""Device PNG encoder alone (GPU box): time of rt_png_encode_bands_dev and rt_png_pack_dev on a rendered frame.
+"""Device PNG encoder alone (GPU box): time of rt_png_encode_bands_dev, rt_png_pack_dev and rt_png_encode_file_dev on a rendered frame.
     python tools/png_device_bench.py [width height] [reps]"""
 import sys
 from pathlib import Path
@@ -33,6 +33,12 @@ def pack(host: bool):
                                   enc.size.data_ptr() if host else dev_size.data_ptr(), sp), "pack")
 
 
+def whole(host: bool):
+    abi.check(lib.rt_png_encode_file_dev(0, img.data_ptr(), 3, w * 3, w, h, enc.scratch.data_ptr(), enc.scratch_bytes,
+                                         enc.file.data_ptr() if host else dev_file.data_ptr(), enc.capacity,
+                                         enc.size.data_ptr() if host else dev_size.data_ptr(), sp), "file")
+
+
 def timed(fn):
     for _ in range(3):
         fn()
@@ -50,3 +56,5 @@ print(f"{w}x{h}: rows per band {enc.rows_per_band}, bands {-(-h // enc.rows_per_
 print(f"  band kernel          {timed(bands):8.1f} us")
 print(f"  pack -> device       {timed(lambda: pack(False)):8.1f} us   file {int(dev_size[0])} bytes")
 print(f"  pack -> pinned host  {timed(lambda: pack(True)):8.1f} us")
+print(f"  one launch -> device {timed(lambda: whole(False)):8.1f} us   file {int(dev_size[0])} bytes   (rt_png_encode_file_dev: memset + kernel)")
+print(f"  one launch -> host   {timed(lambda: whole(True)):8.1f} us")
