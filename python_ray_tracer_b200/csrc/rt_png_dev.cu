@@ -11,9 +11,10 @@
 //   * ONE fixed Huffman code (rt_png_table.h, made from the token statistics of rendered frames by
 //     tools/png_static_table.py) sent in every band's dynamic-block header: no histogram, no tree building;
 //   * a band that would grow is stored instead.
-// The image is cut into bands of a few rows, one thread block each.  A band is one byte stream; every thread owns
-// a contiguous piece of it.  Whether a byte continues a run, where its run began and ends, and therefore which
-// token covers it, follow from two small scans over the threads' summaries; bit positions from a third.  Every
+// The image is cut into bands of a few rows, one thread block each.  A band is one byte stream.  Whether a byte
+// continues a run is one bit per byte, formed four bytes per compare; the bytes that bear tokens (literals, and the
+// first byte of every run, which owns the run's tokens) are counted per 32-byte word, prefix-summed, and dealt to the
+// threads in equal numbers; a run's length is bit arithmetic on its words; bit positions come from a second scan.  Every
 // band becomes one IDAT chunk (PNG allows any number): its deflate block ends byte-aligned on an empty stored
 // block (BFINAL = 0), its CRC-32 is computed by the block that made it, so nothing serial is left but the
 // Adler-32 of the whole image (combined from the bands' sums) in a 9-byte tail chunk.  A second small kernel packs
@@ -38,7 +39,8 @@ namespace {
 #ifndef RT_PNG_BANDS_PER_SM
 #define RT_PNG_BANDS_PER_SM 2  // bands per SM the image is cut into at least (rows_per_band)
 #endif
-constexpr int kThreads = RT_PNG_THREADS;  // per band (measured on B200, 1080p / 8K band kernel: 256: 58 / 569 us, 512: 62 / 544, 1024: 89 / 859)
+constexpr int kThreads = RT_PNG_THREADS;  // per band (measured on B200, 1080p / 8K band kernel: 128: 65 / 300 us, 256: 44 / 240, 512: 43 / 269;
+                                          // 4 bands per SM instead of 2: 42 / 240 with twice the chunks, 1: 68 / 240)
 constexpr int kHeaderWords = 40;       // the dynamic-block header, LSB-first, at most 1280 bits
 constexpr uint32_t kCrcPoly = 0xedb88320u;
 constexpr uint32_t kAdlerMod = 65521u;
@@ -295,58 +297,6 @@ __device__ __forceinline__ unsigned long long block_sum64(unsigned long long v, 
     return all;
 }
 
-// m(i): byte i of the stream equals the byte three before it (it continues a run of one RGB residual)
-__device__ __forceinline__ bool continues_run(const uint8_t* S, int i) { return i >= 3 && S[i] == S[i - 3]; }
-
-// The tokens whose first byte lies in [a, b) of the band's stream S, visited from b - 1 DOWN to a with the same
-// instructions in every thread (a warp walks 32 pieces in lock step: nothing here may diverge).
-// A run of m = 1 bytes is cut into chunks of 258 counted from its END, so what covers byte i follows from
-// rem(i) = how many bytes from i on continue the run (a backward recurrence, carried in from the pieces to the
-// right as run_out) and from m(i - 1), m(i - 2):
-//   m(i) = 0                          literal
-//   rem % 258 = 0                     a match of 258 starts here
-//   the run starts here (m(i-1) = 0)  its head of rem % 258 bytes: a match if that is at least 3, else a literal
-//   rem % 258 = 1, the run started at i - 1   second byte of a two-byte head: literal
-//   otherwise                         inside a match: nothing
-// emit(i, entry) is called for every byte with its token's table entry (bits | count << 24; 0 = nothing).
-// `all_run`: every byte of the piece continues a run (black sky, flat colour: most pieces of a rendered frame).  Then
-// bytes a + 2 .. b - 1 lie inside the run whatever is to the left of the piece, and only the 258-boundaries among them
-// carry a token -- found by arithmetic on rem(i) = run_out + (b - i), no byte is looked at; bytes a + 1 and a take the
-// general rule (the run may start at a, and its head may be the two literals a, a + 1).
-template <class Emit>
-__device__ __forceinline__ void walk_tokens(const uint8_t* S, int a, int b, int run_out, bool all_run, const uint32_t* lit,
-                                            const uint32_t* match, Emit&& emit) {
-    if (all_run && b > a) {
-        const int span = b - a;
-        for (int r = ((run_out + 258) / 258) * 258; r <= run_out + span - 2; r += 258) emit(b - (r - run_out), match[255]);
-        const bool m1 = continues_run(S, a - 1), m2 = continues_run(S, a - 2);
-        if (span >= 2) {
-            const int q1 = (run_out + span - 1) % 258;
-            emit(a + 1, q1 == 0 ? match[255] : ((q1 == 1 && !m1) ? lit[S[a + 1]] : 0u));
-        }
-        const int q0 = (run_out + span) % 258;
-        const uint32_t literal = lit[S[a]];
-        const uint32_t head = q0 >= 3 ? match[q0 - 3] : literal;
-        emit(a, q0 == 0 ? match[255] : (!m1 ? head : ((q0 == 1 && !m2) ? literal : 0u)));
-        return;
-    }
-    int q = run_out % 258;  // rem(i + 1) mod 258
-    bool cur = continues_run(S, b - 1), n1 = continues_run(S, b - 2), n2;
-    for (int i = b - 1; i >= a; --i) {
-        n2 = continues_run(S, i - 2);
-        q = cur ? (q == 257 ? 0 : q + 1) : 0;
-        const uint32_t literal = lit[S[i]];
-        uint32_t entry = literal;
-        if (cur) {
-            const uint32_t head = q >= 3 ? match[q - 3] : literal;  // (q = 1, 2 here: match[] is not read out of range)
-            entry = q == 0 ? match[255] : (!n1 ? head : ((q == 1 && !n2) ? literal : 0u));
-        }
-        emit(i, entry);
-        cur = n1;
-        n1 = n2;
-    }
-}
-
 // ---------------------------------------------------------------------------------------------------------------
 // device: the chunks of all bands -> one contiguous PNG file
 // ---------------------------------------------------------------------------------------------------------------
@@ -440,6 +390,67 @@ __device__ __forceinline__ void write_tail(const PackJob& job, unsigned long lon
     *job.bytes_out = total;
 }
 
+// ---- tokens dealt evenly to the threads ---------------------------------------------------------------------------
+// Bytes are cheap, tokens are not, and tokens are unevenly spread: a thread that owns 46 contiguous bytes of a
+// gradient emits 46 literals while its neighbour's 46 bytes are the inside of one run -- and a warp takes as long as
+// its slowest thread.  So the band's run bits m(i) are formed word-parallel (32 bytes per thread and step, four bytes
+// per compare), the token-bearing bytes -- the literals, m = 0, and the first byte of every run, which owns all the
+// tokens of its run -- are counted per 32-byte word and prefix-summed, and every thread takes the same NUMBER of them.
+struct TokenCursor {  // where a thread's tokens begin: a word of the run-bit array and what is left of its candidates
+    int word;
+    uint32_t left;
+};
+// candidates of word w: bytes that do not continue a run, and bytes that start one
+__device__ __forceinline__ uint32_t token_candidates(const uint32_t* m, int w, int n) {
+    const uint32_t M = m[w];
+    const uint32_t carry = w > 0 ? m[w - 1] >> 31 : 0u;
+    uint32_t c = ~M | (M & ~((M << 1) | carry));
+    const int valid = n - 32 * w;
+    if (valid < 32) c &= (1u << valid) - 1u;
+    return c;
+}
+// The tokens of `count` candidates from `cur` on, in stream order: lit(entry) for one token, rep(entry, k) for k equal
+// ones (the 258-byte pieces of a long run).  m[] ends in a zero word, so every run ends; next[w] = the first word at or
+// after w that is not all ones, so neither a run's length nor the way to the next candidate is walked word by word.
+template <class Lit, class Rep>
+__device__ __forceinline__ void deal_tokens(const uint8_t* S, const uint32_t* m, const uint16_t* next, int n, TokenCursor cur, int count,
+                                            const uint32_t* lit_table, const uint32_t* match_table, Lit&& lit, Rep&& rep) {
+    int w = cur.word;
+    uint32_t c = cur.left;
+    for (int j = 0; j < count; ++j) {
+        if (c == 0u) {
+            // the next word with a candidate: the one after this, unless that lies wholly inside a run (all ones and
+            // entered from a one) -- then the first word that is not all ones, however far (next[])
+            ++w;
+            if (m[w] == 0xffffffffu && (m[w - 1] >> 31) != 0u) w = next[w];
+            c = token_candidates(m, w, n);
+        }
+        const int b = __ffs(c) - 1;
+        c &= c - 1u;
+        const int i = 32 * w + b;
+        const uint32_t M = m[w];
+        if (((M >> b) & 1u) == 0u) {
+            lit(lit_table[S[i]]);
+            continue;
+        }
+        // a run starts here: its length, however many words it spans
+        const uint32_t zeros = ~(M >> b);  // (the shift brings in zeros: the run is at most 32 - b long here; a full word at b = 0 has none)
+        int len = zeros != 0u ? __ffs(zeros) - 1 : 32;
+        if (len == 32 - b) {
+            const int w2 = next[w + 1];
+            len += 32 * (w2 - (w + 1)) + __ffs(~m[w2]) - 1;
+        }
+        const int whole = len / 258, head = len - 258 * whole;
+        if (head >= 3) {
+            lit(match_table[head - 3]);
+        } else if (head >= 1) {  // too short for a match: one or two literals
+            lit(lit_table[S[i]]);
+            if (head == 2) lit(lit_table[S[i + 1]]);
+        }
+        if (whole > 0) rep(match_table[255], whole);
+    }
+}
+
 // c(x) * g(x) mod the CRC-32 polynomial for a multiplier fixed per launch: T[k] = x^k g(x), bit 31 - k of c selects it
 __device__ __forceinline__ uint32_t crc_mul_fixed(const uint32_t (&T)[32], uint32_t c) {
     uint32_t r = 0u;
@@ -453,10 +464,10 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
                                                             const __grid_constant__ PackJob file, const __grid_constant__ FusedCtl ctl) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ uint32_t s_lit[256], s_match[256], s_crc[256], s_wcrc[kThreads / 32];
-    __shared__ uint32_t s_len[kThreads], s_lead[kThreads];
     __shared__ uint32_t s_scan[kThreads / 32 + 1];
     __shared__ unsigned long long s_sum[kThreads / 32];
-    __shared__ uint32_t s_wsum[kThreads / 32], s_wopen[kThreads / 32];
+    __shared__ uint32_t s_wsum[kThreads / 32];
+    __shared__ uint32_t s_coff[kThreads + 1];
     __shared__ unsigned int s_ticket, s_last;
 
     const int t = threadIdx.x;
@@ -514,6 +525,21 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
             s1 += 1u;
             s2 += (unsigned long long)(r * line);
         }
+        if (staged && (row_bytes & 3) == 0) {
+            // four bytes a step: the word against the funnel of its left neighbour and itself (the bytes three back), a
+            // per-byte subtract, the two Adler sums by dot products with (1,1,1,1) and (0,1,2,3)
+            const uint32_t* raw4 = out_words + r * (row_bytes >> 2);
+            for (int k = t; k < (row_bytes >> 2); k += kThreads) {
+                const uint32_t cur4 = raw4[k], prev4 = k > 0 ? raw4[k - 1] : 0u;
+                const uint32_t v4 = __vsub4(cur4, __funnelshift_r(prev4, cur4, 8));
+                uint8_t* d = dst + 1 + 4 * k;
+                d[0] = (uint8_t)v4, d[1] = (uint8_t)(v4 >> 8), d[2] = (uint8_t)(v4 >> 16), d[3] = (uint8_t)(v4 >> 24);
+                const uint32_t sum4 = __dp4a(v4, 0x01010101u, 0u);
+                s1 += sum4;
+                s2 += (unsigned long long)(r * line + 1 + 4 * k) * sum4 + __dp4a(v4, 0x03020100u, 0u);
+            }
+            continue;
+        }
         for (int x = t; x < row_bytes; x += kThreads) {
             uint8_t cur, left;
             if (staged) {
@@ -537,47 +563,87 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
     const uint32_t adler_b = (uint32_t)((((unsigned long long)n % kAdlerMod) + ((unsigned long long)n % kAdlerMod) * (s1 % kAdlerMod) +
                                          (unsigned long long)kAdlerMod - (s2 % kAdlerMod)) % kAdlerMod);
 
-    // ---- every thread's piece of the stream; how far the run that reaches its end goes on to the right
-    const int piece = (n + kThreads - 1) / kThreads;
-    const int a = min(t * piece, n), b = min(a + piece, n);
+    // ---- run bits, 32 bytes per thread and step: byte i against byte i - 3 is word k against the funnel of words
+    // k - 1 and k, four bytes per compare (filt is 16-byte aligned; the bytes past n are masked off)
+    uint32_t* s_m = reinterpret_cast<uint32_t*>(out + (((cap + kBandSlack + kChunkOverhead + 3) / 4) * 4 + 16));
+    const int n_words = (n + 31) >> 5;
     {
-        int rem = 0;  // bytes from the piece's first byte on that continue a run (if all do: its length)
-        for (int i = b - 1; i >= a; --i) rem = continues_run(filt, i) ? rem + 1 : 0;
-        s_len[t] = (uint32_t)(b - a);
-        s_lead[t] = (uint32_t)rem;
-    }
-    // run_out(t) = lead(t + 1) + lead(t + 2) + ... up to and including the first piece that is not all run (a run longer
-    // than a piece -- black sky -- is summed piece by piece): a suffix scan under (s1, o1) o (s2, o2) = (s1 + (o1 ? s2 : 0),
-    // o1 && o2), by shuffles inside the warps and a walk over the (at most seven) warps to the right
-    const bool all_run = s_lead[t] == s_len[t];
-    int run_out;
-    {
-        const int lane = t & 31, warp = t >> 5;
-        int s = (int)s_lead[t];
-        bool o = all_run;
-        for (int d = 1; d < 32; d <<= 1) {
-            const int s2 = __shfl_down_sync(0xffffffffu, s, d);
-            const int o2 = __shfl_down_sync(0xffffffffu, (int)o, d);
-            if (lane + d < 32) {
-                s += o ? s2 : 0;
-                o = o && (o2 != 0);
+        const uint32_t* F = reinterpret_cast<const uint32_t*>(filt);
+        const int n_f = (n + 3) >> 2;
+        for (int w = t; w < n_words; w += kThreads) {
+            uint32_t bits = 0u, prev = w > 0 ? F[8 * w - 1] : 0u;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const uint32_t curw = 8 * w + k < n_f ? F[8 * w + k] : 0u;
+                const uint32_t eq = __vcmpeq4(curw, __funnelshift_r(prev, curw, 8));
+                bits |= (((eq & 0x08040201u) * 0x01010101u) >> 24) << (4 * k);
+                prev = curw;
             }
+            if (w == 0) bits &= ~7u;  // (the first three bytes have nothing three behind them)
+            const int valid = n - 32 * w;
+            if (valid < 32) bits &= (1u << valid) - 1u;
+            s_m[w] = bits;
         }
-        if (lane == 0) s_wsum[warp] = s, s_wopen[warp] = o ? 1u : 0u;
-        int es = __shfl_down_sync(0xffffffffu, s, 1);
-        int eo = __shfl_down_sync(0xffffffffu, (int)o, 1);
-        if (lane == 31) es = 0, eo = 1;
-        __syncthreads();
-        for (int w = warp + 1; w < kThreads / 32 && eo; ++w) {
-            es += (int)s_wsum[w];
-            eo = (int)s_wopen[w];
-        }
-        run_out = es;
+        if (t == 0) s_m[n_words] = 0u;
     }
-
+    uint16_t* s_next = reinterpret_cast<uint16_t*>(s_m + (cap + 31) / 32 + 2);  // [n_words + 1]
+    __syncthreads();
+    // ---- candidates per thread's words, their prefix sum, and every thread's equal share of them
+    const int words_each = (n_words + kThreads - 1) / kThreads;
+    const int w_first = min(t * words_each, n_words), w_last = min(w_first + words_each, n_words);
+    {
+        // next[w] (see deal_tokens): the first word of the thread's own range that is not all ones, then the minimum
+        // over the ranges to the right (a suffix scan: shuffles inside the warps, a walk over the warps to the right)
+        int own = n_words;  // (the end word is zero: it is "not all ones" for every run that reaches it)
+        for (int w = w_last - 1; w >= w_first; --w)
+            if (s_m[w] != 0xffffffffu) own = w;
+        int suffix = own;
+        for (int d = 1; d < 32; d <<= 1) {
+            const int other = __shfl_down_sync(0xffffffffu, suffix, d);
+            if ((t & 31) + d < 32) suffix = min(suffix, other);
+        }
+        if ((t & 31) == 0) s_wsum[t >> 5] = (uint32_t)suffix;
+        int beyond = __shfl_down_sync(0xffffffffu, suffix, 1);  // the ranges to the right of this thread's, inside its warp
+        if ((t & 31) == 31) beyond = n_words;
+        __syncthreads();
+        for (int wp = (t >> 5) + 1; wp < kThreads / 32; ++wp) beyond = min(beyond, (int)s_wsum[wp]);
+        int running = beyond;
+        for (int w = w_last - 1; w >= w_first; --w) {
+            if (s_m[w] != 0xffffffffu) running = w;
+            s_next[w] = (uint16_t)running;
+        }
+        if (t == 0) s_next[n_words] = (uint16_t)n_words;
+    }
+    uint32_t mine = 0u;
+    for (int w = w_first; w < w_last; ++w) mine += (uint32_t)__popc(token_candidates(s_m, w, n));
+    uint32_t n_candidates = 0u;
+    const uint32_t before_mine = block_exclusive_sum(mine, s_scan, &n_candidates);
+    s_coff[t] = before_mine;
+    if (t == 0) s_coff[kThreads] = n_candidates;
+    __syncthreads();
+    const int share = ((int)n_candidates + kThreads - 1) / kThreads;
+    const int c_first = min(t * share, (int)n_candidates), c_count = min(share, (int)n_candidates - c_first);
+    TokenCursor cursor = {0, 0u};
+    if (c_count > 0) {
+        int lo = 0, hi = kThreads;  // the thread u whose words hold candidate c_first: s_coff[u] <= c_first < s_coff[u + 1]
+        while (hi - lo > 1) {
+            const int midp = (lo + hi) >> 1;
+            if (s_coff[midp] <= (uint32_t)c_first) lo = midp; else hi = midp;
+        }
+        int skip = c_first - (int)s_coff[lo];
+        int w = min(lo * words_each, n_words);
+        uint32_t c = token_candidates(s_m, w, n);
+        for (int pc = __popc(c); skip >= pc; pc = __popc(c)) {
+            skip -= pc;
+            c = token_candidates(s_m, ++w, n);
+        }
+        for (; skip > 0; --skip) c &= c - 1u;
+        cursor.word = w, cursor.left = c;
+    }
     // ---- bit positions
     uint32_t my_bits = 0;
-    walk_tokens(filt, a, b, run_out, all_run, s_lit, s_match, [&](int, uint32_t entry) { my_bits += entry >> 24; });
+    deal_tokens(filt, s_m, s_next, n, cursor, c_count, s_lit, s_match, [&](uint32_t entry) { my_bits += entry >> 24; },
+                [&](uint32_t entry, int k) { my_bits += (uint32_t)k * (entry >> 24); });
     uint32_t token_bits = 0;
     const uint32_t my_bit = block_exclusive_sum(my_bits, s_scan, &token_bits);
     const int prefix = band == 0 ? 2 : 0;  // the zlib header travels in the first band's chunk
@@ -600,13 +666,19 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
             atomicOr(out_words + w, (uint32_t)v);
             if ((uint32_t)(v >> 32) != 0u) atomicOr(out_words + w + 1, (uint32_t)(v >> 32));
         }
-        // the piece's tokens from its last one back to its first, each at its own bit position
-        uint32_t bit = bit0 + code.header_bits + my_bit + my_bits;
-        walk_tokens(filt, a, b, run_out, all_run, s_lit, s_match, [&](int, uint32_t entry) {
-            const uint32_t nb = entry >> 24;
-            bit -= nb;
-            if (nb) put_bits(bit, entry);
-        });
+        // the thread's tokens in stream order, each at its own bit position
+        uint32_t bit = bit0 + code.header_bits + my_bit;
+        deal_tokens(filt, s_m, s_next, n, cursor, c_count, s_lit, s_match,
+                    [&](uint32_t entry) {
+                        put_bits(bit, entry);
+                        bit += entry >> 24;
+                    },
+                    [&](uint32_t entry, int k) {
+                        for (; k > 0; --k) {
+                            put_bits(bit, entry);
+                            bit += entry >> 24;
+                        }
+                    });
         if (t == 0) put_bits(bit0 + code.header_bits + token_bits, code.eob);
         data_len = prefix + (int)deflated;
     } else {
@@ -748,7 +820,8 @@ int rows_per_band(int width, int height) {
 }
 size_t band_smem(int width, int rows) {
     const size_t cap = (size_t)rows * (1 + 3 * (size_t)width);
-    return ((cap + 15) & ~(size_t)15) + ((cap + kBandSlack + kChunkOverhead + 3) / 4) * 4 + 16;
+    // the filtered rows, the chunk (+ 16: a word past its end is read when it is copied out), the run bits (+ an end word) and their next[] (16 bits per word)
+    return ((cap + 15) & ~(size_t)15) + ((cap + kBandSlack + kChunkOverhead + 3) / 4) * 4 + 16 + ((cap + 31) / 32 + 2) * 6 + 4;
 }
 long long slot_bytes_of(int width, int rows) {
     const long long cap = (long long)rows * (1 + 3ll * width);
