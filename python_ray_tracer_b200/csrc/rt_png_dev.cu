@@ -103,7 +103,7 @@ struct BandJob {
     // sums over the set bits of crc(A) of crc_mul[level][k] = x^k * x^(8 crc_slice 2^level) mod the polynomial (made on
     // the host): 32 independent AND / XORs against constant-bank operands instead of a 32-step shift-and-add loop.
     int crc_slice;
-    uint32_t crc_mul[6][32];  // levels 0..4: inside a warp; 5: one warp's worth of bytes (Horner over the warps)
+    uint32_t crc_mul[10][32];  // level l: right-hand sides of crc_slice * 2^l bytes
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -463,7 +463,7 @@ template <bool FUSED>
 __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constant__ PngCode code, const __grid_constant__ BandJob job,
                                                             const __grid_constant__ PackJob file, const __grid_constant__ FusedCtl ctl) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ uint32_t s_lit[256], s_match[256], s_crc[256], s_wcrc[kThreads / 32];
+    __shared__ uint32_t s_lit[256], s_match[256], s_crc[256], s_wcrc[1];
     __shared__ uint32_t s_scan[kThreads / 32 + 1];
     __shared__ unsigned long long s_sum[kThreads / 32];
     __shared__ uint32_t s_wsum[kThreads / 32];
@@ -706,7 +706,10 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
 
     // ---- CRC-32 of type + data by every thread (BandJob::crc_slice): a band of noise or fine gradients is a chunk of
     // several KB, and one warp walking it byte by byte (two dependent shared-memory loads per byte) followed by bit-serial
-    // combine steps was the longest serial stretch of such a block
+    // combine steps was the longest serial stretch of such a block.  The slices' CRCs are then combined by ONE warp --
+    // a lane folds kThreads / 32 neighbouring slices (Horner, multiplier of one slice), a shuffle tree the 32 results:
+    // a combine step is ~100 instructions whoever needs its result, so eight warps climbing the tree side by side cost
+    // four times the instructions for the same depth
     const int n_crc = 4 + data_len;
     {
         const int end = n_crc - (kThreads - 1 - t) * job.crc_slice, begin = max(end - job.crc_slice, 0);
@@ -716,18 +719,26 @@ __global__ void __launch_bounds__(kThreads) png_band_kernel(const __grid_constan
             for (int i = begin; i < end; ++i) c = s_crc[(c ^ out[4 + i]) & 255u] ^ (c >> 8);
             c ^= 0xffffffffu;
         }
+        s_coff[t] = c;  // (the candidates' offsets are done with)
+    }
+    __syncthreads();
+    if (t < 32) {
+        constexpr int kFold = kThreads / 32;  // 4, 8, 16 or 32 slices per lane: levels log2(kFold) .. log2(kFold) + 4 of the tree follow
+        constexpr int kFirstLevel = kFold == 4 ? 2 : kFold == 8 ? 3 : kFold == 16 ? 4 : 5;
+        uint32_t c = s_coff[kFold * t];
+#pragma unroll
+        for (int j = 1; j < kFold; ++j) c = crc_mul_fixed(job.crc_mul[0], c) ^ s_coff[kFold * t + j];
 #pragma unroll
         for (int l = 0; l < 5; ++l) {
             const uint32_t right = __shfl_down_sync(0xffffffffu, c, 1 << l);
-            const uint32_t left = crc_mul_fixed(job.crc_mul[l], c);
+            const uint32_t left = crc_mul_fixed(job.crc_mul[kFirstLevel + l], c);
             if ((t & ((2 << l) - 1)) == 0) c = left ^ right;
         }
-        if ((t & 31) == 0) s_wcrc[t >> 5] = c;
+        if (t == 0) s_wcrc[0] = c;
     }
     __syncthreads();
     if (t == 0) {
-        uint32_t crc = s_wcrc[0];
-        for (int w = 1; w < kThreads / 32; ++w) crc = crc_mul_fixed(job.crc_mul[5], crc) ^ s_wcrc[w];
+        const uint32_t crc = s_wcrc[0];
         uint8_t* p = out + 8 + data_len;
         p[0] = (uint8_t)(crc >> 24), p[1] = (uint8_t)(crc >> 16), p[2] = (uint8_t)(crc >> 8), p[3] = (uint8_t)crc;
         job.sizes[band] = (uint32_t)(kChunkOverhead + data_len);
@@ -839,10 +850,10 @@ void fill_band_job(BandJob& job, int width, int height, int r, void* scratch_dev
     job.adlers = job.sizes + bands;
     // the chunk CRC's per-launch multipliers (see BandJob); kept for the next call of the same band size
     static thread_local int made_for = 0;
-    static thread_local uint32_t made[6][32];
+    static thread_local uint32_t made[10][32];
     const int slice = (int)((r * (1 + 3ll * width) + kBandSlack + kChunkOverhead + kThreads - 1) / kThreads);
     if (made_for != slice) {
-        for (int l = 0; l < 6; ++l) {
+        for (int l = 0; l < 10; ++l) {
             uint32_t g = x2nmodp(png_code().x2n, (uint64_t)slice, 3u + (unsigned)l);  // x^(8 slice 2^l)
             for (int k = 0; k < 32; ++k) {
                 made[l][k] = g;
