@@ -115,6 +115,43 @@ def test_device_png_of_rendered_frames(rt_fast, tmp_path):
                                       C.byref(cam), small.data_ptr(), 4096, C.byref(used)) == -1 and b"too small" in lib.rt_last_error()
 
 
+def test_device_png_of_random_sizes_and_contents(tmp_path):
+    """Sizes off every alignment the kernel cares about (4 bytes a compare, 32 bytes a run-bit word, 16 bytes a packed
+    store, bands cut short by the image's end), contents from one run to all literals, and the widest row a band can
+    hold: the file always decodes to its input."""
+    import torch
+
+    from python_ray_tracer_b200.infrastructure.png import DevicePngEncoder
+
+    rng = np.random.default_rng(20260611)
+
+    def content(kind, h, w):
+        if kind == 0:
+            return rng.integers(0, 256, (h, w, 3), dtype=np.uint8)                              # noise: stored bands
+        if kind == 1:
+            return np.broadcast_to(rng.integers(0, 256, 3, dtype=np.uint8), (h, w, 3)).copy()   # one colour: one run per row
+        if kind == 2:
+            img = np.zeros((h, w, 3), dtype=np.uint8)                                           # flat with sparse specks: short and long runs
+            k = max(1, h * w // 17)
+            img[rng.integers(0, h, k), rng.integers(0, w, k)] = rng.integers(0, 256, (k, 3))
+            return img
+        if kind == 3:
+            g = np.add.outer(np.arange(h) * 3, np.arange(w))[:, :, None] // np.array([1, 2, 5])  # gradients: constant residuals
+            return (g % 256).astype(np.uint8)
+        img = np.repeat(rng.integers(0, 256, (h, (w + 6) // 7, 3), dtype=np.uint8), 7, axis=1)[:, :w]  # steps of 7 pixels
+        return np.ascontiguousarray(img)
+
+    sizes = [(1, 1), (1, 7), (2, 1), (3, 3), (5, 1081), (86, 1), (87, 2), (11, 10), (12, 21), (13, 43), (64, 85), (65, 86), (31, 341),
+             (33, 342), (80, 599), (7, 2731), (3, 21666)]
+    sizes += [(int(rng.integers(1, 90)), int(rng.integers(1, 700))) for _ in range(14)]
+    for n, (h, w) in enumerate(sizes):
+        img = content(n % 5, h, w)
+        data = DevicePngEncoder(w, h).encode(torch.from_numpy(img).cuda())
+        assert np.array_equal(_decode(data, tmp_path), img), (h, w, n % 5)
+    with pytest.raises(ValueError):
+        DevicePngEncoder(21667, 2)  # a row that no stored block can hold
+
+
 def test_single_launch_file_equals_bands_plus_pack(tmp_path):
     """rt_png_encode_file_dev (one launch: chunk positions by a single-pass prefix sum, the last block writes the tail)
     makes byte for byte the file of rt_png_encode_bands_dev + rt_png_pack_dev, for every content and size, again and
