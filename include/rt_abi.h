@@ -18,8 +18,12 @@
  *     stream).  Device entry points only enqueue work on `stream`; they do not
  *     synchronise.  Host entry points are synchronous;
  *   - the library keeps no scene state between calls.  The host entry points
- *     keep a per-thread, per-device staging cache (pinned + device scratch) that
- *     rt_release_cache() frees.
+ *     keep a per-thread, per-device staging cache (device scratch buffers, two
+ *     streams, a small pinned landing zone for rt_render_png_host) that
+ *     rt_release_cache() frees.  Their copies into the caller's buffers run under
+ *     the rendering of the next row chunk only when those buffers are pinned
+ *     (cudaHostAlloc / cudaHostRegister); into pageable memory every chunk's copy
+ *     blocks the call, and the result is the same;
  *
  * Scene layout ("sphere SoA"): a field-major table of doubles,
  *     spheres[f * n_spheres + s],  f in rt_sphere_field,  s = shape index

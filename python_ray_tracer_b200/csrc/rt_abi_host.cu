@@ -235,6 +235,15 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
     };
     char* rgb_base = static_cast<char*>(c->rgb.ptr);
     uint64_t* stats_dev = stats_host != nullptr ? static_cast<uint64_t*>(c->stats.ptr) : nullptr;
+    // (a failure inside the loop must not return while earlier chunks are still being copied into the caller's
+    // buffers: it leaves the loop, both streams are drained below, then the status is returned)
+    cudaError_t failed = cudaSuccess;
+    const char* failed_call = "";
+#define LOOP_CUDA(call)                          \
+    if ((failed = (call)) != cudaSuccess) {      \
+        failed_call = #call;                     \
+        break;                                   \
+    }
     for (int i = 0; i < chunks && n > 0; ++i) {
         const int r0 = row0 + chunk_start(i), r1 = row0 + chunk_start(i + 1);
         if (r1 <= r0) continue;
@@ -243,27 +252,39 @@ int rt_render_frame_host(int device, const double* spheres_host, int32_t n_spher
                                 rgb_host != nullptr ? rgb_base + first * elem : nullptr, rgb_dtype, n,
                                 rgb8_host != nullptr ? static_cast<uint8_t*>(c->rgb8.ptr) + first * 3 : nullptr, stats_dev,
                                 c->stream);
-        if (rc != RT_OK) return rc;
-        HOST_CUDA(cudaEventRecord(c->rendered[i], c->stream));
-        HOST_CUDA(cudaStreamWaitEvent(c->copy_stream, c->rendered[i], 0));
+        if (rc != RT_OK) break;
+        LOOP_CUDA(cudaEventRecord(c->rendered[i], c->stream));
+        LOOP_CUDA(cudaStreamWaitEvent(c->copy_stream, c->rendered[i], 0));
         if (rgb_host != nullptr) {
             // the chunk's rows of the three planes: one strided copy (three when a plane is
             // longer than a 2-D copy's pitch may be)
             const size_t pitch = (size_t)n * elem;
             if (pitch <= ((size_t)1 << 30)) {
-                HOST_CUDA(cudaMemcpy2DAsync(static_cast<char*>(rgb_host) + (size_t)first * elem, pitch,
+                LOOP_CUDA(cudaMemcpy2DAsync(static_cast<char*>(rgb_host) + (size_t)first * elem, pitch,
                                             rgb_base + (size_t)first * elem, pitch, (size_t)count * elem, 3,
                                             cudaMemcpyDeviceToHost, c->copy_stream));
             } else {
                 for (int ch = 0; ch < 3; ++ch)
-                    HOST_CUDA(cudaMemcpyAsync(static_cast<char*>(rgb_host) + ((size_t)ch * n + first) * elem,
+                    LOOP_CUDA(cudaMemcpyAsync(static_cast<char*>(rgb_host) + ((size_t)ch * n + first) * elem,
                                               rgb_base + ((size_t)ch * n + first) * elem, (size_t)count * elem,
                                               cudaMemcpyDeviceToHost, c->copy_stream));
             }
         }
         if (rgb8_host != nullptr)
-            HOST_CUDA(cudaMemcpyAsync(rgb8_host + first * 3, static_cast<uint8_t*>(c->rgb8.ptr) + first * 3,
+            LOOP_CUDA(cudaMemcpyAsync(rgb8_host + first * 3, static_cast<uint8_t*>(c->rgb8.ptr) + first * 3,
                                       (size_t)count * 3, cudaMemcpyDeviceToHost, c->copy_stream));
+    }
+#undef LOOP_CUDA
+    if (failed != cudaSuccess || rc != RT_OK) {
+        cudaStreamSynchronize(c->copy_stream);
+        cudaStreamSynchronize(c->stream);
+        if (failed != cudaSuccess) {
+            char msg[256];
+            snprintf(msg, sizeof(msg), "%.160s: %s", failed_call, cudaGetErrorString(failed));
+            rt_internal_set_error(msg);
+            return RT_ERR_CUDA;
+        }
+        return rc;
     }
     HOST_CUDA(cudaStreamSynchronize(c->copy_stream));
     if (stats_host != nullptr)
