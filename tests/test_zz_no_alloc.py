@@ -87,7 +87,7 @@ def test_static_encoder_equals_the_callers_scratch_encoder_two_calls_in_a_row(tm
         stream.synchronize()
         assert torch.cuda.memory_allocated(device) == allocated, name
         if name.endswith("again"):  # (the first call on a device may load the module; later ones must not move the free-memory figure)
-            assert torch.cuda.mem_get_info(device)[0] == free_before, name
+            assert torch.cuda.mem_get_info(device)[0] >= free_before, name  # (nothing was taken from the device)
         n_want, n_got = int(want_size.item()), int(got_size.item())
         assert n_want > 0 and n_got == n_want, (name, n_want, n_got)
         want = want_file[:n_want].cpu().numpy()
