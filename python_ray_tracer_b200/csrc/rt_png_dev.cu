@@ -788,14 +788,14 @@ __global__ void __launch_bounds__(kThreads) png_pack_kernel(const __grid_constan
     __shared__ unsigned long long s_sum[kThreads / 32];
     const int t = threadIdx.x, b = blockIdx.x;
     // where this band's chunk goes: after the head and the chunks of the bands before it
-    unsigned long long before = 0, all = 0;
+    // (both sums in one reduction: a PNG is far below 4 GB, so each fits 32 bits of the 64-bit word)
+    unsigned long long both = 0;
     for (int j = t; j < job.n_bands; j += kThreads) {
         const unsigned long long s = job.sizes[j];
-        all += s;
-        if (j < b) before += s;
+        both += (s << 32) | (j < b ? s : 0ull);
     }
-    before = block_sum64(before, s_sum);
-    all = block_sum64(all, s_sum);
+    both = block_sum64(both, s_sum);
+    const unsigned long long before = both & 0xffffffffull, all = both >> 32;
     const bool fits = 33ull + all + 21ull + 12ull <= (unsigned long long)job.capacity;
     if (fits) copy_chunk(job.out + 33 + before, job.slots + (long long)b * job.slot_bytes, (int)job.sizes[b], t);
     if (b == 0 && fits)
