@@ -186,6 +186,12 @@ int rt_release_cache(void);
  * it.  Every device entry point makes the same check first, so such a launch never goes unnoticed;
  * call this after synchronising to learn about the launch just finished. */
 int rt_device_status(int device);
+/* 1 if a camera launch (rt_render_rows_dev / rt_render_strips_dev) with this env and sphere count reads the whole
+ * scene from its kernel parameters (rt_env.spheres_host: at most RT_SMALL_SCENE_SPHERES shapes, fast policy, no tree,
+ * RT_FLAG_GENERIC_KERNEL clear): spheres_dev and point_lights_dev are then never dereferenced -- any non-NULL
+ * pointer will do -- so a caller whose scene changes every frame (an animation) need not upload it, and its host
+ * thread need not wait on the stream for the copy.  0 otherwise.  Nothing in the reference corresponds to it. */
+int rt_scene_travels_as_parameter(const rt_env* env, int32_t n_spheres);
 
 /*
  * rt_measure_fma_peak -- achieved FLOP/s (2 per FMA) of a register-resident chain of

@@ -316,6 +316,11 @@ __attribute__((visibility("hidden"))) int rt_internal_small_scene(const rt_env* 
 
 int rt_device_status(int device) { return pending_device_error(device); }
 
+int rt_scene_travels_as_parameter(const rt_env* env, int32_t n_spheres) {
+    if (env == nullptr || n_spheres <= 0) return 0;
+    return small_scene(env, n_spheres) ? 1 : 0;
+}
+
 int rt_device_count(int* count_out) {
     if (count_out == nullptr) return fail(RT_ERR_BAD_ARG, "count_out is NULL");
     int count = 0;

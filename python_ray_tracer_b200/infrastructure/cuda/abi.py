@@ -171,6 +171,7 @@ PROTOTYPES = {
         [C.c_int, _P, C.c_int32, _P, C.POINTER(RtEnv), _P, C.POINTER(C.c_double), _P, C.c_int64,
          _P, C.c_int32, _P],
     ),
+    "rt_scene_travels_as_parameter": (C.c_int, [C.POINTER(RtEnv), C.c_int32]),
     "rt_png_rows_per_band": (C.c_int32, [C.c_int32, C.c_int32]),
     "rt_png_scratch_bytes": (C.c_int64, [C.c_int32, C.c_int32]),
     "rt_png_file_bound": (C.c_int64, [C.c_int32, C.c_int32]),

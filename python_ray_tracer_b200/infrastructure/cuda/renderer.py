@@ -247,6 +247,7 @@ class CudaRenderer(Renderer):
         self._accel_dev = None
         self._scene_key: Optional[bytes] = None
         self._scene_dev: Optional[Tuple[Any, Any]] = None
+        self._unused_dev = None  # what camera launches of kernel-parameter scenes are handed as table pointers
 
     # ------------------------------------------------------------------ helpers
     def _wants_accel(self, flat: FlatScene) -> bool:
@@ -299,6 +300,19 @@ class CudaRenderer(Renderer):
             self._scene_key, self._scene_dev = key, (spheres, lights)
         return self._scene_dev
 
+    def _scene_pointers(self, flat: FlatScene, env: abi.RtEnv):
+        """Device pointers of the sphere SoA and the light table for a CAMERA launch with ``env``.  A scene the
+        library sends as a kernel parameter (``rt_scene_travels_as_parameter``: the README and ``main.py`` scenes)
+        is never read from device memory, so nothing is uploaded for it -- and a scene that changes every frame
+        (an animation) costs no copy and no wait on the stream."""
+        if abi.load().rt_scene_travels_as_parameter(C.byref(env), flat.n_spheres):
+            if self._unused_dev is None:
+                torch = _require_cuda(self.device)
+                self._unused_dev = torch.zeros(256, dtype=torch.uint8, device=torch.device("cuda", self.device))
+            return self._unused_dev.data_ptr(), self._unused_dev.data_ptr()
+        spheres, lights = self.upload_scene(flat)
+        return spheres.data_ptr(), lights.data_ptr()
+
     def _stream(self) -> int:
         return int(_torch().cuda.current_stream(self.device).cuda_stream)
 
@@ -349,18 +363,20 @@ class CudaRenderer(Renderer):
         torch = _require_cuda(self.device)
         lib = abi.load()
         dev = torch.device("cuda", self.device)
-        spheres, lights = self.upload_scene(flat)
         n = (row1 - row0) * int(camera.width)
         if planes is None and not no_planes:
             planes = torch.empty((3, n), dtype=self._torch_dtype(), device=dev)
         if rgba8 is None and want_rgba8:
             rgba8 = torch.empty((n, 3 if flags & abi.RT_FLAG_RGB8 else 4), dtype=torch.uint8, device=dev)
         stats = self._new_stats()
+        if self._wants_accel(flat):
+            self.upload_scene(flat)  # (builds and uploads the tree that _env names)
         env = self._env(flat, flags)
+        spheres_ptr, lights_ptr = self._scene_pointers(flat, env)
         cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
         abi.check(
             lib.rt_render_rows_dev(
-                self.device, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env), C.byref(cam),
+                self.device, spheres_ptr, flat.n_spheres, lights_ptr, C.byref(env), C.byref(cam),
                 row0, row1, None if planes is None else planes.data_ptr(), self._abi_dtype(),
                 max(n, 1) if planes is None else planes.stride(0),
                 None if rgba8 is None else rgba8.data_ptr(), None if stats is None else stats.data_ptr(),
@@ -381,7 +397,6 @@ class CudaRenderer(Renderer):
         dev = torch.device("cuda", self.device)
         if int(camera.height) != shard.height:
             raise ValueError(f"shard is for {shard.height} rows, camera has {camera.height}")
-        spheres, lights = self.upload_scene(flat)
         rows = int(lib.rt_strip_shard_rows(int(camera.height), shard.strip_rows, shard.rank, shard.world))
         if rows != shard.n_rows:
             raise RuntimeError(f"host and library disagree on the shard size: {shard.n_rows} vs {rows}")
@@ -391,11 +406,14 @@ class CudaRenderer(Renderer):
         if rgba8 is None and want_rgba8:
             rgba8 = torch.empty((n, 3 if flags & abi.RT_FLAG_RGB8 else 4), dtype=torch.uint8, device=dev)
         stats = self._new_stats()
+        if self._wants_accel(flat):
+            self.upload_scene(flat)
         env = self._env(flat, flags)
+        spheres_ptr, lights_ptr = self._scene_pointers(flat, env)
         cam = abi.make_camera(as_float_triple(camera.position, "camera position"), camera.width, camera.height)
         abi.check(
             lib.rt_render_strips_dev(
-                self.device, spheres.data_ptr(), flat.n_spheres, lights.data_ptr(), C.byref(env), C.byref(cam),
+                self.device, spheres_ptr, flat.n_spheres, lights_ptr, C.byref(env), C.byref(cam),
                 shard.strip_rows, shard.rank, shard.world, planes.data_ptr(), self._abi_dtype(), max(planes.stride(0), 1),
                 None if rgba8 is None else rgba8.data_ptr(), None if stats is None else stats.data_ptr(),
                 self._stream(),

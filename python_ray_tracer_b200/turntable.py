@@ -73,8 +73,11 @@ def _write_atomically(path: Path, data) -> None:
 
 def _render_frames_device(renderer, scene_of_frame, todo, out_dir: Path, stats: Dict[str, float]) -> Dict[str, float]:
     """The batch with the PNGs made on the GPU (``DevicePngEncoder``): per frame one trace launch (8-bit image
-    only), the band encoder and the pack kernel, which writes the ~0.6 MB file into a pinned host buffer; two
-    frames in flight, so the host writes frame ``k`` while the GPU traces and encodes frame ``k + 1``."""
+    only), the band encoder and the pack kernel, which writes the ~0.6 MB file into a pinned host buffer.  The GPU
+    needs ~0.12 ms per 1080p frame; describing the next scene and writing a file take the host longer than that, so
+    the files are written by a small thread pool (the system calls release the GIL) while this thread only describes
+    scenes and enqueues launches: four frames in flight -- a frame's file is handed to the pool two iterations after
+    its launches, and its slot is taken again two iterations after that."""
     import torch
 
     from .infrastructure.cuda import abi
@@ -85,38 +88,61 @@ def _render_frames_device(renderer, scene_of_frame, todo, out_dir: Path, stats: 
     width, height = int(first.width), int(first.height)
     stream = torch.cuda.current_stream(device)
     dev = torch.device("cuda", device)
+    n_slots, lag = 4, 2
     slots = [{"rgb8": torch.empty((width * height, 3), dtype=torch.uint8, device=dev), "enc": DevicePngEncoder(width, height, device),
               "done": torch.cuda.Event(), "start": torch.cuda.Event(enable_timing=True), "end": torch.cuda.Event(enable_timing=True),
-              "frame": None} for _ in range(2)]
+              "frame": None, "written": None} for _ in range(n_slots)]
+    failed = []
 
-    def retire(slot) -> None:
+    def write(frame: int, data) -> float:
+        t0 = time.perf_counter()
+        _write_atomically(frame_path(out_dir, frame), data)
+        return time.perf_counter() - t0
+
+    def hand_over(slot, pool) -> None:
+        """The slot's frame is (or is about to be) finished on the GPU: its file goes to the writers."""
         if slot["frame"] is None:
             return
         slot["done"].synchronize()
         stats["gpu_s"] += slot["start"].elapsed_time(slot["end"]) * 1e-3
-        t0 = time.perf_counter()
-        _write_atomically(frame_path(out_dir, slot["frame"]), slot["enc"].finish())
-        stats["encode_s"] += time.perf_counter() - t0
-        stats["frames"] += 1
+        slot["written"] = pool.submit(write, slot["frame"], slot["enc"].finish())  # (a view of the slot's pinned buffer)
         slot["frame"] = None
 
+    def release(slot) -> None:
+        """The slot's buffers may be used again once its file is on disk."""
+        if slot["written"] is None:
+            return
+        try:
+            stats["encode_s"] += slot["written"].result()
+            stats["frames"] += 1
+        except Exception as exc:  # noqa: BLE001 -- re-raised once every frame that can be written is written
+            failed.append(exc)
+        slot["written"] = None
+
     wall0 = time.perf_counter()
-    for i, frame in enumerate(todo):
-        slot = slots[i % 2]
-        retire(slot)
-        scene = scene_of_frame(frame)
-        flat = renderer.flatten(scene)
-        slot["start"].record(stream)
-        renderer.render_rows(flat, scene.camera, 0, height, rgba8=slot["rgb8"], flags=abi.RT_FLAG_RGB8, no_planes=True)
-        slot["enc"].enqueue(slot["rgb8"], int(stream.cuda_stream))
-        slot["end"].record(stream)
-        slot["done"].record(stream)
-        slot["frame"] = frame
-    for slot in slots:
-        retire(slot)
+    with ThreadPoolExecutor(max(2, min(4, stats.get("encoder_threads", 2)))) as pool:
+        for i, frame in enumerate(todo):
+            if i >= lag:
+                hand_over(slots[(i - lag) % n_slots], pool)
+            slot = slots[i % n_slots]
+            release(slot)
+            scene = scene_of_frame(frame)
+            flat = renderer.flatten(scene)
+            slot["start"].record(stream)
+            renderer.render_rows(flat, scene.camera, 0, height, rgba8=slot["rgb8"], flags=abi.RT_FLAG_RGB8, no_planes=True)
+            slot["enc"].enqueue(slot["rgb8"], int(stream.cuda_stream))
+            slot["end"].record(stream)
+            slot["done"].record(stream)
+            slot["frame"] = frame
+        for k in range(len(todo), len(todo) + n_slots):  # the frames still in flight, oldest first
+            hand_over(slots[(k - lag) % n_slots], pool)
+        for slot in slots:
+            release(slot)
     abi.check(abi.load().rt_device_status(device), "rt_device_status")
     stats["wall_s"] = time.perf_counter() - wall0
-    stats["encoder"] = "device (rt_png_encode_bands_dev + rt_png_pack_dev); encode_s = file writes"
+    stats["encoder"] = "device (rt_png_encode_bands_dev + rt_png_pack_dev); encode_s = file writes (on a thread pool)"
+    if failed:
+        raise failed[0]
     return stats
 
 

@@ -236,6 +236,32 @@ def test_abi_rejects_bad_arguments_without_a_gpu():
     assert rc == -1
 
 
+def test_scene_travels_as_parameter_predicate():
+    """rt_scene_travels_as_parameter: only small scenes of the fast policy whose host tables the env names, with no
+    tree and the kernel-parameter path not switched off (then a camera launch never reads the device tables)."""
+    lib = abi.load()
+    table = np.ascontiguousarray(np.ones((abi.RT_SPHERE_FIELDS if hasattr(abi, "RT_SPHERE_FIELDS") else 12, 3)))
+    lights = np.ascontiguousarray(np.ones((2, 3)))
+
+    def env(**kw):
+        args = dict(mode=abi.RT_MODE_FAST, flags=abi.RT_FLAG_NONE, spheres_host=table, point_lights_host=lights)
+        args.update(kw)
+        n_lights = args.pop("n_lights", 1)
+        return abi.make_env((0.0, 0.2, -2.0), n_lights, [0.1], (1.0, 1.0, 1.0), **args)
+
+    yes = lambda e, n=3: lib.rt_scene_travels_as_parameter(ctypes.byref(e), n)  # noqa: E731
+    assert yes(env()) == 1 and yes(env(), abi.RT_SMALL_SCENE_SPHERES) == 1
+    assert yes(env(), abi.RT_SMALL_SCENE_SPHERES + 1) == 0 and yes(env(), 0) == 0
+    assert yes(env(mode=abi.RT_MODE_EXACT)) == 0
+    assert yes(env(flags=abi.RT_FLAG_GENERIC_KERNEL)) == 0
+    assert yes(env(spheres_host=None)) == 0 and yes(env(point_lights_host=None)) == 0
+    assert yes(env(flags=abi.RT_FLAG_ALL_POINT_LIGHTS, n_lights=2)) == 0 and yes(env(flags=abi.RT_FLAG_ALL_POINT_LIGHTS)) == 1
+    with_tree = env()
+    with_tree.accel_dev, with_tree.accel_bytes = 4096, 64
+    assert yes(with_tree) == 0
+    assert lib.rt_scene_travels_as_parameter(None, 3) == 0
+
+
 def test_parallel_png_is_a_valid_png_with_the_same_pixels(tmp_path):
     """The banded (pigz-style) encoder of the animation path decodes to the same pixels as the
     single-stream one, with our reader and with Pillow when it is installed."""
