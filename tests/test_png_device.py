@@ -163,7 +163,12 @@ def test_single_launch_file_equals_bands_plus_pack(tmp_path):
     lib = abi.load()
     rng = np.random.default_rng(7)
     stream = int(torch.cuda.current_stream(0).cuda_stream)
-    for name, img in list(_images(rng)) + [("noise 1920x1080 (every band stored)", rng.integers(0, 256, (1080, 1920, 3), dtype=np.uint8))]:
+    big = np.zeros((2200, 7680, 3), dtype=np.uint8)  # 2 200 bands of one row: more bands than blocks fit the GPU at once,
+    big[:, :, 0] = (np.arange(7680) // 11 % 256).astype(np.uint8)  # so late blocks wait on the sizes of blocks long gone
+    big[500:900, 1000:5000] = rng.integers(0, 256, (400, 4000, 3), dtype=np.uint8)
+    big[1500:, :, 2] = (np.arange(700)[:, None] % 256).astype(np.uint8)
+    for name, img in list(_images(rng)) + [("noise 1920x1080 (every band stored)", rng.integers(0, 256, (1080, 1920, 3), dtype=np.uint8)),
+                                            ("mixed 7680x2200 (2 200 bands)", big)]:
         h, w, _ = img.shape
         pixels = torch.from_numpy(np.ascontiguousarray(img)).cuda()
         scratch_bytes, capacity = int(lib.rt_png_scratch_bytes(w, h)), int(lib.rt_png_file_bound(w, h))
